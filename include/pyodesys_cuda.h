@@ -1,0 +1,145 @@
+/*
+ * pyodesys_cuda.h - C ABI of one compiled ODE system (one shared library per system).
+ *
+ * A library exporting these symbols is what pyodesys' native layer would bind for a
+ * ``cuda`` back end, next to the Cython modules ``_cvode_wrapper`` / ``_odeint_wrapper`` /
+ * ``_gsl_wrapper``.  Each entry point names the reference interface it replaces
+ * (paths relative to the pyodesys source tree):
+ *
+ *   pyodesys_cuda_integrate_predefined  <->  integrate_predefined(y0, xout, params, atol, rtol,
+ *        dx0, dx_max, mxsteps, method, autorestart, return_on_error, special_settings)
+ *        pyodesys/native/sources/_odeint_wrapper.pyx:111-177, _cvode_wrapper.pyx:238-365,
+ *        _gsl_wrapper.pyx:117-194  (which call multi_predefined<OdeSys>, :163-166)
+ *   pyodesys_cuda_integrate_adaptive    <->  integrate_adaptive(y0, x0, xend, params, ...)
+ *        _odeint_wrapper.pyx:37-108, _cvode_wrapper.pyx:78-235, _gsl_wrapper.pyx:37-114
+ *        (multi_adaptive<OdeSys>, :89-92)
+ *   pyodesys_cuda_info                  <->  OdeSys::get_ny()/get_nnz()/get_nroots()
+ *        pyodesys/native/sources/odesys_anyode_template.cpp:127-145
+ *   per-system ``status`` / ``counters``  <->  AnyODE::Status and AnyODE::Info
+ *        external/anyode/include/anyode/anyode.hpp:25-92,125
+ *
+ * Conventions
+ *   - every array is float64 / int32, C-contiguous, row-major exactly as the Cython wrappers
+ *     receive them: y0[n,ny], params[n,np_tot], xout[n,nt] (or one shared row, see options),
+ *     yout[n,nt,ny];
+ *   - the caller owns every buffer; nothing returned needs to be freed;
+ *   - ptr_kind 0: all array arguments are host pointers (pageable or pinned), the library
+ *     stages them through device memory (H2D, kernels, D2H inside the call);
+ *     ptr_kind 1: all array arguments (except atol) are device pointers on ``device`` and
+ *     stay resident; the call returns after the kernels completed;
+ *   - return value 0 = OK, <0 = argument or CUDA error (text via pyodesys_cuda_last_error);
+ *     failure of an individual system is NOT an error return: it is status[i] != 0 and
+ *     (predefined mode) nreached[i] < nt, like ``return_on_error`` in the reference;
+ *   - one in-flight call per device per library; distinct devices may be driven from
+ *     distinct host threads concurrently.
+ */
+#ifndef PYODESYS_CUDA_H
+#define PYODESYS_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PYODESYS_CUDA_ABI_VERSION 1
+
+/* integration methods (``method=`` keyword of the reference wrappers) */
+#define PYODESYS_CUDA_RK4 0        /* fixed step classical Runge-Kutta (pyodesys/integrators.py:17-61) */
+#define PYODESYS_CUDA_DOPRI5 1     /* odeint ``dopri5``: Dormand-Prince 5(4), dense output */
+#define PYODESYS_CUDA_ROSENBROCK4 2 /* odeint ``rosenbrock4`` (default of _odeint_wrapper.pyx:43,116) */
+#define PYODESYS_CUDA_BDF 3        /* variable step BDF + Newton, order <= 5 (cvode ``bdf`` role) */
+
+/* per-system status codes written to ``status`` */
+#define PYODESYS_CUDA_OK 0
+#define PYODESYS_CUDA_ERR_MXSTEPS 1       /* more than mxsteps steps were needed */
+#define PYODESYS_CUDA_ERR_STEP_TOO_SMALL 2 /* step size underflow (|h| <= dx_min or eps*|x|) */
+#define PYODESYS_CUDA_ERR_RHS 3           /* rhs/jac kept returning an error or produced NaN/Inf */
+#define PYODESYS_CUDA_ERR_ROWS 4          /* adaptive mode: more accepted steps than max_rows */
+
+/* counters[k*n + i], k = */
+#define PYODESYS_CUDA_NCOUNTERS 6
+#define PYODESYS_CUDA_C_NSTEPS 0
+#define PYODESYS_CUDA_C_NFEV 1
+#define PYODESYS_CUDA_C_NJEV 2
+#define PYODESYS_CUDA_C_NLU 3
+#define PYODESYS_CUDA_C_NSOLVE 4
+#define PYODESYS_CUDA_C_NREJECT 5
+
+/* timings[] (seconds) written by the integrate calls when non-NULL */
+#define PYODESYS_CUDA_NTIMINGS 4
+#define PYODESYS_CUDA_T_KERNEL 0 /* CUDA-event time of the integration kernel(s) */
+#define PYODESYS_CUDA_T_H2D 1
+#define PYODESYS_CUDA_T_D2H 2
+#define PYODESYS_CUDA_T_TOTAL 3 /* host wall clock of the whole call */
+
+/* optional knobs; pass NULL for defaults.  Mirrors the trailing constructor arguments of
+ * the generated OdeSys (odesys_anyode_template.cpp:92-98) plus launch controls. */
+typedef struct pyodesys_cuda_options {
+    double get_dx_max_factor;        /* <=0: ignore OdeSys::get_dx_max (default 0) */
+    double max_invariant_violation;  /* reserved (0 = off) */
+    int32_t error_outside_bounds;    /* nonzero: rhs outside bounds -> recoverable error */
+    int32_t xout_shared;             /* nonzero: ``xout`` is ONE row [nt] shared by all systems */
+    int32_t schedule;                /* 0 auto, 1 static (grid-stride), 2 dynamic (work stealing) */
+    int32_t block_size;              /* 0 = library default */
+    int32_t blocks_per_sm;           /* 0 = library default (persistent grid = SMs * this) */
+    int32_t yout_soa;                /* nonzero (ptr_kind 1 only): yout laid out [nt,ny,n] */
+    void *stream;                    /* cudaStream_t to launch on (ptr_kind 1); NULL = library stream */
+} pyodesys_cuda_options;
+
+/* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */
+int pyodesys_cuda_info(int *ny, int *np_tot, int *npcse, int *flops_rhs, int *flops_jac);
+
+/* abi version, warp-per-system flag, etc.: key/value lookup; returns -1 for unknown keys */
+int64_t pyodesys_cuda_query(const char *key);
+
+int pyodesys_cuda_integrate_predefined(
+    int device, int64_t n, int nt,
+    const double *y0,      /* [n, ny] */
+    const double *xout,    /* [n, nt]  (or [nt] when options->xout_shared) */
+    const double *params,  /* [n, np_tot] (NULL allowed when np_tot == 0) */
+    const double *atol, int natol, /* host; natol == 1 or ny */
+    double rtol,
+    const double *dx0,     /* [n] or NULL (0.0 = choose automatically) */
+    const double *dx_min,  /* [n] or NULL */
+    const double *dx_max,  /* [n] or NULL (inf) */
+    int64_t mxsteps, int method, int autorestart, int return_on_error,
+    double *yout,          /* [n, nt, ny] */
+    int32_t *nreached,     /* [n] number of rows of yout that are valid */
+    int32_t *status,       /* [n] */
+    int32_t *counters,     /* [PYODESYS_CUDA_NCOUNTERS, n] or NULL */
+    double *timings,       /* [PYODESYS_CUDA_NTIMINGS] host, or NULL */
+    int ptr_kind, const pyodesys_cuda_options *options);
+
+int pyodesys_cuda_integrate_adaptive(
+    int device, int64_t n,
+    const double *y0, const double *x0 /* [n] */, const double *xend /* [n] */,
+    const double *params, const double *atol, int natol, double rtol,
+    const double *dx0, const double *dx_min, const double *dx_max,
+    int64_t mxsteps, int method, int autorestart, int return_on_error,
+    int64_t max_rows_per_system,
+    double *xyout,         /* [n, max_rows_per_system, 1 + ny]: rows of (x, y...) */
+    int32_t *nrows,        /* [n] rows written per system (first row is (x0, y0)) */
+    int32_t *status, int32_t *counters, double *timings,
+    int ptr_kind, const pyodesys_cuda_options *options);
+
+/* Verification hooks (host pointers): evaluate the generated OdeSys::rhs / dense_jac_rmaj
+ * (odesys_anyode_template.cpp:147-204,246-293) for a batch, and run the in-register LU that
+ * the Rosenbrock stepper uses (role of AnyODE::getrf_callback/getrs_callback,
+ * external/anyode/include/anyode/anyode_blasless.hpp:10-95) on a batch of ny x ny systems.
+ * x[n], y[n,ny], params[n,np_tot] -> f[n,ny], jac[n,ny,ny] row-major (may be NULL), dfdt[n,ny]
+ * (may be NULL);  A[n,ny,ny] row-major, b[n,ny] -> x[n,ny], ok[n] (0 = singular). */
+int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params,
+                       double *f, double *jac, double *dfdt);
+int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok);
+
+/* Number of kernel launches issued by this library since it was loaded (bench bookkeeping). */
+int64_t pyodesys_cuda_launch_count(void);
+
+/* Thread-local, valid until the next failing call on the same thread. */
+const char *pyodesys_cuda_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYODESYS_CUDA_H */

@@ -1,0 +1,668 @@
+// ORACLE - TEST INFRASTRUCTURE ONLY.  Never imported by the product path (pyodesys_b200/).
+// Allowed users: tests/, __graft_entry__.smoke(), bench.py's cpu_baseline / --impl reference.
+//
+// CPU restatement of the reference's batched native integration path, compiled per ODE system
+// with g++ (-fopenmp) against the same generated ``odesys_generated.h`` the CUDA shim uses:
+//
+//   * batch driver: one integrator per system inside an OpenMP loop over systems, the role of
+//     multi_predefined<OdeSys> / multi_adaptive<OdeSys> (call sites
+//     pyodesys/native/sources/_odeint_wrapper.pyx:89-92,163-166, _cvode_wrapper.pyx:190-197,339-345);
+//     thread count plays ANYODE_NUM_THREADS (README.rst:215-218);
+//   * system callbacks: the generated OdeSys::rhs / dense_jac_rmaj
+//     (pyodesys/native/sources/odesys_anyode_template.cpp:147-204,246-293);
+//   * linear algebra: Doolittle LU with row pivoting + triangular solves following
+//     AnyODE::getrf_callback / getrs_callback (external/anyode/include/anyode/anyode_blasless.hpp:10-95)
+//     (the unmodified header itself is compiled into oracle/_ref and compared in tests);
+//   * steppers: the reference delegates them to third-party code that is NOT in its tree:
+//     pyodeint >= 0.10.3 -> Boost.Numeric.Odeint (Boost >= 1.72; setup.py:80, README.rst:84-86):
+//     ``runge_kutta4``, ``runge_kutta_dopri5`` + ``controlled_runge_kutta`` + dense output,
+//     ``rosenbrock4`` + ``rosenbrock4_controller`` + ``rosenbrock4_dense_output``.  Their published
+//     algorithms are restated here TABLE-DRIVEN (Butcher / Rosenbrock coefficient arrays, generic
+//     loops) - deliberately a different formulation from the hand-unrolled register code of the
+//     CUDA kernels so that the two implementations check each other.
+//
+// Parity pinning: see tests/test_oracle_golden.py (reference known answers G1-G9, fixtures generated
+// from the Python reference in this container by tests/golden/make_golden.py).
+#include "odesys_generated.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+using odesys_anyode::OdeSys;
+constexpr int NY = ODESYS_NY;
+constexpr int NP_TOT = ODESYS_NP_TOT;
+typedef std::vector<double> vec;
+
+enum { ST_OK = 0, ST_MXSTEPS = 1, ST_STEP_TOO_SMALL = 2, ST_RHS = 3, ST_ROWS = 4 };
+
+struct Settings {
+    double rtol;
+    double atol[NY];
+    double get_dx_max_factor;
+    int error_outside_bounds;
+};
+
+struct Work {
+    OdeSys sys;
+    const Settings *cfg;
+    int nlu = 0, nsolve = 0;
+    int rhs(double x, const double *y, double *f) {
+        int st = sys.rhs(x, y, f);
+#if ODESYS_HAS_BOUNDS
+        if (cfg->error_outside_bounds && sys.outside_bounds(y)) st = 1;
+#endif
+#if ODESYS_NONNEGATIVE
+        for (int i = 0; i < NY; ++i)
+            if (y[i] < 0) st = 1;
+#endif
+        return st;
+    }
+};
+
+bool all_finite(const double *v) {
+    for (int i = 0; i < NY; ++i)
+        if (!std::isfinite(v[i])) return false;
+    return true;
+}
+
+// ---- dense LU, column-major like anyode_blasless.hpp:21 (a[ci*lda + ri]) -----------------------
+struct DenseLU {
+    double a[NY * NY];
+    int ipiv[NY];
+    bool ok;
+    double &A(int ri, int ci) { return a[ci * NY + ri]; }
+    void factor() {
+        ok = true;
+        for (int i = 0; i < NY; ++i) {
+            int pivrow = i;
+            double absmax = std::fabs(A(i, i));
+            for (int j = i + 1; j < NY; ++j) {
+                const double cur = std::fabs(A(j, i));
+                if (cur > absmax) {
+                    absmax = cur;
+                    pivrow = j;
+                }
+            }
+            if (absmax == 0 || !std::isfinite(absmax)) ok = false;
+            ipiv[i] = pivrow;
+            if (pivrow != i)
+                for (int ci = 0; ci < NY; ++ci) std::swap(A(i, ci), A(pivrow, ci));
+            for (int ri = i + 1; ri < NY; ++ri) A(ri, i) /= A(i, i);
+            for (int ci = i + 1; ci < NY; ++ci) {
+                const double aici = A(i, ci);
+                for (int ri = i + 1; ri < NY; ++ri) A(ri, ci) -= A(ri, i) * aici;
+            }
+        }
+    }
+    void solve(double *b) {
+        for (int i = 0; i < NY; ++i)
+            if (ipiv[i] != i) std::swap(b[i], b[ipiv[i]]);
+        for (int i = 1; i < NY; ++i)
+            for (int j = 0; j < i; ++j) b[i] -= A(i, j) * b[j];
+        for (int i = NY - 1; i >= 0; --i) {
+            for (int j = i + 1; j < NY; ++j) b[i] -= A(i, j) * b[j];
+            b[i] /= A(i, i);
+        }
+    }
+};
+
+// ---- stepper interface ----------------------------------------------------------------------------
+struct StepperBase {
+    virtual ~StepperBase() {}
+    virtual bool adaptive() const = 0;
+    virtual int begin(Work &, double, const double *) { return 0; }
+    virtual double auto_step(Work &, double t, const double *y, double span) = 0;
+    virtual int attempt(Work &, double t, const double *y, double h, double *ynew, double *err) = 0;
+    virtual bool control(double err, double h, double *hnext) = 0;
+    virtual void accepted() {}
+    virtual void dense(double theta, const double *yold, const double *ynew, double *out) = 0;
+};
+
+// Starting step size (Hairer, Norsett, Wanner, Solving ODEs I, II.4 "Starting Step Size"; max norm).
+double starting_step(Work &w, double t0, const double *y, const double *f0, double span, int order) {
+    const Settings &c = *w.cfg;
+    double d0 = 0, d1 = 0;
+    for (int i = 0; i < NY; ++i) {
+        const double sk = c.atol[i] + c.rtol * std::fabs(y[i]);
+        d0 = std::max(d0, std::fabs(y[i]) / sk);
+        d1 = std::max(d1, std::fabs(f0[i]) / sk);
+    }
+    double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    h0 = std::min(h0, std::fabs(span));
+    const double dir = span >= 0 ? 1.0 : -1.0;
+    double y1[NY], f1[NY];
+    for (int i = 0; i < NY; ++i) y1[i] = y[i] + dir * h0 * f0[i];
+    const int st = w.rhs(t0 + dir * h0, y1, f1);
+    double d2 = 0;
+    for (int i = 0; i < NY; ++i) {
+        const double sk = c.atol[i] + c.rtol * std::fabs(y[i]);
+        d2 = std::max(d2, std::fabs(f1[i] - f0[i]) / sk);
+    }
+    d2 /= h0;
+    if (st != 0 || !std::isfinite(d2)) d2 = 0;
+    const double dmax = std::max(d1, d2);
+    const double h1 = (dmax <= 1e-15) ? std::max(1e-6, h0 * 1e-3) : std::pow(0.01 / dmax, 1.0 / order);
+    return std::min(std::min(100 * h0, h1), std::fabs(span));
+}
+
+// ---- explicit Runge-Kutta driven by a Butcher tableau ---------------------------------------------------
+struct Tableau {
+    int stages;
+    const double *c;       // [stages]
+    const double *a;       // [stages*stages] lower triangular
+    const double *b;       // [stages]
+    const double *e;       // [stages] error weights (b - bhat) or nullptr
+};
+
+const double rk4_c[4] = {0, 0.5, 0.5, 1};
+const double rk4_a[16] = {0, 0, 0, 0, 0.5, 0, 0, 0, 0, 0.5, 0, 0, 0, 0, 1, 0};
+const double rk4_b[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+const Tableau RK4 = {4, rk4_c, rk4_a, rk4_b, nullptr};
+
+// Dormand & Prince (1980) RK5(4)7M
+const double dp_c[7] = {0, 1.0 / 5, 3.0 / 10, 4.0 / 5, 8.0 / 9, 1, 1};
+const double dp_a[49] = {
+    0, 0, 0, 0, 0, 0, 0,
+    1.0 / 5, 0, 0, 0, 0, 0, 0,
+    3.0 / 40, 9.0 / 40, 0, 0, 0, 0, 0,
+    44.0 / 45, -56.0 / 15, 32.0 / 9, 0, 0, 0, 0,
+    19372.0 / 6561, -25360.0 / 2187, 64448.0 / 6561, -212.0 / 729, 0, 0, 0,
+    9017.0 / 3168, -355.0 / 33, 46732.0 / 5247, 49.0 / 176, -5103.0 / 18656, 0, 0,
+    35.0 / 384, 0, 500.0 / 1113, 125.0 / 192, -2187.0 / 6784, 11.0 / 84, 0};
+const double dp_b[7] = {35.0 / 384, 0, 500.0 / 1113, 125.0 / 192, -2187.0 / 6784, 11.0 / 84, 0};
+const double dp_bhat[7] = {5179.0 / 57600, 0, 7571.0 / 16695, 393.0 / 640, -92097.0 / 339200, 187.0 / 2100, 1.0 / 40};
+const Tableau DP5 = {7, dp_c, dp_a, dp_b, dp_bhat};
+// dense output weights of dopri5.f (CONTD5)
+const double dp_d[7] = {-12715105075.0 / 11282082432.0, 0, 87487479700.0 / 32700410799.0,
+                        -10690763975.0 / 1880347072.0, 701980252875.0 / 199316789632.0,
+                        -1453857185.0 / 822651844.0, 69997945.0 / 29380423.0};
+
+struct ExplicitRK : StepperBase {
+    const Tableau &tb;
+    bool fsal;
+    int order;
+    double k[7][NY];
+    double kfirst[NY];
+    double hlast;
+    double ylast_old[NY], ylast_new[NY];
+    ExplicitRK(const Tableau &t, bool fsal_, int order_) : tb(t), fsal(fsal_), order(order_) {}
+    bool adaptive() const override { return tb.e != nullptr || fsal; }
+    int begin(Work &w, double t, const double *y) override {
+        if (fsal) return w.rhs(t, y, kfirst);
+        return 0;
+    }
+    double auto_step(Work &w, double t, const double *y, double span) override {
+        return starting_step(w, t, y, kfirst, span, order) * (span >= 0 ? 1 : -1);
+    }
+    int attempt(Work &w, double t, const double *y, double h, double *ynew, double *err) override {
+        int bad = 0;
+        double tmp[NY];
+        for (int s = 0; s < tb.stages; ++s) {
+            if (s == 0 && fsal) {
+                std::memcpy(k[0], kfirst, sizeof(kfirst));
+                continue;
+            }
+            for (int i = 0; i < NY; ++i) {
+                double acc = 0;
+                for (int j = 0; j < s; ++j) acc += tb.a[s * tb.stages + j] * k[j][i];
+                tmp[i] = y[i] + h * acc;
+            }
+            bad |= w.rhs(t + tb.c[s] * h, tmp, k[s]);
+            if (fsal && s == tb.stages - 1) std::memcpy(ynew, tmp, sizeof(tmp));
+        }
+        if (!fsal) {
+            for (int i = 0; i < NY; ++i) {
+                double acc = 0;
+                for (int s = 0; s < tb.stages; ++s) acc += tb.b[s] * k[s][i];
+                ynew[i] = y[i] + h * acc;
+            }
+            *err = 0;
+            return bad;
+        }
+        // odeint default_error_checker: max_i |err_i| / (eps_abs + eps_rel (|x_i| + |dt| |dxdt_i|))
+        const Settings &c = *w.cfg;
+        double e = 0;
+        for (int i = 0; i < NY; ++i) {
+            double acc = 0;
+            for (int s = 0; s < tb.stages; ++s) acc += (dp_b[s] - dp_bhat[s]) * k[s][i];
+            const double sc = c.atol[i] + c.rtol * (std::fabs(y[i]) + std::fabs(h) * std::fabs(k[0][i]));
+            e = std::max(e, std::fabs(h * acc) / sc);
+        }
+        *err = e;
+        hlast = h;
+        std::memcpy(ylast_old, y, sizeof(ylast_old));
+        std::memcpy(ylast_new, ynew, sizeof(ylast_new));
+        if (!std::isfinite(e)) bad |= 1;
+        return bad;
+    }
+    // odeint default_step_adjuster (stepper order 5, error order 4)
+    bool control(double err, double h, double *hnext) override {
+        if (!fsal) {
+            *hnext = h;
+            return true;
+        }
+        if (err > 1.0) {
+            *hnext = h * std::max(0.9 * std::pow(err, -1.0 / 3.0), 0.2);
+            return false;
+        }
+        *hnext = h;
+        if (err < 0.5) {
+            const double e = std::max(std::pow(5.0, -5.0), err);
+            *hnext = h * std::min(0.9 * std::pow(e, -1.0 / 5.0), 5.0);
+        }
+        return true;
+    }
+    void accepted() override {
+        if (fsal) std::memcpy(kfirst, k[tb.stages - 1], sizeof(kfirst));
+    }
+    void dense(double th, const double *yold, const double *ynew, double *out) override {
+        if (!fsal) {
+            for (int i = 0; i < NY; ++i) out[i] = yold[i] + th * (ynew[i] - yold[i]);
+            return;
+        }
+        const double th1 = 1 - th;
+        for (int i = 0; i < NY; ++i) {
+            const double ydiff = ynew[i] - yold[i];
+            const double bspl = hlast * k[0][i] - ydiff;
+            const double r4 = ydiff - hlast * k[6][i] - bspl;
+            double r5 = 0;
+            for (int s = 0; s < 7; ++s) r5 += dp_d[s] * k[s][i];
+            r5 *= hlast;
+            out[i] = yold[i] + th * (ydiff + th1 * (bspl + th * (r4 + th1 * r5)));
+        }
+    }
+};
+
+#if ODESYS_HAS_JAC
+// ---- Rosenbrock 4(3): (I/(gamma h) - J) u_i = f(y + sum a_ij u_j) + sum c_ij u_j / h + h d_i f_t -----------
+// Coefficients: oracle/check_ros4_coeffs.py proves them against the order conditions.
+const double ros_gamma = 0.25;
+const double ros_a[6][6] = {
+    {0, 0, 0, 0, 0, 0},
+    {0.1544000000000000e+01, 0, 0, 0, 0, 0},
+    {0.9466785280815826e+00, 0.2557011698983284e+00, 0, 0, 0, 0},
+    {0.3314825187068521e+01, 0.2896124015972201e+01, 0.9986419139977817e+00, 0, 0, 0},
+    {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950e+00, 0, 0},
+    {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950e+00, 1, 0}};
+const double ros_c[6][6] = {
+    {0, 0, 0, 0, 0, 0},
+    {-0.5668800000000000e+01, 0, 0, 0, 0, 0},
+    {-0.2430093356833875e+01, -0.2063599157091915e+00, 0, 0, 0, 0},
+    {-0.1073529058151375e+00, -0.9594562251023355e+01, -0.2047028614809616e+02, 0, 0, 0},
+    {0.7496443313967647e+01, -0.1024680431464352e+02, -0.3399990352819905e+02, 0.1170890893206160e+02, 0, 0},
+    {0.8083246795921522e+01, -0.7981132988064893e+01, -0.3152159432874371e+02, 0.1631930543123136e+02,
+     -0.6058818238834054e+01, 0}};
+const double ros_ct[6] = {0, 0.386, 0.21, 0.63, 1, 1};
+const double ros_d[6] = {0.25, -0.1043, 0.1035, -0.3620000000000023e-01, 0, 0};
+const double ros_dense[2][5] = {
+    {0.1012623508344586e+02, -0.7487995877610167e+01, -0.3480091861555747e+02, -0.7992771707568823e+01,
+     0.1025137723295662e+01},
+    {-0.6762803392801253e+00, 0.6087714651680015e+01, 0.1643084320892478e+02, 0.2476722511418386e+02,
+     -0.6594389125716872e+01}};
+
+struct Rosenbrock4 : StepperBase {
+    double u[6][NY];
+    double cont3[NY], cont4[NY];
+    bool first = true, last_rejected = false;
+    double h_old = 0, err_old = 1;
+    bool adaptive() const override { return true; }
+    int begin(Work &, double, const double *) override {
+        first = true;
+        last_rejected = false;
+        h_old = 0;
+        err_old = 1;
+        return 0;
+    }
+    double auto_step(Work &w, double t, const double *y, double span) override {
+        double f0[NY];
+        w.rhs(t, y, f0);
+        return starting_step(w, t, y, f0, span, 4) * (span >= 0 ? 1 : -1);
+    }
+    int attempt(Work &w, double t, const double *y, double h, double *ynew, double *err) override {
+        int bad = 0;
+        double f[NY], J[NY * NY], dfdt[NY], ytmp[NY];
+        bad |= w.rhs(t, y, f);
+        bad |= w.sys.dense_jac_rmaj(t, y, f, J, NY, dfdt);
+        DenseLU lu;
+        for (int r = 0; r < NY; ++r)
+            for (int cidx = 0; cidx < NY; ++cidx)
+                lu.A(r, cidx) = (r == cidx ? 1.0 / (ros_gamma * h) : 0.0) - J[r * NY + cidx];
+        lu.factor();
+        w.nlu += 1;
+        if (!lu.ok) bad |= 1;
+        for (int s = 0; s < 6; ++s) {
+            if (s > 0) {
+                for (int i = 0; i < NY; ++i) {
+                    double acc = y[i];
+                    for (int j = 0; j < s; ++j) acc += ros_a[s][j] * u[j][i];
+                    ytmp[i] = acc;
+                }
+                bad |= w.rhs(t + ros_ct[s] * h, ytmp, f);
+            }
+            for (int i = 0; i < NY; ++i) {
+                double acc = 0;
+                for (int j = 0; j < s; ++j) acc += ros_c[s][j] * u[j][i];
+                u[s][i] = f[i] + acc / h + h * ros_d[s] * dfdt[i];
+            }
+            lu.solve(u[s]);
+            w.nsolve += 1;
+        }
+        const Settings &c = *w.cfg;
+        double e = 0;
+        for (int i = 0; i < NY; ++i) {
+            ynew[i] = ytmp[i] + u[5][i];  // ytmp = y + sum_{j<5} a_6j u_j  (a_65 = 1)
+            const double sk = c.atol[i] + c.rtol * std::max(std::fabs(y[i]), std::fabs(ynew[i]));
+            e = std::max(e, std::fabs(u[5][i]) / sk);
+            cont3[i] = cont4[i] = 0;
+            for (int j = 0; j < 5; ++j) {
+                cont3[i] += ros_dense[0][j] * u[j][i];
+                cont4[i] += ros_dense[1][j] * u[j][i];
+            }
+        }
+        *err = e;
+        if (!std::isfinite(e)) bad |= 1;
+        return bad;
+    }
+    // rosenbrock4_controller::try_step
+    bool control(double err, double h, double *hnext) override {
+        const double safe = 0.9, fac1 = 5.0, fac2 = 1.0 / 6.0;
+        double fac = std::max(fac2, std::min(fac1, std::pow(err, 0.25) / safe));
+        double hn = h / fac;
+        if (err <= 1.0) {
+            if (!first) {
+                double fp = (h_old / h) * std::pow(err * err / err_old, 0.25) / safe;
+                fp = std::max(fac2, std::min(fac1, fp));
+                fac = std::max(fac, fp);
+                hn = h / fac;
+            }
+            first = false;
+            h_old = h;
+            err_old = std::max(0.01, err);
+            if (last_rejected) hn = (h >= 0) ? std::min(hn, h) : std::max(hn, h);
+            last_rejected = false;
+            *hnext = hn;
+            return true;
+        }
+        last_rejected = true;
+        *hnext = hn;
+        return false;
+    }
+    void dense(double s, const double *yold, const double *ynew, double *out) override {
+        const double s1 = 1 - s;
+        for (int i = 0; i < NY; ++i) out[i] = yold[i] * s1 + s * (ynew[i] + s1 * (cont3[i] + s * cont4[i]));
+    }
+};
+#endif
+
+StepperBase *make_stepper(int method) {
+    switch (method) {
+    case 0: return new ExplicitRK(RK4, false, 4);
+    case 1: return new ExplicitRK(DP5, true, 5);
+#if ODESYS_HAS_JAC
+    case 2: return new Rosenbrock4();
+#endif
+    default: return nullptr;
+    }
+}
+
+struct Job {
+    int64_t n;
+    int nt;
+    const double *y0, *params, *xout;
+    int64_t xout_stride;
+    const double *x0, *xend, *dx0, *dx_min, *dx_max;
+    int64_t mxsteps;
+    int autorestart;
+    double *yout, *xyout;
+    int64_t max_rows;
+    int32_t *nrows, *nreached, *status, *counters;
+};
+
+// One system, start to finish: the body of the reference's OpenMP loop.
+void run_one(const Job &J, const Settings &cfg, int method, int mode, int64_t s) {
+    Work w;
+    w.cfg = &cfg;
+    for (int i = 0; i < NP_TOT; ++i) w.sys.m_p[i] = J.params[s * NP_TOT + i];
+    w.sys.setup();
+    StepperBase *st = make_stepper(method);
+    double y[NY], ynew[NY];
+    for (int i = 0; i < NY; ++i) y[i] = J.y0[s * NY + i];
+    const double *xo = (mode == 0) ? J.xout + s * J.xout_stride : nullptr;
+    double t = (mode == 0) ? xo[0] : J.x0[s];
+    const double tend = (mode == 0) ? xo[J.nt - 1] : J.xend[s];
+    const double dir = tend >= t ? 1.0 : -1.0;
+    int k_out = 1;
+    if (mode == 0) {
+        for (int i = 0; i < NY; ++i) J.yout[(s * J.nt) * NY + i] = y[i];
+        if (tend == t)
+            for (; k_out < J.nt; ++k_out)
+                for (int i = 0; i < NY; ++i) J.yout[(s * J.nt + k_out) * NY + i] = y[i];
+    } else {
+        double *row = J.xyout + (s * J.max_rows) * (1 + NY);
+        row[0] = t;
+        for (int i = 0; i < NY; ++i) row[1 + i] = y[i];
+    }
+    const double hmin = J.dx_min ? J.dx_min[s] : 0.0;
+    double hmax = J.dx_max ? J.dx_max[s] : INFINITY;
+    if (!(hmax > 0)) hmax = INFINITY;
+    const int64_t budget = J.mxsteps > 0 ? J.mxsteps : std::numeric_limits<int64_t>::max();
+    int64_t steps_left = budget;
+    int restarts = J.autorestart, nfail = 0, nsteps = 0, nreject = 0;
+    int bad0 = st->begin(w, t, y);
+    double h = J.dx0 ? J.dx0[s] : 0.0;
+#if ODESYS_HAS_FIRST_STEP
+    if (h == 0.0) h = w.sys.get_dx0(t, y);
+#endif
+    if (h != 0.0) h = std::fabs(h) * dir;
+    else if (method == 0) h = (mode == 0) ? dir * INFINITY : (tend - t) / 100.0;
+    else h = st->auto_step(w, t, y, tend - t);
+    if (bad0 || !all_finite(y)) nfail = 1 << 20;
+    int status = -1;
+    while (true) {
+        if (nfail >= (1 << 20)) status = ST_RHS;
+        else if (t == tend) status = ST_OK;
+        else if (steps_left <= 0) {
+            if (restarts > 0) {
+                restarts -= 1;
+                steps_left = J.mxsteps;
+                st->begin(w, t, y);
+                if (method != 0) h = st->auto_step(w, t, y, tend - t);
+            } else {
+                status = ST_MXSTEPS;
+            }
+        }
+        if (status >= 0) break;
+        double hh = h;
+        if (std::fabs(hh) > hmax) hh = dir * hmax;
+#if ODESYS_HAS_DX_MAX
+        if (cfg.get_dx_max_factor > 0.0) {
+            const double m = cfg.get_dx_max_factor * w.sys.get_dx_max(t, y);
+            if (std::fabs(hh) > m) hh = dir * m;
+        }
+#endif
+        if (st->adaptive() && std::fabs(hh) < hmin) hh = dir * hmin;
+        double target = tend;
+        if (method == 0 && mode == 0) target = xo[k_out];
+        const double rem = target - t;
+        const bool lands = std::fabs(hh) >= std::fabs(rem) * (1.0 - 1e-13);
+        double tnew = t + hh;
+        if (lands) {
+            hh = rem;
+            tnew = target;
+        }
+        const bool hits_end = lands && (target == tend);
+        double err = 0, hnext = hh;
+        const int bad = st->attempt(w, t, y, hh, ynew, &err);
+        nsteps += 1;
+        steps_left -= 1;
+        bool ok;
+        if (bad || !all_finite(ynew)) {
+            ok = false;
+            nfail += 1;
+            if (nfail >= 12 || !st->adaptive()) nfail = 1 << 20;
+            double ignored;
+            st->control(2.0, hh, &ignored);
+            hnext = 0.25 * hh;
+        } else {
+            ok = st->control(err, hh, &hnext);
+            if (ok) nfail = 0;
+        }
+        if (!ok) {
+            nreject += 1;
+            if (st->adaptive() && (std::fabs(hnext) <= 16.0 * DBL_EPSILON * std::fabs(t) || hnext == 0.0 ||
+                                   (hmin > 0.0 && std::fabs(hh) <= hmin)))
+                status = ST_STEP_TOO_SMALL;
+            h = hnext;
+            if (status >= 0) break;
+            continue;
+        }
+        if (mode == 0) {
+            while (k_out < J.nt) {
+                const double xk = xo[k_out];
+                if ((xk - tnew) * dir > 0.0) break;
+                double yo[NY];
+                if (xk == tnew) std::memcpy(yo, ynew, sizeof(yo));
+                else st->dense((xk - t) / hh, y, ynew, yo);
+                for (int i = 0; i < NY; ++i) J.yout[(s * J.nt + k_out) * NY + i] = yo[i];
+                k_out += 1;
+                steps_left = budget;
+            }
+        } else {
+            if (k_out >= J.max_rows) {
+                status = ST_ROWS;
+                break;
+            }
+            double *row = J.xyout + (s * J.max_rows + k_out) * (1 + NY);
+            row[0] = tnew;
+            for (int i = 0; i < NY; ++i) row[1 + i] = ynew[i];
+            k_out += 1;
+        }
+        st->accepted();
+        std::memcpy(y, ynew, sizeof(y));
+        t = hits_end ? tend : tnew;
+        if (st->adaptive()) h = hnext;
+    }
+    J.status[s] = status;
+    if (mode == 0) {
+        J.nreached[s] = k_out;
+        if (status != ST_OK)
+            for (int k = k_out; k < J.nt; ++k)
+                for (int i = 0; i < NY; ++i) J.yout[(s * J.nt + k) * NY + i] = NAN;
+    } else {
+        J.nrows[s] = k_out;
+    }
+    if (J.counters) {
+        J.counters[0 * J.n + s] = nsteps;
+        J.counters[1 * J.n + s] = w.sys.nfev;
+        J.counters[2 * J.n + s] = w.sys.njev;
+        J.counters[3 * J.n + s] = w.nlu;
+        J.counters[4 * J.n + s] = w.nsolve;
+        J.counters[5 * J.n + s] = nreject;
+    }
+    delete st;
+}
+
+void run_batch(const Job &J, const Settings &cfg, int method, int mode, int nthreads) {
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic, 16)
+    for (int64_t s = 0; s < J.n; ++s) run_one(J, cfg, method, mode, s);
+}
+
+Settings make_settings(const double *atol, int natol, double rtol, double get_dx_max_factor, int eob) {
+    Settings c;
+    c.rtol = rtol;
+    for (int i = 0; i < NY; ++i) c.atol[i] = atol[natol == 1 ? 0 : i];
+    c.get_dx_max_factor = get_dx_max_factor;
+    c.error_outside_bounds = eob;
+    return c;
+}
+
+}  // namespace
+
+extern "C" {
+
+int oracle_info(int *ny, int *np_tot) {
+    *ny = NY;
+    *np_tot = NP_TOT;
+    return 0;
+}
+
+int oracle_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+int oracle_integrate_predefined(int64_t n, int nt, const double *y0, const double *xout, int xout_shared,
+                                const double *params, const double *atol, int natol, double rtol,
+                                const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
+                                int method, int autorestart, double get_dx_max_factor, int error_outside_bounds,
+                                double *yout, int32_t *nreached, int32_t *status, int32_t *counters, int nthreads) {
+    if (method < 0 || method > 2 || (method == 2 && !ODESYS_HAS_JAC)) return -1;
+    Job J;
+    std::memset(&J, 0, sizeof(J));
+    J.n = n; J.nt = nt; J.y0 = y0; J.params = params; J.xout = xout; J.xout_stride = xout_shared ? 0 : nt;
+    J.dx0 = dx0; J.dx_min = dx_min; J.dx_max = dx_max; J.mxsteps = mxsteps; J.autorestart = autorestart;
+    J.yout = yout; J.nreached = nreached; J.status = status; J.counters = counters;
+    const Settings cfg = make_settings(atol, natol, rtol, get_dx_max_factor, error_outside_bounds);
+    run_batch(J, cfg, method, 0, nthreads);
+    return 0;
+}
+
+int oracle_integrate_adaptive(int64_t n, const double *y0, const double *x0, const double *xend,
+                              const double *params, const double *atol, int natol, double rtol, const double *dx0,
+                              const double *dx_min, const double *dx_max, int64_t mxsteps, int method,
+                              int autorestart, double get_dx_max_factor, int error_outside_bounds, int64_t max_rows,
+                              double *xyout, int32_t *nrows, int32_t *status, int32_t *counters, int nthreads) {
+    if (method < 0 || method > 2 || (method == 2 && !ODESYS_HAS_JAC)) return -1;
+    Job J;
+    std::memset(&J, 0, sizeof(J));
+    J.n = n; J.y0 = y0; J.params = params; J.x0 = x0; J.xend = xend;
+    J.dx0 = dx0; J.dx_min = dx_min; J.dx_max = dx_max; J.mxsteps = mxsteps; J.autorestart = autorestart;
+    J.xyout = xyout; J.max_rows = max_rows; J.nrows = nrows; J.status = status; J.counters = counters;
+    const Settings cfg = make_settings(atol, natol, rtol, get_dx_max_factor, error_outside_bounds);
+    run_batch(J, cfg, method, 1, nthreads);
+    return 0;
+}
+
+int oracle_eval(int64_t n, const double *x, const double *y, const double *params, double *f, double *jac,
+                double *dfdt) {
+    for (int64_t s = 0; s < n; ++s) {
+        OdeSys sys;
+        for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+        sys.setup();
+        sys.rhs(x[s], y + s * NY, f + s * NY);
+#if ODESYS_HAS_JAC
+        if (jac) sys.dense_jac_rmaj(x[s], y + s * NY, f + s * NY, jac + s * NY * NY, NY, dfdt ? dfdt + s * NY : nullptr);
+#endif
+    }
+    return 0;
+}
+
+int oracle_lu_solve(int64_t n, const double *A, const double *b, double *x, int32_t *ok) {
+    for (int64_t s = 0; s < n; ++s) {
+        DenseLU lu;
+        for (int r = 0; r < NY; ++r)
+            for (int c = 0; c < NY; ++c) lu.A(r, c) = A[s * NY * NY + r * NY + c];
+        lu.factor();
+        for (int i = 0; i < NY; ++i) x[s * NY + i] = b[s * NY + i];
+        lu.solve(x + s * NY);
+        ok[s] = lu.ok ? 1 : 0;
+    }
+    return 0;
+}
+}

@@ -1,0 +1,307 @@
+# -*- coding: utf-8 -*-
+"""
+Host-side driver for the batched native path: argument shaping, dispatch and results.
+
+Mirrors the slice of ``pyodesys.core.ODESys`` that the batched native ``integrate`` call
+runs through (``pyodesys/core.py:240-290`` ``to_arrays``/``pre_process``,
+``core.py:400-449`` ``integrate``) and ``pyodesys.results.Result``
+(``pyodesys/results.py:13-57``).  Everything below the ``_integrate_native`` dispatch is
+CUDA (see :mod:`pyodesys_b200.native.cuda`).
+
+The only deliberate extension is :class:`BatchResult`: the reference builds ``N`` ``Result``
+objects and ``N`` info dicts in a Python loop (``core.py:436-441``, ``native/_base.py:331-340``)
+which at N=1e6 costs orders of magnitude more than the device work; ``BatchResult`` keeps
+the arrays and materialises a ``Result`` on ``__getitem__``.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+class Result:
+    """ Same attribute and tuple-unpacking layout as ``pyodesys/results.py:13-40``. """
+
+    def __init__(self, xout, yout, params, info, odesys):
+        self.xout = xout
+        self.yout = yout
+        self.params = params
+        self.info = info
+        self.odesys = odesys
+        self.names = getattr(odesys, 'names', ())
+
+    def copy(self):
+        return Result(self.xout.copy(), self.yout.copy(), self.params.copy(),
+                      self.info.copy(), self.odesys)
+
+    def __len__(self):
+        return 3
+
+    def __getitem__(self, key):
+        if key == 0:
+            return self.xout
+        elif key == 1:
+            return self.yout
+        elif key == 2:
+            return self.info
+        elif key == 3:
+            raise StopIteration
+        raise KeyError("Invalid key: %s (for backward compatibility reasons)." % str(key))
+
+    def named_param(self, param_name):
+        return self.params[self.odesys.param_names.index(param_name)]
+
+    def named_dep(self, name):
+        return self.yout[..., self.odesys.names.index(name)]
+
+    def between(self, lower, upper, xdata=None, ydata=None):
+        xdata = self.xout if xdata is None else xdata
+        ydata = self.yout if ydata is None else ydata
+        sel = (xdata > lower) & (xdata < upper)
+        return xdata[..., sel], ydata[..., sel, :]
+
+
+class BatchInfo:
+    """ Array-backed per-system info: ``batch_info[i]`` builds the reference's dict.
+
+    Keys per system follow ``_odeint_wrapper.pyx:25-34`` (``mode``, ``success``,
+    ``nreached`` + the integer/double ``Info`` maps) and ``native/_base.py:331-340``
+    (``internal_xout``, ``internal_yout``, ``internal_params``, ``nfev``/``njev`` aliases).
+    """
+
+    counter_names = ('n_steps', 'nfev', 'njev', 'nlu', 'nsolve', 'nreject')
+
+    def __init__(self, mode, status, nreached, counters, time_wall, time_cpu, xout, yout, params,
+                 return_on_error, nt=None, timings=None, method=None):
+        self.mode = mode
+        self.status = status
+        self.nreached = nreached
+        self.counters = counters
+        self.time_wall = time_wall
+        self.time_cpu = time_cpu
+        self.xout = xout
+        self.yout = yout
+        self.params = params
+        self.return_on_error = return_on_error
+        self.nt = nt
+        self.timings = timings or {}
+        self.method = method
+
+    def __len__(self):
+        return len(self.status)
+
+    def success(self):
+        return self.status == 0
+
+    def __getitem__(self, i):
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        c = self.counters[:, i]  # SoA [ncounters, N] as written by the kernel
+        d = {k: int(c[j]) for j, k in enumerate(self.counter_names)}
+        d['n_rhs_evals'] = d['nfev']
+        d['dense_n_dls_jac_evals'] = d['njev']
+        d['n_lu'] = d.pop('nlu')
+        d['n_solve'] = d.pop('nsolve')
+        d['n_err_test_fails'] = d.pop('nreject')
+        d['time_wall'] = self.time_wall
+        d['time_cpu'] = self.time_cpu
+        d['mode'] = self.mode
+        d['status'] = int(self.status[i])
+        d['success'] = bool(self.status[i] == 0)
+        if self.mode == 'predefined':
+            d['nreached'] = int(self.nreached[i])
+        d['internal_xout'] = self.xout[i]
+        d['internal_yout'] = self.yout[i]
+        d['internal_params'] = self.params[i, ...]
+        if self.method is not None:
+            d['method'] = self.method
+        return d
+
+    def __iter__(self):
+        for i in range(len(self)):
+            yield self[i]
+
+
+class BatchResult:
+    """ Lazy list of :class:`Result` (``len``, indexing, slicing and iteration like a list).
+
+    ``xout``/``yout``/``params`` are the *internal* arrays; post-processors run when an
+    element is materialised, exactly where ``core.py:439-441`` runs them.
+    """
+
+    def __init__(self, info, odesys):
+        self.info = info
+        self.odesys = odesys
+        self._cache = {}
+
+    @property
+    def xout(self):
+        return self.info.xout
+
+    @property
+    def yout(self):
+        return self.info.yout
+
+    @property
+    def params(self):
+        return self.info.params
+
+    def __len__(self):
+        return len(self.info)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
+        if i not in self._cache:
+            nfo = self.info[i]
+            x, y, p = self.odesys.post_process(nfo['internal_xout'], nfo['internal_yout'],
+                                               nfo['internal_params'])
+            r = Result(x, y, p, nfo, self.odesys)
+            if len(self._cache) > 4096:
+                self._cache.clear()
+            self._cache[i] = r
+        return self._cache[i]
+
+    def __iter__(self):
+        for i in range(len(self)):
+            yield self[i]
+
+
+class ODESys:
+    """ Argument shaping + dispatch of the reference's ``ODESys`` for the native path. """
+
+    append_iv = False
+    numpy = np
+
+    def __init__(self, names=(), param_names=(), dep_by_name=False, par_by_name=False,
+                 pre_processors=None, post_processors=None, append_iv=False,
+                 to_arrays_callbacks=None, indep_name=None, description=None, **kwargs):
+        if kwargs:
+            raise TypeError("Unsupported keyword arguments: %s" % ', '.join(sorted(kwargs)))
+        self.names = tuple(names or ())
+        self.param_names = tuple(param_names or ())
+        self.dep_by_name = dep_by_name
+        self.par_by_name = par_by_name
+        self.pre_processors = list(pre_processors or [])
+        self.post_processors = list(post_processors or [])
+        self.append_iv = append_iv
+        self.to_arrays_callbacks = to_arrays_callbacks
+        self.indep_name = indep_name
+        self.description = description
+        self.taken_names = ()
+
+    # -- ``core.py:209-238`` ------------------------------------------------------------
+    @staticmethod
+    def _array_from_dict(d, keys):
+        vals = [d[k] for k in keys]
+        lens = [len(v) if hasattr(v, '__len__') else 0 for v in vals]
+        n = max(lens) if lens else 0
+        if n == 0:
+            return np.array(vals, dtype=np.float64)
+        if any(ln not in (0, n) for ln in lens):
+            raise ValueError("Mixed lengths in dictionary.")
+        out = np.empty((n, len(keys)), dtype=np.float64)
+        for idx, v in enumerate(vals):
+            out[:, idx] = v
+        return out
+
+    def _conditional_from_dict(self, cont, by_name, names):
+        if isinstance(cont, dict):
+            if not by_name:
+                raise ValueError("not by name, yet a dictionary was passed.")
+            cont = self._array_from_dict(cont, names)
+        return cont
+
+    # -- ``core.py:240-284`` ------------------------------------------------------------
+    def to_arrays(self, x, y, p, callbacks=None, reshape=True):
+        try:
+            nx = len(x)
+        except TypeError:
+            _x = 0*x, x
+        else:
+            _x = (0*x[0], x[0]) if nx == 1 else x
+        _y = self._conditional_from_dict(y, self.dep_by_name, self.names)
+        _p = self._conditional_from_dict(p, self.par_by_name, self.param_names)
+        callbacks = callbacks or self.to_arrays_callbacks
+        if callbacks is not None:
+            if len(callbacks) != 3:
+                raise ValueError("Need 3 callbacks/None values.")
+            _x, _y, _p = [e if cb is None else cb(e) for cb, e in zip(callbacks, [_x, _y, _p])]
+        arrs = [np.atleast_1d(np.asarray(a, dtype=np.float64)) for a in (_x, _y, _p)]
+        if reshape:
+            extra = None
+            for a in arrs:
+                if a.ndim == 1:
+                    continue
+                elif a.ndim == 2:
+                    if extra is None:
+                        extra = a.shape[0]
+                    elif extra != a.shape[0]:
+                        raise ValueError("Size mismatch!")
+                else:
+                    raise NotImplementedError("Only 2 dimensions currently supported.")
+            if extra is not None:
+                # broadcast views instead of the reference's numpy.tile (core.py:282-283):
+                # no O(N) copy until the native shim needs contiguous memory.
+                arrs = [a if a.ndim == 2 else np.broadcast_to(a, (extra, a.shape[0])) for a in arrs]
+        return arrs
+
+    def pre_process(self, xout, y0, params=()):
+        for pre in self.pre_processors:
+            xout, y0, params = pre(xout, y0, params)
+        return [np.atleast_1d(a) for a in (xout, y0, params)]
+
+    def post_process(self, xout, yout, params):
+        for post in self.post_processors:
+            xout, yout, params = post(xout, yout, params)
+        return xout, yout, params
+
+    def adaptive(self, y0, x0, xend, params=(), **kwargs):
+        """ ``core.py:298-321`` """
+        return self.integrate((x0, xend), y0, params=params, **kwargs)
+
+    def predefined(self, y0, xout, params=(), **kwargs):
+        """ ``core.py:323-345`` """
+        xout, yout, info = self.integrate(xout, y0, params=params, force_predefined=True, **kwargs)
+        return yout, info
+
+    # -- ``core.py:347-449`` ------------------------------------------------------------
+    def integrate(self, x, y0, params=(), atol=1e-8, rtol=1e-8, **kwargs):
+        arrs = self.to_arrays(x, y0, params)
+        _x, _y, _p = _arrs = self.pre_process(*arrs)
+        ndims = [a.ndim for a in _arrs]
+        if ndims == [1, 1, 1]:
+            twodim = False
+        elif ndims == [2, 2, 2]:
+            twodim = True
+        else:
+            raise ValueError("Pre-processor made ndims inconsistent?")
+
+        if self.append_iv:
+            _p = np.concatenate((_p, _y), axis=-1)
+
+        if hasattr(self, 'ny') and _y.shape[-1] != self.ny:
+            raise ValueError("Incorrect shape of intern_y0")
+        if isinstance(atol, dict):
+            kwargs['atol'] = [atol[k] for k in self.names]
+        else:
+            kwargs['atol'] = atol
+        kwargs['rtol'] = rtol
+
+        integrator = kwargs.pop('integrator', None)
+        if integrator is None:
+            integrator = 'native'
+        if not isinstance(integrator, str):
+            raise ValueError("Only named integrators are supported by this back end")
+        args = tuple(map(np.atleast_2d, (_x, _y, _p)))
+        self._current_integration_kwargs = kwargs
+        binfo = getattr(self, '_integrate_' + integrator)(*args, **kwargs)
+        if twodim:
+            return BatchResult(binfo, self)
+        nfo = binfo[0]
+        self._internal = (np.array(nfo['internal_xout']), np.array(nfo['internal_yout']), _p.copy())
+        return Result(*(tuple(self.post_process(nfo['internal_xout'], nfo['internal_yout'], _p))
+                        + (nfo, self)))

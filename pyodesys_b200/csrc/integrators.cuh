@@ -1,0 +1,787 @@
+// Batched ODE integrators for sm_100a: ONE SYSTEM PER THREAD, state in registers.
+//
+// This file replaces the hot loop of the reference's batched native path: the OpenMP loop over
+// systems inside ``multi_predefined<OdeSys>`` / ``multi_adaptive<OdeSys>`` (call sites
+// pyodesys/native/sources/_odeint_wrapper.pyx:89-92,163-166; _cvode_wrapper.pyx:190-197,339-345),
+// where each iteration owns one integrator instance and calls ``OdeSys::rhs`` /
+// ``dense_jac_rmaj`` through virtual functions.  Here every lane of a persistent grid owns one
+// system at a time; when a lane finishes it fetches the next index (grid-stride or a
+// warp-aggregated atomic counter = work stealing), so divergent step counts do not idle the SM.
+//
+// The steppers restate published algorithms (the reference delegates them to Boost.odeint via
+// pyodeint, which is not vendored in the reference tree):
+//   * RK4      - classical fixed step (pyodesys/integrators.py:17-61 is the in-tree oracle);
+//   * DOPRI5   - Dormand & Prince 5(4) with FSAL, Hairer's 4th order dense output, odeint's
+//                ``controlled_runge_kutta`` error measure and step-size rule;
+//   * ROS4     - six-stage stiffly accurate Rosenbrock 4(3) (odeint ``rosenbrock4``, the default
+//                ``method`` of _odeint_wrapper.pyx:43,116) with its predictive controller and
+//                dense output; the per-system ny x ny LU lives in registers.
+// Requires the generated header (struct odesys_anyode::OdeSys, ODESYS_* macros) to be included
+// first.  float64 throughout; no tensor cores (per-system matrices are 2x2 .. 8x8 with pivoting).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include <float.h>
+
+namespace pyodesys_cuda {
+
+using odesys_anyode::OdeSys;
+constexpr int NY = ODESYS_NY;
+constexpr int NP_TOT = ODESYS_NP_TOT;
+constexpr int NP_USED = ODESYS_NP_USED;
+constexpr unsigned FULL_MASK = 0xffffffffu;
+
+enum : int { M_RK4 = 0, M_DOPRI5 = 1, M_ROS4 = 2, M_BDF = 3 };
+enum : int { ST_OK = 0, ST_MXSTEPS = 1, ST_STEP_TOO_SMALL = 2, ST_RHS = 3, ST_ROWS = 4 };
+enum : int { C_NSTEPS = 0, C_NFEV = 1, C_NJEV = 2, C_NLU = 3, C_NSOLVE = 4, C_NREJECT = 5, NCOUNT = 6 };
+
+struct KernelArgs {
+    int64_t n;
+    int nt;                 // predefined: number of output points per system
+    const double *y0;       // [n, NY]
+    const double *params;   // [n, NP_TOT]
+    const double *xout;     // predefined: [n, nt] or [nt] (xout_stride == 0)
+    int64_t xout_stride;
+    const double *x0;       // adaptive: [n]
+    const double *xend;     // adaptive: [n]
+    const double *dx0, *dx_min, *dx_max;  // [n] or nullptr
+    double atol[NY];
+    double rtol;
+    int64_t mxsteps;
+    int autorestart;
+    double get_dx_max_factor;
+    int error_outside_bounds;
+    // outputs
+    double *yout;           // predefined: [n, nt, NY]  (or [nt, NY, n] when yout_soa)
+    int yout_soa;
+    double *xyout;          // adaptive: [n, max_rows, 1+NY]
+    int64_t max_rows;
+    int32_t *nrows;         // adaptive
+    int32_t *nreached;      // predefined
+    int32_t *status;
+    int32_t *counters;      // [NCOUNT, n] or nullptr
+    unsigned long long *work_counter;  // dynamic scheduling (nullptr = static grid-stride)
+};
+
+struct Counters {
+    int nsteps, nlu, nsolve, nreject;
+};
+
+struct Tol {
+    double rtol;
+    double atol[NY];
+};
+
+// ----------------------------------------------------------------------------------------------
+// small helpers
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool finite_all(const double *v) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < NY; ++i) ok = ok && (fabs(v[i]) <= DBL_MAX);
+    return ok;
+}
+
+// x^(1/4), x^(-1/5), x^(-1/3) for step-size factors.  The factor only steers the step size, it
+// never enters the solution, so single precision SFU math (ex2/lg2) is ample.
+__device__ __forceinline__ double fast_pow(double x, float e) {
+    float xf = (float)fmin(fmax(x, 1e-30), 1e30);
+    return (double)exp2f(e * __log2f(xf));
+}
+
+__device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs &a, double x, const double *y,
+                                                   double *f) {
+    AnyODE::Status st = sys.rhs(x, y, f);
+#if ODESYS_HAS_BOUNDS
+    if (a.error_outside_bounds && sys.outside_bounds(y)) st = AnyODE::Status::recoverable_error;
+#endif
+#if ODESYS_NONNEGATIVE
+#pragma unroll
+    for (int i = 0; i < NY; ++i)
+        if (y[i] < 0) st = AnyODE::Status::recoverable_error;
+#endif
+    return st;
+}
+
+// In-register LU with partial (row) pivoting, row-major a[N*N]; the reciprocal pivots are kept
+// on the diagonal so the six triangular solves per Rosenbrock step are division free.
+// Same factorisation as AnyODE::getrf_callback (anyode_blasless.hpp:10-60): Doolittle, row
+// pivot = largest magnitude in the column (first one wins on ties).
+template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) {
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        int p = k;
+        double amax = fabs(a[k * N + k]);
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) {
+            const double v = fabs(a[i * N + k]);
+            if (v > amax) {
+                amax = v;
+                p = i;
+            }
+        }
+        piv[k] = p;
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) {
+            const bool sw = (p == i);
+#pragma unroll
+            for (int j = 0; j < N; ++j) {
+                const double u = a[k * N + j], w = a[i * N + j];
+                a[k * N + j] = sw ? w : u;
+                a[i * N + j] = sw ? u : w;
+            }
+        }
+        ok = ok && (amax > 0.0) && (amax <= DBL_MAX);
+        const double inv = 1.0 / a[k * N + k];
+        a[k * N + k] = inv;
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) {
+            const double l = a[i * N + k] * inv;
+            a[i * N + k] = l;
+#pragma unroll
+            for (int j = k + 1; j < N; ++j) a[i * N + j] = fma(-l, a[k * N + j], a[i * N + j]);
+        }
+    }
+    return ok;
+}
+
+// Solves L U x = P b in place (anyode_blasless.hpp:63-95).
+template <int N> __device__ __forceinline__ void lu_solve(const double *a, const int *piv, double *b) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) {
+            const bool sw = (piv[k] == i);
+            const double u = b[k], w = b[i];
+            b[k] = sw ? w : u;
+            b[i] = sw ? u : w;
+        }
+    }
+    // the multipliers were swapped together with their rows (LAPACK convention), hence all row
+    // interchanges are applied to b before the forward substitution starts
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) b[i] = fma(-a[i * N + k], b[k], b[i]);
+    }
+#pragma unroll
+    for (int i = N - 1; i >= 0; --i) {
+        double s = b[i];
+#pragma unroll
+        for (int j = i + 1; j < N; ++j) s = fma(-a[i * N + j], b[j], s);
+        b[i] = s * a[i * N + i];
+    }
+}
+
+// Hairer's starting step-size heuristic (dopri5.f / rodas.f ``HINIT``) with the max norm that the
+// controllers below use.  ``f0`` = f(t0, y0).  Costs one rhs evaluation.
+__device__ __forceinline__ double initial_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t0,
+                                               const double *y, const double *f0, double span, int order) {
+    double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+    for (int i = 0; i < NY; ++i) {
+        const double sk = tol.atol[i] + tol.rtol * fabs(y[i]);
+        d0 = fmax(d0, fabs(y[i]) / sk);
+        d1 = fmax(d1, fabs(f0[i]) / sk);
+    }
+    double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    h0 = fmin(h0, fabs(span));
+    const double dir = span >= 0 ? 1.0 : -1.0;
+    double y1[NY], f1[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) y1[i] = fma(dir * h0, f0[i], y[i]);
+    AnyODE::Status st = eval_rhs(sys, a, t0 + dir * h0, y1, f1);
+    double d2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < NY; ++i) {
+        const double sk = tol.atol[i] + tol.rtol * fabs(y[i]);
+        d2 = fmax(d2, fabs(f1[i] - f0[i]) / sk);
+    }
+    d2 /= h0;
+    if (st != AnyODE::Status::success || !(d2 <= DBL_MAX)) d2 = 0.0;
+    const double dmax = fmax(d1, d2);
+    const double h1 = (dmax <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : pow(0.01 / dmax, 1.0 / order);
+    return fmin(fmin(100.0 * h0, h1), fabs(span));
+}
+
+// ----------------------------------------------------------------------------------------------
+// Steppers.  Common protocol (all inlined into the persistent kernel):
+//   begin(...)      once per system (and after an autorestart)
+//   attempt(...)    one trial step t -> t+h producing ynew and the scaled error norm
+//   control(...)    accept/reject + next step size
+//   dense(...)      interpolate inside the last accepted step
+// ----------------------------------------------------------------------------------------------
+template <int METHOD> struct Stepper;
+
+// ---- classical RK4, fixed step -----------------------------------------------------------------
+template <> struct Stepper<M_RK4> {
+    static constexpr bool kAdaptive = false;
+    static constexpr int kOrder = 4;
+    __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) { return 0; }
+    __device__ __forceinline__ void auto_step(OdeSys &, const KernelArgs &, const Tol &, double, const double *,
+                                              double, double &) {}  // the nominal step never changes
+    // Same evaluation order as RK4_example_integrator.integrate_predefined (integrators.py:44-61).
+    __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &, double t, const double *y,
+                                           double h, double *ynew, double &err, Counters &) {
+        double k1[NY], k2[NY], k3[NY], k4[NY], tmp[NY];
+        int bad = 0;
+        bad |= eval_rhs(sys, a, t, y, k1);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h / 2 * k1[i];
+        bad |= eval_rhs(sys, a, t + h / 2, tmp, k2);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h / 2 * k2[i];
+        bad |= eval_rhs(sys, a, t + h / 2, tmp, k3);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h * k3[i];
+        bad |= eval_rhs(sys, a, t + h, tmp, k4);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) ynew[i] = y[i] + h / 6 * (k1[i] + 2 * k2[i] + 2 * k3[i] + k4[i]);
+        err = 0.0;
+        return bad;
+    }
+    __device__ __forceinline__ bool control(double, double, double &hnext, double h) {
+        hnext = h;
+        return true;
+    }
+    __device__ __forceinline__ void accepted(const double *) {}
+    __device__ __forceinline__ void dense(double theta, double, const double *yold, const double *ynew, double *out) {
+#pragma unroll
+        for (int i = 0; i < NY; ++i) out[i] = yold[i] + theta * (ynew[i] - yold[i]);  // only hit at theta == 1
+    }
+};
+
+// ---- Dormand-Prince 5(4) -----------------------------------------------------------------------
+template <> struct Stepper<M_DOPRI5> {
+    static constexpr bool kAdaptive = true;
+    static constexpr int kOrder = 5;
+    double k1[NY];                                   // f(t, y), FSAL
+    double k7[NY];                                   // f(t+h, ynew) of the last attempt
+    double r3[NY], r4[NY], r5[NY];                   // dense output polynomial of the last attempt
+
+    __device__ __forceinline__ int begin(OdeSys &sys, const KernelArgs &a, const Tol &, double t, const double *y) {
+        return eval_rhs(sys, a, t, y, k1);
+    }
+    __device__ __forceinline__ void auto_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t,
+                                              const double *y, double span, double &h) {
+        h = initial_step(sys, a, tol, t, y, k1, span, 5) * (span >= 0 ? 1.0 : -1.0);
+    }
+    __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
+                                           double h, double *ynew, double &err, Counters &) {
+        double k2[NY], k3[NY], k4[NY], k5[NY], k6[NY], tmp[NY];
+        int bad = 0;
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h * (0.2 * k1[i]);
+        bad |= eval_rhs(sys, a, t + 0.2 * h, tmp, k2);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h * (3.0 / 40.0 * k1[i] + 9.0 / 40.0 * k2[i]);
+        bad |= eval_rhs(sys, a, t + 0.3 * h, tmp, k3);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = y[i] + h * (44.0 / 45.0 * k1[i] - 56.0 / 15.0 * k2[i] + 32.0 / 9.0 * k3[i]);
+        bad |= eval_rhs(sys, a, t + 0.8 * h, tmp, k4);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = y[i] + h * (19372.0 / 6561.0 * k1[i] - 25360.0 / 2187.0 * k2[i] + 64448.0 / 6561.0 * k3[i] -
+                                 212.0 / 729.0 * k4[i]);
+        bad |= eval_rhs(sys, a, t + 8.0 / 9.0 * h, tmp, k5);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = y[i] + h * (9017.0 / 3168.0 * k1[i] - 355.0 / 33.0 * k2[i] + 46732.0 / 5247.0 * k3[i] +
+                                 49.0 / 176.0 * k4[i] - 5103.0 / 18656.0 * k5[i]);
+        bad |= eval_rhs(sys, a, t + h, tmp, k6);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            ynew[i] = y[i] + h * (35.0 / 384.0 * k1[i] + 500.0 / 1113.0 * k3[i] + 125.0 / 192.0 * k4[i] -
+                                  2187.0 / 6784.0 * k5[i] + 11.0 / 84.0 * k6[i]);
+        bad |= eval_rhs(sys, a, t + h, ynew, k7);
+        // error estimate and odeint's measure: |err_i| / (atol + rtol (|y_i| + |h| |y'_i|))
+        err = 0.0;
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            const double e = h * (71.0 / 57600.0 * k1[i] - 71.0 / 16695.0 * k3[i] + 71.0 / 1920.0 * k4[i] -
+                                  17253.0 / 339200.0 * k5[i] + 22.0 / 525.0 * k6[i] - 1.0 / 40.0 * k7[i]);
+            const double sc = tol.atol[i] + tol.rtol * (fabs(y[i]) + fabs(h) * fabs(k1[i]));
+            err = fmax(err, fabs(e) / sc);
+            // continuous extension (Hairer, Norsett, Wanner: Solving ODEs I, II.6; dopri5.f CONTD5)
+            const double ydiff = ynew[i] - y[i];
+            const double bspl = h * k1[i] - ydiff;
+            r3[i] = bspl;
+            r4[i] = ydiff - h * k7[i] - bspl;
+            r5[i] = h * (-12715105075.0 / 11282082432.0 * k1[i] + 87487479700.0 / 32700410799.0 * k3[i] -
+                         10690763975.0 / 1880347072.0 * k4[i] + 701980252875.0 / 199316789632.0 * k5[i] -
+                         1453857185.0 / 822651844.0 * k6[i] + 69997945.0 / 29380423.0 * k7[i]);
+        }
+        if (!(err <= DBL_MAX)) bad |= 1;
+        return bad;
+    }
+    // odeint default_step_adjuster: shrink by max(0.9 err^-1/3, 1/5); grow (only if err < 0.5) by
+    // 0.9 err^-1/5 capped at 5.
+    __device__ __forceinline__ bool control(double err, double, double &hnext, double h) {
+        if (err > 1.0) {
+            hnext = h * fmax(0.9 * fast_pow(err, -1.0f / 3.0f), 0.2);
+            return false;
+        }
+        hnext = h;
+        if (err < 0.5) {
+            const double e = fmax(3.2e-4 /* 5^-5 */, err);
+            hnext = h * fmin(0.9 * fast_pow(e, -0.2f), 5.0);
+        }
+        return true;
+    }
+    __device__ __forceinline__ void accepted(const double *) {
+#pragma unroll
+        for (int i = 0; i < NY; ++i) k1[i] = k7[i];
+    }
+    __device__ __forceinline__ void dense(double theta, double, const double *yold, const double *ynew, double *out) {
+        const double th1 = 1.0 - theta;
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            out[i] = yold[i] + theta * ((ynew[i] - yold[i]) + th1 * (r3[i] + theta * (r4[i] + th1 * r5[i])));
+    }
+};
+
+#if ODESYS_HAS_JAC
+// ---- Rosenbrock 4(3), six stages (RODAS-type; coefficients proven by oracle/check_ros4_coeffs.py) ---
+template <> struct Stepper<M_ROS4> {
+    static constexpr bool kAdaptive = true;
+    static constexpr int kOrder = 4;
+    double c3[NY], c4[NY];  // dense output: cont3, cont4 of the last attempt
+    double h_old, err_old;  // predictive (Gustafsson) controller memory
+    bool first, last_rejected;
+
+    __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) {
+        first = true;
+        last_rejected = false;
+        h_old = 0.0;
+        err_old = 1.0;
+        return 0;
+    }
+    __device__ __forceinline__ void auto_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t,
+                                              const double *y, double span, double &h) {
+        double f0[NY];
+        eval_rhs(sys, a, t, y, f0);
+        h = initial_step(sys, a, tol, t, y, f0, span, 4) * (span >= 0 ? 1.0 : -1.0);
+    }
+    __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
+                                           double h, double *ynew, double &err, Counters &cnt) {
+        constexpr double gam = 0.25;
+        constexpr double a21 = 0.1544000000000000e+01, a31 = 0.9466785280815826e+00, a32 = 0.2557011698983284e+00,
+                         a41 = 0.3314825187068521e+01, a42 = 0.2896124015972201e+01, a43 = 0.9986419139977817e+00,
+                         a51 = 0.1221224509226641e+01, a52 = 0.6019134481288629e+01, a53 = 0.1253708332932087e+02,
+                         a54 = -0.6878860361058950e+00;
+        constexpr double c21 = -0.5668800000000000e+01, c31 = -0.2430093356833875e+01, c32 = -0.2063599157091915e+00,
+                         c41 = -0.1073529058151375e+00, c42 = -0.9594562251023355e+01, c43 = -0.2047028614809616e+02,
+                         c51 = 0.7496443313967647e+01, c52 = -0.1024680431464352e+02, c53 = -0.3399990352819905e+02,
+                         c54 = 0.1170890893206160e+02, c61 = 0.8083246795921522e+01, c62 = -0.7981132988064893e+01,
+                         c63 = -0.3152159432874371e+02, c64 = 0.1631930543123136e+02, c65 = -0.6058818238834054e+01;
+        constexpr double d1 = 0.2500000000000000e+00, d2 = -0.1043000000000000e+00, d3 = 0.1035000000000000e+00,
+                         d4 = -0.3620000000000023e-01;
+        constexpr double c2x = 0.386, c3x = 0.21, c4x = 0.63;
+        constexpr double d21 = 0.1012623508344586e+02, d22 = -0.7487995877610167e+01, d23 = -0.3480091861555747e+02,
+                         d24 = -0.7992771707568823e+01, d25 = 0.1025137723295662e+01, d31 = -0.6762803392801253e+00,
+                         d32 = 0.6087714651680015e+01, d33 = 0.1643084320892478e+02, d34 = 0.2476722511418386e+02,
+                         d35 = -0.6594389125716872e+01;
+        double W[NY * NY], dfdt[NY], f[NY], g1[NY], g2[NY], g3[NY], g4[NY], g5[NY], tmp[NY];
+        int piv[NY];
+        int bad = 0;
+        bad |= eval_rhs(sys, a, t, y, f);
+        bad |= sys.dense_jac_rmaj(t, y, f, W, NY, dfdt);
+        // W = I/(gamma h) - J
+        const double ih = 1.0 / h;
+        const double diag = ih * (1.0 / gam);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+#pragma unroll
+            for (int j = 0; j < NY; ++j) W[i * NY + j] = (i == j ? diag : 0.0) - W[i * NY + j];
+        if (!lu_factor<NY>(W, piv)) bad |= 1;
+        cnt.nlu += 1;
+        cnt.nsolve += 6;
+#pragma unroll
+        for (int i = 0; i < NY; ++i) g1[i] = ODESYS_AUTONOMOUS ? f[i] : fma(h * d1, dfdt[i], f[i]);
+        lu_solve<NY>(W, piv, g1);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = fma(a21, g1[i], y[i]);
+        bad |= eval_rhs(sys, a, t + c2x * h, tmp, f);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            g2[i] = fma(c21 * ih, g1[i], f[i]);
+            if (!ODESYS_AUTONOMOUS) g2[i] = fma(h * d2, dfdt[i], g2[i]);
+        }
+        lu_solve<NY>(W, piv, g2);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a31 * g1[i] + a32 * g2[i];
+        bad |= eval_rhs(sys, a, t + c3x * h, tmp, f);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            g3[i] = f[i] + ih * (c31 * g1[i] + c32 * g2[i]);
+            if (!ODESYS_AUTONOMOUS) g3[i] = fma(h * d3, dfdt[i], g3[i]);
+        }
+        lu_solve<NY>(W, piv, g3);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a41 * g1[i] + a42 * g2[i] + a43 * g3[i];
+        bad |= eval_rhs(sys, a, t + c4x * h, tmp, f);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            g4[i] = f[i] + ih * (c41 * g1[i] + c42 * g2[i] + c43 * g3[i]);
+            if (!ODESYS_AUTONOMOUS) g4[i] = fma(h * d4, dfdt[i], g4[i]);
+        }
+        lu_solve<NY>(W, piv, g4);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a51 * g1[i] + a52 * g2[i] + a53 * g3[i] + a54 * g4[i];
+        bad |= eval_rhs(sys, a, t + h, tmp, f);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) g5[i] = f[i] + ih * (c51 * g1[i] + c52 * g2[i] + c53 * g3[i] + c54 * g4[i]);
+        lu_solve<NY>(W, piv, g5);
+#pragma unroll
+        for (int i = 0; i < NY; ++i) tmp[i] += g5[i];
+        bad |= eval_rhs(sys, a, t + h, tmp, f);
+        double xerr[NY];
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            xerr[i] = f[i] + ih * (c61 * g1[i] + c62 * g2[i] + c63 * g3[i] + c64 * g4[i] + c65 * g5[i]);
+        lu_solve<NY>(W, piv, xerr);
+        err = 0.0;
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            ynew[i] = tmp[i] + xerr[i];
+            const double sk = tol.atol[i] + tol.rtol * fmax(fabs(y[i]), fabs(ynew[i]));
+            err = fmax(err, fabs(xerr[i]) / sk);
+            c3[i] = d21 * g1[i] + d22 * g2[i] + d23 * g3[i] + d24 * g4[i] + d25 * g5[i];
+            c4[i] = d31 * g1[i] + d32 * g2[i] + d33 * g3[i] + d34 * g4[i] + d35 * g5[i];
+        }
+        if (!(err <= DBL_MAX)) bad |= 1;
+        return bad;
+    }
+    // odeint rosenbrock4_controller::try_step: fac in [1/6, 5], predictive correction after the
+    // first accepted step, no growth directly after a rejection.
+    __device__ __forceinline__ bool control(double err, double, double &hnext, double h) {
+        constexpr double safe = 0.9, fac1 = 5.0, fac2 = 1.0 / 6.0;
+        double fac = fmax(fac2, fmin(fac1, fast_pow(err, 0.25f) / safe));
+        double hn = h / fac;
+        if (err <= 1.0) {
+            if (!first) {
+                double fp = (h_old / h) * fast_pow(err * err / err_old, 0.25f) / safe;
+                fp = fmax(fac2, fmin(fac1, fp));
+                fac = fmax(fac, fp);
+                hn = h / fac;
+            }
+            first = false;
+            h_old = h;
+            err_old = fmax(0.01, err);
+            if (last_rejected) hn = (h >= 0.0) ? fmin(hn, h) : fmax(hn, h);
+            last_rejected = false;
+            hnext = hn;
+            return true;
+        }
+        last_rejected = true;
+        hnext = hn;
+        return false;
+    }
+    __device__ __forceinline__ void accepted(const double *) {}
+    __device__ __forceinline__ void dense(double theta, double, const double *yold, const double *ynew, double *out) {
+        const double s1 = 1.0 - theta;
+#pragma unroll
+        for (int i = 0; i < NY; ++i) out[i] = yold[i] * s1 + theta * (ynew[i] + s1 * (c3[i] + theta * c4[i]));
+    }
+};
+#endif  // ODESYS_HAS_JAC
+
+// ----------------------------------------------------------------------------------------------
+// The persistent kernel.  MODE 0: predefined output points, MODE 1: every accepted step.
+// ----------------------------------------------------------------------------------------------
+template <int METHOD, int MODE, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) integrate_kernel(const KernelArgs a) {
+    using St = Stepper<METHOD>;
+    const unsigned lane = threadIdx.x & 31u;
+    const int64_t nthreads = (int64_t)gridDim.x * BLOCK;
+    int64_t s = (int64_t)blockIdx.x * BLOCK + threadIdx.x - nthreads;  // static schedule cursor
+
+    OdeSys sys;
+    St st;
+    Tol tol;
+    tol.rtol = a.rtol;
+#pragma unroll
+    for (int i = 0; i < NY; ++i) tol.atol[i] = a.atol[i];
+
+    double y[NY], t = 0, h = 0, tend = 0, dir = 1, hmin = 0, hmax = INFINITY;
+    int64_t steps_left = 0;
+    int k_out = 0;        // MODE 0: next output index; MODE 1: rows written
+    int restarts = 0, nfail = 0;
+    Counters cnt = {0, 0, 0, 0};
+    bool active = false, exhausted = false;
+
+    for (;;) {
+        // ---- (A) fetch a new system for every idle lane ---------------------------------------
+        if (a.work_counter != nullptr) {
+            const unsigned need = __ballot_sync(FULL_MASK, !active && !exhausted);
+            if (need) {
+                const int leader = __ffs(need) - 1;
+                unsigned long long base = 0;
+                if ((int)lane == leader) base = atomicAdd(a.work_counter, (unsigned long long)__popc(need));
+                base = __shfl_sync(FULL_MASK, base, leader);
+                if (!active && !exhausted) s = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+            }
+        } else if (!active && !exhausted) {
+            s += nthreads;
+        }
+        if (!active && !exhausted) {
+            if (s >= a.n) {
+                exhausted = true;
+            } else {
+                // ---- load one system (row-major inputs; a warp reads one contiguous span) -------
+#pragma unroll
+                for (int i = 0; i < NY; ++i) y[i] = a.y0[s * NY + i];
+#pragma unroll
+                for (int i = 0; i < NP_USED; ++i) sys.m_p[i] = a.params[s * NP_TOT + i];
+                sys.setup();
+                cnt = {0, 0, 0, 0};
+                restarts = a.autorestart;
+                nfail = 0;
+                if (MODE == 0) {
+                    const double *xo = a.xout + s * a.xout_stride;
+                    t = xo[0];
+                    tend = xo[a.nt - 1];
+                    if (a.yout_soa) {
+#pragma unroll
+                        for (int i = 0; i < NY; ++i) a.yout[(int64_t)i * a.n + s] = y[i];
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < NY; ++i) a.yout[(s * a.nt) * NY + i] = y[i];
+                    }
+                    k_out = 1;
+                } else {
+                    t = a.x0[s];
+                    tend = a.xend[s];
+                    double *row = a.xyout + (s * a.max_rows) * (1 + NY);
+                    row[0] = t;
+#pragma unroll
+                    for (int i = 0; i < NY; ++i) row[1 + i] = y[i];
+                    k_out = 1;
+                }
+                dir = (tend >= t) ? 1.0 : -1.0;
+                hmin = a.dx_min ? a.dx_min[s] : 0.0;
+                hmax = a.dx_max ? a.dx_max[s] : INFINITY;
+                if (!(hmax > 0.0)) hmax = INFINITY;
+                steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
+                int bad = st.begin(sys, a, tol, t, y);
+                h = a.dx0 ? a.dx0[s] : 0.0;
+#if ODESYS_HAS_FIRST_STEP
+                if (h == 0.0) h = sys.get_dx0(t, y);
+#endif
+                if (h != 0.0) {
+                    h = fabs(h) * dir;
+                } else if (METHOD == M_RK4) {
+                    // no step given: one step per requested interval / 100 steps over the span
+                    h = (MODE == 0) ? dir * INFINITY : (tend - t) / 100.0;
+                } else {
+                    st.auto_step(sys, a, tol, t, y, tend - t, h);
+                }
+                active = true;
+                if (bad || !finite_all(y)) {
+                    nfail = 1 << 20;  // fail on the first pass through (D)
+                }
+                if (tend == t) {
+                    // zero-length span: every requested point equals the start
+                    if (MODE == 0) {
+                        for (; k_out < a.nt; ++k_out) {
+#pragma unroll
+                            for (int i = 0; i < NY; ++i) {
+                                if (a.yout_soa) a.yout[((int64_t)k_out * NY + i) * a.n + s] = y[i];
+                                else a.yout[(s * a.nt + k_out) * NY + i] = y[i];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (__all_sync(FULL_MASK, !active)) break;
+        if (!active) continue;
+
+        // ---- (B) termination / failure bookkeeping for this lane --------------------------------
+        int status = -1;  // -1: keep stepping
+        if (nfail >= (1 << 20)) status = ST_RHS;
+        else if (t == tend) status = ST_OK;
+        else if (steps_left <= 0) {
+            if (restarts > 0) {
+                // autorestart (_cvode_wrapper.pyx:90): new step budget, re-initialised stepper
+                restarts -= 1;
+                steps_left = a.mxsteps;
+                st.begin(sys, a, tol, t, y);
+                st.auto_step(sys, a, tol, t, y, tend - t, h);
+            } else {
+                status = ST_MXSTEPS;
+            }
+        }
+
+        if (status < 0) {
+            // ---- (C) one trial step --------------------------------------------------------------
+            double hh = h;
+            if (fabs(hh) > hmax) hh = dir * hmax;
+#if ODESYS_HAS_DX_MAX
+            if (a.get_dx_max_factor > 0.0) {
+                const double m = a.get_dx_max_factor * sys.get_dx_max(t, y);
+                if (fabs(hh) > m) hh = dir * m;
+            }
+#endif
+            if (St::kAdaptive && fabs(hh) < hmin) hh = dir * hmin;
+            // Mandatory landing point: the end of the span, or (fixed-step RK4 with requested output
+            // points, integrators.py:44-61) the next requested point.  Never step over it and snap onto
+            // it when the remainder is a rounding artefact.
+            double target = tend;
+            if (METHOD == M_RK4 && MODE == 0) target = (a.xout + s * a.xout_stride)[k_out];
+            const double rem = target - t;
+            const bool lands = fabs(hh) >= fabs(rem) * (1.0 - 1e-13);
+            double tnew = t + hh;
+            if (lands) {
+                hh = rem;
+                tnew = target;
+            }
+            const bool hits_end = lands && (target == tend);
+            double ynew[NY], err = 0.0, hnext = hh;
+            int bad = st.attempt(sys, a, tol, t, y, hh, ynew, err, cnt);
+            cnt.nsteps += 1;
+            steps_left -= 1;
+            bool ok;
+            if (bad || !finite_all(ynew)) {
+                // recoverable error (AnyODE::Status::recoverable_error) or NaN: retry with h/4
+                ok = false;
+                hnext = 0.25 * hh;
+                nfail += 1;
+                if (nfail >= 12 || !St::kAdaptive) nfail = 1 << 20;
+                double ignored;
+                st.control(2.0, 0.0, ignored, hh);  // let the controller know a rejection happened
+            } else {
+                ok = st.control(err, 0.0, hnext, hh);
+                if (ok) nfail = 0;
+            }
+            if (!ok) {
+                cnt.nreject += 1;
+                if (St::kAdaptive && (fabs(hnext) <= 16.0 * DBL_EPSILON * fabs(t) || fabs(hnext) == 0.0 ||
+                                      (hmin > 0.0 && fabs(hh) <= hmin)))
+                    status = ST_STEP_TOO_SMALL;
+                h = hnext;
+            } else {
+                // ---- (D) accepted: emit outputs ---------------------------------------------------
+                if (MODE == 0) {
+                    const double *xo = a.xout + s * a.xout_stride;
+                    while (k_out < a.nt) {
+                        const double xk = xo[k_out];
+                        if ((xk - tnew) * dir > 0.0) break;
+                        double yo[NY];
+                        if (xk == tnew) {
+#pragma unroll
+                            for (int i = 0; i < NY; ++i) yo[i] = ynew[i];
+                        } else {
+                            st.dense((xk - t) / hh, hh, y, ynew, yo);
+                        }
+                        if (a.yout_soa) {
+#pragma unroll
+                            for (int i = 0; i < NY; ++i) a.yout[((int64_t)k_out * NY + i) * a.n + s] = yo[i];
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < NY; ++i) a.yout[(s * a.nt + k_out) * NY + i] = yo[i];
+                        }
+                        k_out += 1;
+                        steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;  // budget is per output interval
+                    }
+                } else {
+                    if (k_out >= a.max_rows) {
+                        status = ST_ROWS;
+                    } else {
+                        double *row = a.xyout + (s * a.max_rows + k_out) * (1 + NY);
+                        row[0] = tnew;
+#pragma unroll
+                        for (int i = 0; i < NY; ++i) row[1 + i] = ynew[i];
+                        k_out += 1;
+                    }
+                }
+                st.accepted(ynew);
+#pragma unroll
+                for (int i = 0; i < NY; ++i) y[i] = ynew[i];
+                t = tnew;
+                if (hits_end) t = tend;
+                if (St::kAdaptive) h = hnext;  // a fixed-step method keeps its nominal step
+            }
+        }
+
+        if (status >= 0) {
+            // ---- (E) retire the system --------------------------------------------------------------
+            a.status[s] = status;
+            if (MODE == 0) {
+                a.nreached[s] = k_out;
+                if (status != ST_OK) {
+                    const double qnan = nan("");
+                    for (int k = k_out; k < a.nt; ++k)
+#pragma unroll
+                        for (int i = 0; i < NY; ++i) {
+                            if (a.yout_soa) a.yout[((int64_t)k * NY + i) * a.n + s] = qnan;
+                            else a.yout[(s * a.nt + k) * NY + i] = qnan;
+                        }
+                }
+            } else {
+                a.nrows[s] = k_out;
+            }
+            if (a.counters) {
+                a.counters[C_NSTEPS * a.n + s] = cnt.nsteps;
+                a.counters[C_NFEV * a.n + s] = sys.nfev;
+                a.counters[C_NJEV * a.n + s] = sys.njev;
+                a.counters[C_NLU * a.n + s] = cnt.nlu;
+                a.counters[C_NSOLVE * a.n + s] = cnt.nsolve;
+                a.counters[C_NREJECT * a.n + s] = cnt.nreject;
+            }
+            active = false;
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Test kernels: evaluate the generated functions / the register LU for a batch (parity tests).
+// ----------------------------------------------------------------------------------------------
+__global__ void eval_kernel(int64_t n, const double *x, const double *y, const double *params, double *f,
+                            double *jac, double *dfdt) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    OdeSys sys;
+    double yy[NY], ff[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) yy[i] = y[s * NY + i];
+#pragma unroll
+    for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+    sys.setup();
+    sys.rhs(x[s], yy, ff);
+#pragma unroll
+    for (int i = 0; i < NY; ++i) f[s * NY + i] = ff[i];
+#if ODESYS_HAS_JAC
+    if (jac) {
+        double J[NY * NY], dd[NY];
+        sys.dense_jac_rmaj(x[s], yy, ff, J, NY, dd);
+#pragma unroll
+        for (int i = 0; i < NY * NY; ++i) jac[s * NY * NY + i] = J[i];
+        if (dfdt) {
+#pragma unroll
+            for (int i = 0; i < NY; ++i) dfdt[s * NY + i] = dd[i];
+        }
+    }
+#endif
+}
+
+__global__ void lu_kernel(int64_t n, const double *A, const double *b, double *xsol, int32_t *ok) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    double a[NY * NY], v[NY];
+    int piv[NY];
+#pragma unroll
+    for (int i = 0; i < NY * NY; ++i) a[i] = A[s * NY * NY + i];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) v[i] = b[s * NY + i];
+    const bool good = lu_factor<NY>(a, piv);
+    lu_solve<NY>(a, piv, v);
+#pragma unroll
+    for (int i = 0; i < NY; ++i) xsol[s * NY + i] = v[i];
+    ok[s] = good ? 1 : 0;
+}
+
+}  // namespace pyodesys_cuda

@@ -1,0 +1,432 @@
+// C-ABI shim of one generated ODE system (see include/pyodesys_cuda.h for the contract).
+//
+// Plays the role of the Cython batch wrappers of the reference
+// (pyodesys/native/sources/_odeint_wrapper.pyx:37-177, _cvode_wrapper.pyx:78-365): validate,
+// stage the row-major arrays, run the batch, hand back per-system status/counters.  Where the
+// wrappers ``new`` one OdeSys per row under the GIL (_odeint_wrapper.pyx:158-160) and fan out
+// with OpenMP, this shim copies the arrays to HBM once and launches one persistent kernel.
+// Compiled once per system:  nvcc -gencode arch=compute_100a,code=sm_100a -shared ...
+#include "odesys_generated.h"
+
+#include "integrators.cuh"
+#include "pyodesys_cuda.h"
+
+#include <atomic>
+#include <chrono>
+#include <mutex>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+using namespace pyodesys_cuda;
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+int fail(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return -1;
+}
+
+#define CU_CHECK(expr)                                                                        \
+    do {                                                                                      \
+        cudaError_t e_ = (expr);                                                              \
+        if (e_ != cudaSuccess) return fail("%s failed: %s", #expr, cudaGetErrorString(e_)); \
+    } while (0)
+
+constexpr int kMaxDev = 64;
+constexpr int kBlock = 128;
+
+enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, NBUF };
+
+struct DevCtx {
+    std::mutex mtx;
+    bool ready = false;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4];
+    void *buf[NBUF] = {};
+    size_t cap[NBUF] = {};
+    int sm_count = 0;
+};
+DevCtx g_ctx[kMaxDev];
+
+int ctx_init(DevCtx &c, int device) {
+    CU_CHECK(cudaSetDevice(device));
+    if (c.ready) return 0;
+    cudaDeviceProp prop;
+    CU_CHECK(cudaGetDeviceProperties(&prop, device));
+    c.sm_count = prop.multiProcessorCount;
+    CU_CHECK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    for (auto &e : c.ev) CU_CHECK(cudaEventCreate(&e));
+    c.ready = true;
+    return 0;
+}
+
+int ensure(DevCtx &c, Buf b, size_t bytes) {
+    if (bytes == 0) bytes = 8;
+    if (c.cap[b] >= bytes) return 0;
+    if (c.buf[b]) CU_CHECK(cudaFree(c.buf[b]));
+    c.buf[b] = nullptr;
+    c.cap[b] = 0;
+    CU_CHECK(cudaMalloc(&c.buf[b], bytes));
+    c.cap[b] = bytes;
+    return 0;
+}
+
+template <int METHOD, int MODE> int launch(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
+    auto kern = integrate_kernel<METHOD, MODE, kBlock>;
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kBlock, 0));
+    if (occ < 1) occ = 1;
+    if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
+    // persistent grid: a multiple of the SM count, never more blocks than there is work
+    int64_t grid = (int64_t)c.sm_count * occ;
+    const int64_t need = (a.n + kBlock - 1) / kBlock;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kBlock, 0, stream>>>(a);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+
+template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cudaStream_t stream, int bps) {
+    switch (method) {
+    case PYODESYS_CUDA_RK4: return launch<M_RK4, MODE>(c, a, stream, bps);
+    case PYODESYS_CUDA_DOPRI5: return launch<M_DOPRI5, MODE>(c, a, stream, bps);
+#if ODESYS_HAS_JAC
+    case PYODESYS_CUDA_ROSENBROCK4: return launch<M_ROS4, MODE>(c, a, stream, bps);
+#else
+    case PYODESYS_CUDA_ROSENBROCK4: return fail("rosenbrock4 needs a Jacobian but the system was generated with jac=False");
+#endif
+    default: return fail("unknown method id %d", method);
+    }
+}
+
+struct Common {
+    int device;
+    int64_t n;
+    const double *y0, *params, *atol;
+    int natol;
+    double rtol;
+    const double *dx0, *dx_min, *dx_max;
+    int64_t mxsteps;
+    int method, autorestart;
+    int32_t *status, *counters;
+    double *timings;
+    int ptr_kind;
+    const pyodesys_cuda_options *opt;
+};
+
+int check_common(const Common &q) {
+    if (q.device < 0 || q.device >= kMaxDev) return fail("invalid device %d", q.device);
+    if (q.n < 0) return fail("negative batch size");
+    if (q.natol != 1 && q.natol != NY) return fail("atol needs to be of length 1 or %d", NY);
+    if (!q.atol) return fail("atol is NULL");
+    if (!q.y0 && q.n > 0) return fail("y0 is NULL");
+    if (!q.params && NP_TOT > 0 && q.n > 0) return fail("params is NULL but the system has %d parameters", NP_TOT);
+    if (!q.status && q.n > 0) return fail("status is NULL");
+    if (q.ptr_kind != 0 && q.ptr_kind != 1) return fail("ptr_kind must be 0 (host) or 1 (device)");
+    if (!(q.rtol >= 0.0)) return fail("rtol must be non-negative");
+    return 0;
+}
+
+void fill_args(KernelArgs &a, const Common &q) {
+    memset(&a, 0, sizeof(a));
+    a.n = q.n;
+    for (int i = 0; i < NY; ++i) a.atol[i] = q.atol[q.natol == 1 ? 0 : i];
+    a.rtol = q.rtol;
+    a.mxsteps = q.mxsteps;
+    a.autorestart = q.autorestart;
+    a.get_dx_max_factor = q.opt ? q.opt->get_dx_max_factor : 0.0;
+    a.error_outside_bounds = q.opt ? q.opt->error_outside_bounds : 0;
+}
+
+bool want_dynamic(const Common &q) {
+    const int sched = q.opt ? q.opt->schedule : 0;
+    if (sched == 1) return false;
+    if (sched == 2) return true;
+    return q.method != PYODESYS_CUDA_RK4;  // adaptive steppers have data dependent step counts
+}
+
+double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// Stage an optional host array; returns the device pointer (nullptr when src is nullptr).
+int stage(DevCtx &c, Buf b, const void *src, size_t bytes, const void **dst) {
+    *dst = nullptr;
+    if (!src) return 0;
+    if (ensure(c, b, bytes)) return -1;
+    CU_CHECK(cudaMemcpyAsync(c.buf[b], src, bytes, cudaMemcpyHostToDevice, c.stream));
+    *dst = c.buf[b];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pyodesys_cuda_info(int *ny, int *np_tot, int *npcse, int *flops_rhs, int *flops_jac) {
+    if (ny) *ny = NY;
+    if (np_tot) *np_tot = NP_TOT;
+    if (npcse) *npcse = ODESYS_NPCSE;
+    if (flops_rhs) *flops_rhs = ODESYS_FLOPS_RHS;
+    if (flops_jac) *flops_jac = ODESYS_FLOPS_JAC;
+    return 0;
+}
+
+int64_t pyodesys_cuda_query(const char *key) {
+    if (!key) return -1;
+    struct KV { const char *k; int64_t v; };
+    const KV kv[] = {
+        {"abi_version", PYODESYS_CUDA_ABI_VERSION}, {"ny", NY}, {"nparams", ODESYS_NPARAMS}, {"np_tot", NP_TOT},
+        {"np_used", NP_USED}, {"npcse", ODESYS_NPCSE}, {"has_jac", ODESYS_HAS_JAC}, {"autonomous", ODESYS_AUTONOMOUS},
+        {"nroots", ODESYS_NROOTS}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
+        {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
+        {"ncounters", NCOUNT}, {"has_first_step", ODESYS_HAS_FIRST_STEP}, {"has_dx_max", ODESYS_HAS_DX_MAX},
+    };
+    for (const auto &e : kv)
+        if (strcmp(e.k, key) == 0) return e.v;
+    // registers per thread of a kernel variant: "regs:<method>:<mode>" (needs a CUDA device)
+    int m = -1, mode = -1;
+    if (sscanf(key, "regs:%d:%d", &m, &mode) == 2) {
+        cudaFuncAttributes fa;
+        cudaError_t e = cudaErrorInvalidValue;
+        if (m == PYODESYS_CUDA_RK4) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_RK4, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_RK4, 0, kBlock>);
+        if (m == PYODESYS_CUDA_DOPRI5) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 0, kBlock>);
+#if ODESYS_HAS_JAC
+        if (m == PYODESYS_CUDA_ROSENBROCK4) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 0, kBlock>);
+#endif
+        if (e != cudaSuccess) { cudaGetLastError(); return -1; }
+        return fa.numRegs;
+    }
+    return -1;
+}
+
+int64_t pyodesys_cuda_launch_count(void) { return g_launches.load(); }
+
+const char *pyodesys_cuda_last_error(void) { return g_err; }
+
+int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const double *y0, const double *xout,
+                                       const double *params, const double *atol, int natol, double rtol,
+                                       const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
+                                       int method, int autorestart, int return_on_error, double *yout,
+                                       int32_t *nreached, int32_t *status, int32_t *counters, double *timings,
+                                       int ptr_kind, const pyodesys_cuda_options *opt) {
+    (void)return_on_error;  // per-system failures are always reported through status/nreached
+    const double t_begin = now_s();
+    Common q{device, n, y0, params, atol, natol, rtol, dx0, dx_min, dx_max, mxsteps, method, autorestart,
+             status, counters, timings, ptr_kind, opt};
+    if (check_common(q)) return -1;
+    if (nt < 1) return fail("need at least one output point (nt=%d)", nt);
+    if ((!xout || !yout || !nreached) && n > 0) return fail("xout/yout/nreached must not be NULL");
+    if (timings) for (int i = 0; i < PYODESYS_CUDA_NTIMINGS; ++i) timings[i] = 0.0;
+    if (n == 0) return 0;
+    DevCtx &c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mtx);
+    if (ctx_init(c, device)) return -1;
+
+    const bool shared_x = opt && opt->xout_shared;
+    KernelArgs a;
+    fill_args(a, q);
+    a.nt = nt;
+    a.xout_stride = shared_x ? 0 : nt;
+    a.yout_soa = (opt && ptr_kind == 1) ? opt->yout_soa : 0;
+    cudaStream_t stream = c.stream;
+    if (want_dynamic(q)) {
+        if (ensure(c, B_WORK, sizeof(unsigned long long))) return -1;
+        a.work_counter = (unsigned long long *)c.buf[B_WORK];
+    }
+    const int bps = opt ? opt->blocks_per_sm : 0;
+
+    if (ptr_kind == 1) {
+        if (opt && opt->stream) stream = (cudaStream_t)opt->stream;
+        a.y0 = y0; a.params = params; a.xout = xout; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
+        a.yout = yout; a.nreached = nreached; a.status = status; a.counters = counters;
+        if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
+        CU_CHECK(cudaEventRecord(c.ev[0], stream));
+        if (dispatch<0>(c, a, method, stream, bps)) return -1;
+        CU_CHECK(cudaEventRecord(c.ev[1], stream));
+        CU_CHECK(cudaStreamSynchronize(stream));
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1]));
+        if (timings) { timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3; timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin; }
+        return 0;
+    }
+
+    // ---- host pointers: H2D, kernel, D2H ---------------------------------------------------------
+    const size_t nn = (size_t)n;
+    const void *p;
+    CU_CHECK(cudaEventRecord(c.ev[0], stream));
+    if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
+    if (stage(c, B_PARAMS, NP_TOT ? params : nullptr, nn * NP_TOT * 8, &p)) return -1; a.params = (const double *)p;
+    if (stage(c, B_XOUT, xout, (shared_x ? 1 : nn) * nt * 8, &p)) return -1; a.xout = (const double *)p;
+    if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;
+    if (stage(c, B_DXMIN, dx_min, nn * 8, &p)) return -1; a.dx_min = (const double *)p;
+    if (stage(c, B_DXMAX, dx_max, nn * 8, &p)) return -1; a.dx_max = (const double *)p;
+    if (ensure(c, B_YOUT, nn * nt * NY * 8) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4)) return -1;
+    a.yout = (double *)c.buf[B_YOUT];
+    a.nreached = (int32_t *)c.buf[B_NREACHED];
+    a.status = (int32_t *)c.buf[B_STATUS];
+    if (counters) {
+        if (ensure(c, B_COUNTERS, nn * NCOUNT * 4)) return -1;
+        a.counters = (int32_t *)c.buf[B_COUNTERS];
+    }
+    if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
+    CU_CHECK(cudaEventRecord(c.ev[1], stream));
+    if (dispatch<0>(c, a, method, stream, bps)) return -1;
+    CU_CHECK(cudaEventRecord(c.ev[2], stream));
+    CU_CHECK(cudaMemcpyAsync(yout, a.yout, nn * nt * NY * 8, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaMemcpyAsync(nreached, a.nreached, nn * 4, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaMemcpyAsync(status, a.status, nn * 4, cudaMemcpyDeviceToHost, stream));
+    if (counters) CU_CHECK(cudaMemcpyAsync(counters, a.counters, nn * NCOUNT * 4, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaEventRecord(c.ev[3], stream));
+    CU_CHECK(cudaStreamSynchronize(stream));
+    if (timings) {
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1])); timings[PYODESYS_CUDA_T_H2D] = ms * 1e-3;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[1], c.ev[2])); timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[2], c.ev[3])); timings[PYODESYS_CUDA_T_D2H] = ms * 1e-3;
+        timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin;
+    }
+    return 0;
+}
+
+int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, const double *x0, const double *xend,
+                                     const double *params, const double *atol, int natol, double rtol,
+                                     const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
+                                     int method, int autorestart, int return_on_error, int64_t max_rows,
+                                     double *xyout, int32_t *nrows, int32_t *status, int32_t *counters,
+                                     double *timings, int ptr_kind, const pyodesys_cuda_options *opt) {
+    (void)return_on_error;
+    const double t_begin = now_s();
+    Common q{device, n, y0, params, atol, natol, rtol, dx0, dx_min, dx_max, mxsteps, method, autorestart,
+             status, counters, timings, ptr_kind, opt};
+    if (check_common(q)) return -1;
+    if (max_rows < 2) return fail("max_rows_per_system must be at least 2");
+    if ((!x0 || !xend || !xyout || !nrows) && n > 0) return fail("x0/xend/xyout/nrows must not be NULL");
+    if (timings) for (int i = 0; i < PYODESYS_CUDA_NTIMINGS; ++i) timings[i] = 0.0;
+    if (n == 0) return 0;
+    DevCtx &c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mtx);
+    if (ctx_init(c, device)) return -1;
+
+    KernelArgs a;
+    fill_args(a, q);
+    a.max_rows = max_rows;
+    cudaStream_t stream = c.stream;
+    if (want_dynamic(q)) {
+        if (ensure(c, B_WORK, sizeof(unsigned long long))) return -1;
+        a.work_counter = (unsigned long long *)c.buf[B_WORK];
+    }
+    const int bps = opt ? opt->blocks_per_sm : 0;
+    const size_t nn = (size_t)n;
+    const size_t out_bytes = nn * (size_t)max_rows * (1 + NY) * 8;
+
+    if (ptr_kind == 1) {
+        if (opt && opt->stream) stream = (cudaStream_t)opt->stream;
+        a.y0 = y0; a.params = params; a.x0 = x0; a.xend = xend; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
+        a.xyout = xyout; a.nrows = nrows; a.status = status; a.counters = counters;
+        if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
+        CU_CHECK(cudaEventRecord(c.ev[0], stream));
+        if (dispatch<1>(c, a, method, stream, bps)) return -1;
+        CU_CHECK(cudaEventRecord(c.ev[1], stream));
+        CU_CHECK(cudaStreamSynchronize(stream));
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1]));
+        if (timings) { timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3; timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin; }
+        return 0;
+    }
+
+    const void *p;
+    CU_CHECK(cudaEventRecord(c.ev[0], stream));
+    if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
+    if (stage(c, B_PARAMS, NP_TOT ? params : nullptr, nn * NP_TOT * 8, &p)) return -1; a.params = (const double *)p;
+    if (stage(c, B_XOUT, x0, nn * 8, &p)) return -1; a.x0 = (const double *)p;
+    if (stage(c, B_XEND, xend, nn * 8, &p)) return -1; a.xend = (const double *)p;
+    if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;
+    if (stage(c, B_DXMIN, dx_min, nn * 8, &p)) return -1; a.dx_min = (const double *)p;
+    if (stage(c, B_DXMAX, dx_max, nn * 8, &p)) return -1; a.dx_max = (const double *)p;
+    if (ensure(c, B_YOUT, out_bytes) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4)) return -1;
+    a.xyout = (double *)c.buf[B_YOUT];
+    a.nrows = (int32_t *)c.buf[B_NREACHED];
+    a.status = (int32_t *)c.buf[B_STATUS];
+    if (counters) {
+        if (ensure(c, B_COUNTERS, nn * NCOUNT * 4)) return -1;
+        a.counters = (int32_t *)c.buf[B_COUNTERS];
+    }
+    if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
+    CU_CHECK(cudaEventRecord(c.ev[1], stream));
+    if (dispatch<1>(c, a, method, stream, bps)) return -1;
+    CU_CHECK(cudaEventRecord(c.ev[2], stream));
+    CU_CHECK(cudaMemcpyAsync(xyout, a.xyout, out_bytes, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaMemcpyAsync(nrows, a.nrows, nn * 4, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaMemcpyAsync(status, a.status, nn * 4, cudaMemcpyDeviceToHost, stream));
+    if (counters) CU_CHECK(cudaMemcpyAsync(counters, a.counters, nn * NCOUNT * 4, cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaEventRecord(c.ev[3], stream));
+    CU_CHECK(cudaStreamSynchronize(stream));
+    if (timings) {
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1])); timings[PYODESYS_CUDA_T_H2D] = ms * 1e-3;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[1], c.ev[2])); timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3;
+        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[2], c.ev[3])); timings[PYODESYS_CUDA_T_D2H] = ms * 1e-3;
+        timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin;
+    }
+    return 0;
+}
+
+int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params, double *f,
+                       double *jac, double *dfdt) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+    if (n <= 0) return 0;
+    CU_CHECK(cudaSetDevice(device));
+    const size_t nn = (size_t)n;
+    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *df = nullptr, *dj = nullptr, *dd = nullptr;
+    CU_CHECK(cudaMalloc(&dx, nn * 8));
+    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
+    CU_CHECK(cudaMalloc(&df, nn * NY * 8));
+    CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
+    CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
+    if (NP_TOT) CU_CHECK(cudaMemcpy(dp, params, nn * NP_TOT * 8, cudaMemcpyHostToDevice));
+    if (jac) CU_CHECK(cudaMalloc(&dj, nn * NY * NY * 8));
+    if (jac && dfdt) CU_CHECK(cudaMalloc(&dd, nn * NY * 8));
+    eval_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dx, dy, dp, df, dj, dd);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    CU_CHECK(cudaMemcpy(f, df, nn * NY * 8, cudaMemcpyDeviceToHost));
+    if (dj) CU_CHECK(cudaMemcpy(jac, dj, nn * NY * NY * 8, cudaMemcpyDeviceToHost));
+    if (dd) CU_CHECK(cudaMemcpy(dfdt, dd, nn * NY * 8, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(df); cudaFree(dj); cudaFree(dd);
+    return 0;
+}
+
+int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+    if (n <= 0) return 0;
+    CU_CHECK(cudaSetDevice(device));
+    const size_t nn = (size_t)n;
+    double *dA = nullptr, *db = nullptr, *dx = nullptr;
+    int32_t *dok = nullptr;
+    CU_CHECK(cudaMalloc(&dA, nn * NY * NY * 8));
+    CU_CHECK(cudaMalloc(&db, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dx, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dok, nn * 4));
+    CU_CHECK(cudaMemcpy(dA, A, nn * NY * NY * 8, cudaMemcpyHostToDevice));
+    CU_CHECK(cudaMemcpy(db, b, nn * NY * 8, cudaMemcpyHostToDevice));
+    lu_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dA, db, dx, dok);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    CU_CHECK(cudaMemcpy(x, dx, nn * NY * 8, cudaMemcpyDeviceToHost));
+    CU_CHECK(cudaMemcpy(ok, dok, nn * 4, cudaMemcpyDeviceToHost));
+    cudaFree(dA); cudaFree(db); cudaFree(dx); cudaFree(dok);
+    return 0;
+}
+
+}  // extern "C"

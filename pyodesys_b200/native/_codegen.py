@@ -1,0 +1,343 @@
+# -*- coding: utf-8 -*-
+"""
+Code generation: SymPy expressions -> one self-contained C++/CUDA header.
+
+This is the CUDA counterpart of ``_NativeCodeBase.variables`` (``pyodesys/native/_base.py:126-281``)
+plus the mako template it feeds (``pyodesys/native/sources/odesys_anyode_template.cpp``):
+
+* symbols are replaced by C identifiers ``y[i]``, ``x``, ``m_p[i]`` (``_base.py:157-164``);
+* CSE level 1 ("common"): sub-expressions that only involve parameters are hoisted into
+  ``m_p_cse[k]`` and evaluated once per system (``_base.py:181-195``, ``template:104-110``);
+* CSE level 2 per function group: rhs, jac(+dfdt), first_step, roots
+  (``_base.py:197-226``);
+* ``namespace_override`` lets the user replace a generated body with raw source
+  (``_base.py:275-279``) - the same member names (``m_p``, ``this->nfev``,
+  ``AnyODE::Status::recoverable_error``) are valid inside the generated ``struct OdeSys`` so
+  the reference's snippets compile unchanged.
+
+The emitted text is plain C++ guarded by ``ODESYS_FN`` (``__host__ __device__ __forceinline__``
+under nvcc, ``inline`` under g++) so that the very same functions are used by the sm_100a
+kernels and by the CPU oracle (``oracle/``).  Operation counts of the CSE'd forms are
+emitted as ``ODESYS_FLOPS_*`` and feed the FP64 roofline.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+
+import sympy
+from sympy.printing.c import C99CodePrinter
+
+
+class _Printer(C99CodePrinter):
+    """ C printer that never emits ``pow`` for small integer exponents. """
+
+    def _print_Pow(self, expr):
+        base, exp = expr.base, expr.exp
+        if exp.is_Integer and 1 < abs(int(exp)) <= 16:
+            b = self._print(base)
+            n = abs(int(exp))
+            if n == 2:
+                s = '((%s)*(%s))' % (b, b)
+            else:
+                s = 'odesys_ipow<%d>(%s)' % (n, b)
+            return s if int(exp) > 0 else '(1.0/%s)' % s
+        if exp == -1:
+            return '(1.0/(%s))' % self._print(base)
+        return super()._print_Pow(expr)
+
+    def _print_Symbol(self, expr):
+        return expr.name  # names such as ``y[0]``/``m_p[2]`` must survive verbatim
+
+    def _print_Float(self, expr):
+        return repr(float(expr))
+
+    def _print_Integer(self, expr):
+        return '%d.0' % int(expr) if abs(int(expr)) < 2**53 else repr(float(int(expr)))
+
+    def _print_Rational(self, expr):
+        return '(%d.0/%d.0)' % (expr.p, expr.q)
+
+
+_printer = _Printer({'contract': False})
+
+
+def _ccode(expr):
+    return _printer.doprint(sympy.sympify(expr))
+
+
+def _count(exprs_and_cses):
+    tot = 0
+    for e in exprs_and_cses:
+        tot += int(sympy.count_ops(e, visual=False))
+    return tot
+
+
+class GeneratedCode:
+    """ Result of :func:`generate`: header text + the compile-time facts about the system. """
+
+    def __init__(self, text, ny, nparams, np_tot, np_used, npcse, flops, has_jac, autonomous,
+                 has_first_step, has_dx_max, nroots, jac_nnz):
+        self.text = text
+        self.ny = ny
+        self.nparams = nparams
+        self.np_tot = np_tot
+        self.np_used = np_used
+        self.npcse = npcse
+        self.flops = flops
+        self.has_jac = has_jac
+        self.autonomous = autonomous
+        self.has_first_step = has_first_step
+        self.has_dx_max = has_dx_max
+        self.nroots = nroots
+        self.jac_nnz = jac_nnz
+
+    @property
+    def digest(self):
+        return hashlib.sha256(self.text.encode('utf-8')).hexdigest()[:20]
+
+
+def _body(cses, assigns, ret='return AnyODE::Status::success;', indent='        '):
+    lines = []
+    for tok, expr in cses:
+        lines.append('%sconst double %s = %s;' % (indent, tok, expr))
+    for lhs, expr in assigns:
+        lines.append('%s%s = %s;' % (indent, lhs, expr))
+    if ret:
+        lines.append(indent + ret)
+    return '\n'.join(lines)
+
+
+def generate(odesys, namespace_override=None, namespace_extend=None):
+    """ Build the header for ``odesys`` (a :class:`pyodesys_b200.symbolic.SymbolicSys`). """
+    ns_over = dict(namespace_override or {})
+    ns_ext = dict(namespace_extend or {})
+    be = odesys.be
+    ny = odesys.ny
+    if odesys.band is not None:
+        raise NotImplementedError("Banded jacobian not yet implemented.")  # _base.py:128-129
+    nparams = len(odesys.params)
+    np_tot = nparams + (ny if odesys.append_iv else 0)
+
+    jac = odesys.get_jac()
+    all_exprs = list(odesys.exprs)
+    if jac is not False:
+        dfdx = odesys.get_dfdx()
+        jac_flat = [jac[i, j] for i in range(ny) for j in range(ny)]
+        dfdx_flat = [dfdx[i] for i in range(ny)] if dfdx is not False else [sympy.S.Zero]*ny
+        all_exprs += jac_flat + dfdx_flat
+        nj = len(jac_flat) + len(dfdx_flat)
+    else:
+        nj = 0
+    first_step = odesys.first_step_expr
+    nfs = 0
+    if first_step is not None and 'p_first_step' not in ns_over:
+        all_exprs.append(be.sympify(first_step))
+        nfs = 1
+    roots = odesys.roots
+    nroots = 0 if roots is None else len(roots)
+    if nroots:
+        all_exprs += [be.sympify(r) for r in roots]
+
+    xsym = be.Symbol('x')
+    subsd = {k: be.Symbol('y[%d]' % i) for i, k in enumerate(odesys.dep)}
+    if odesys.indep is not None:
+        subsd[odesys.indep] = xsym
+    subsd.update({k: be.Symbol('m_p[%d]' % i) for i, k in enumerate(odesys.params)})
+    if odesys.append_iv and odesys.init_dep is not None:
+        subsd.update({k: be.Symbol('m_p[%d]' % (nparams + i)) for i, k in enumerate(odesys.init_dep)})
+
+    use_cse = os.getenv('PYODESYS_NATIVE_CSE', '1') == '1'  # _base.py:175-179
+
+    def cse_cb(exprs, symbols, ignore=()):
+        if not use_cse or len(exprs) == 0:
+            return [], list(exprs)
+        return be.cse(exprs, symbols=symbols, ignore=ignore)
+
+    # ---- level 1: parameter-only sub-expressions -> m_p_cse[] -------------------------------
+    ignore = tuple(odesys.dep) + ((odesys.indep,) if odesys.indep is not None else ())
+    common_cses, common_exprs = cse_cb(all_exprs, be.numbered_symbols('cse_temporary'), ignore)
+    common_subs, k = {}, 0
+    for symb, _sub in common_cses:
+        if any(symb in e.free_symbols for e in common_exprs):
+            common_subs[symb] = be.Symbol('m_p_cse[%d]' % k)
+            k += 1
+    npcse = k
+    common_cses = [(s.xreplace(common_subs), e.xreplace(common_subs)) for s, e in common_cses]
+    common_exprs = [e.xreplace(common_subs) for e in common_exprs]
+
+    def cc(e):
+        return _ccode(sympy.sympify(e).xreplace(subsd))
+
+    rhs_cses, rhs_exprs = cse_cb(common_exprs[:ny], be.numbered_symbols('cse'))
+    off = ny
+    if nj:
+        jac_cses, jac_exprs = cse_cb(common_exprs[off:off + nj], be.numbered_symbols('cse'))
+        off += nj
+    if nfs:
+        fs_cses, fs_exprs = cse_cb(common_exprs[off:off + 1], be.numbered_symbols('cse'))
+        off += 1
+    if nroots:
+        roots_cses, roots_exprs = cse_cb(common_exprs[off:off + nroots], be.numbered_symbols('cse'))
+
+    flops = {
+        'pcse': _count([e for _s, e in common_cses]),
+        'rhs': _count([e for _s, e in rhs_cses] + list(rhs_exprs)),
+        'jac': _count([e for _s, e in jac_cses] + list(jac_exprs)) if nj else 0,
+    }
+    jac_nnz = sum(1 for e in jac_exprs[:ny*ny] if e != 0) if nj else 0
+
+    # ---- which leading entries of m_p are referenced at all ---------------------------------
+    used = -1
+    all_final = [e for _s, e in common_cses] + list(common_exprs)
+    psyms = list(odesys.params) + (list(odesys.init_dep) if odesys.append_iv and odesys.init_dep else [])
+    for i, ps in enumerate(psyms):
+        if any(ps in sympy.sympify(e).free_symbols for e in all_final):
+            used = i
+    np_used = used + 1
+    if any(key in ns_over for key in ('p_rhs', 'p_jac', 'p_first_step', 'p_get_dx_max', 'p_constructor')):
+        np_used = np_tot  # raw user source may read any entry
+
+    # ---- emit ---------------------------------------------------------------------------------
+    setup_lines = []
+    for symb, expr in common_cses:
+        tok = symb.name
+        if tok.startswith('m_p_cse'):
+            setup_lines.append('        %s = %s;' % (tok, cc(expr)))
+        else:
+            setup_lines.append('        const double %s = %s;' % (tok, cc(expr)))
+    for line in ns_over.get('p_constructor', []) + ns_ext.get('p_constructor', []):
+        setup_lines.append('        ' + line)
+
+    if 'p_rhs' in ns_over:
+        rhs_body = ns_over['p_rhs']
+    else:
+        rhs_body = _body([(s.name, cc(e)) for s, e in rhs_cses],
+                         [('f[%d]' % i, cc(e)) for i, e in enumerate(rhs_exprs)],
+                         ret='this->nfev++;\n        return AnyODE::Status::success;')
+
+    if 'p_jac' in ns_over:
+        jac_body = ns_over['p_jac']
+    elif nj:
+        assigns = [('jac[ldim*%d + %d]' % (idx // ny, idx % ny), cc(e))
+                   for idx, e in enumerate(jac_exprs[:ny*ny])]
+        dfdt_assigns = '\n'.join('            dfdt[%d] = %s;' % (i, cc(e))
+                                 for i, e in enumerate(jac_exprs[ny*ny:]))
+        jac_body = _body([(s.name, cc(e)) for s, e in jac_cses], assigns, ret=None)
+        jac_body += '\n        if (dfdt) {\n%s\n        }\n' % dfdt_assigns
+        jac_body += '        this->njev++;\n        return AnyODE::Status::success;'
+    else:
+        jac_body = '        return AnyODE::Status::unrecoverable_error;'
+
+    if 'p_first_step' in ns_over:
+        fs_body = '        ' + ns_over['p_first_step']
+        has_fs = True
+    elif nfs:
+        fs_body = _body([(s.name, cc(e)) for s, e in fs_cses], [], ret='return %s;' % cc(fs_exprs[0]))
+        has_fs = True
+    else:
+        fs_body = '        return 0.0;  // invokes the default behaviour of the stepper'
+        has_fs = False
+
+    if ns_over.get('p_get_dx_max'):
+        dxmax_body = '        ' + ns_over['p_get_dx_max']
+        has_dx_max = True
+    else:
+        dxmax_body = '        return INFINITY;'
+        has_dx_max = False
+
+    if nroots:
+        roots_body = _body([(s.name, cc(e)) for s, e in roots_cses],
+                           [('out[%d]' % i, cc(e)) for i, e in enumerate(roots_exprs)])
+    else:
+        roots_body = '        return AnyODE::Status::success;'
+
+    lb = odesys.lower_bounds
+    ub = odesys.upper_bounds
+
+    checks = []
+    if lb is not None:
+        checks += ['y[%d] < %r' % (i, float(v)) for i, v in enumerate(lb)]
+    if ub is not None:
+        checks += ['y[%d] > %r' % (i, float(v)) for i, v in enumerate(ub)]
+    bounds_body = '        return %s;' % (' || '.join(checks) if checks else 'false')
+
+    anon = ns_over.get('p_anon') or ''
+    includes = ''.join('#include %s\n' % inc for inc in ns_ext.get('p_includes', []))
+    macros = [
+        ('ODESYS_NY', ny), ('ODESYS_NPARAMS', nparams), ('ODESYS_NP_TOT', np_tot),
+        ('ODESYS_NP_USED', np_used), ('ODESYS_NPCSE', npcse), ('ODESYS_HAS_JAC', int(bool(nj) or 'p_jac' in ns_over)),
+        ('ODESYS_AUTONOMOUS', int(odesys.autonomous_exprs)), ('ODESYS_HAS_FIRST_STEP', int(has_fs)),
+        ('ODESYS_HAS_DX_MAX', int(has_dx_max)), ('ODESYS_NROOTS', nroots),
+        ('ODESYS_FLOPS_RHS', flops['rhs']), ('ODESYS_FLOPS_JAC', flops['jac']),
+        ('ODESYS_FLOPS_PCSE', flops['pcse']), ('ODESYS_JAC_NNZ', jac_nnz),
+        ('ODESYS_HAS_BOUNDS', int(lb is not None or ub is not None)),
+        ('ODESYS_NONNEGATIVE', int(bool(getattr(odesys, '_nonnegative', False)))),
+    ]
+    text = '''// -*- mode: read-only -*-
+// Generated by pyodesys_b200.native._codegen (CUDA counterpart of
+// pyodesys/native/sources/odesys_anyode_template.cpp).  Do not edit.
+#pragma once
+%(macros)s
+#include "odesys_prelude.h"
+%(includes)s
+%(anon)s
+
+namespace odesys_anyode {
+struct OdeSys {
+    double m_p[ODESYS_NP_TOT > 0 ? ODESYS_NP_TOT : 1];
+    double m_p_cse[ODESYS_NPCSE > 0 ? ODESYS_NPCSE : 1];
+    int nfev, njev;
+
+    // template:163-190 - true when a lower/upper bound is violated
+    ODESYS_FN bool outside_bounds(const double * const y) const {
+        AnyODE::ignore(y);
+%(bounds)s
+    }
+    // template:92-125 - parameter-only sub-expressions, once per system
+    ODESYS_FN void setup() {
+        nfev = 0; njev = 0;
+%(setup)s
+    }
+    // template:147-204
+    ODESYS_FN AnyODE::Status rhs(double x, const double * const ODESYS_RESTRICT y,
+                                 double * const ODESYS_RESTRICT f) {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(rhs)s
+    }
+    // template:246-293 (row-major: jac[ldim*row + col]); all ny*ny entries are written
+    ODESYS_FN AnyODE::Status dense_jac_rmaj(double x, const double * const ODESYS_RESTRICT y,
+                                            const double * const ODESYS_RESTRICT fy,
+                                            double * const ODESYS_RESTRICT jac, long int ldim,
+                                            double * const ODESYS_RESTRICT dfdt) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(fy); AnyODE::ignore(ldim);
+%(jac)s
+    }
+    // template:295-309
+    ODESYS_FN double get_dx0(double x, const double * const y) {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(fs)s
+    }
+    // template:346-375
+    ODESYS_FN double get_dx_max(double x, const double * const y) {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(dxmax)s
+    }
+    // template:377-396
+    ODESYS_FN AnyODE::Status roots(double x, const double * const y, double * const out) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(out);
+%(roots)s
+    }
+};
+}  // namespace odesys_anyode
+''' % dict(
+        macros='\n'.join('#define %s %d' % kv for kv in macros),
+        includes=includes, anon=anon,
+        bounds=bounds_body,
+        setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body, fs=fs_body,
+        dxmax=dxmax_body, roots=roots_body)
+
+    return GeneratedCode(text, ny, nparams, np_tot, np_used, npcse, flops,
+                         has_jac=bool(nj) or 'p_jac' in ns_over,
+                         autonomous=bool(odesys.autonomous_exprs), has_first_step=has_fs,
+                         has_dx_max=has_dx_max, nroots=nroots, jac_nnz=jac_nnz)
