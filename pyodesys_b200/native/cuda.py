@@ -238,6 +238,28 @@ class CudaModule:
         self._check(rc)
         return xyout, nrows, status, counters, timings
 
+    def integrate_predefined_device(self, n, nt, y0, xout, params, atol, rtol, yout, nreached, status,
+                                    counters=None, dx0=None, dx_min=None, dx_max=None, mxsteps=0,
+                                    method=None, autorestart=0, device=0, stream=None, xout_shared=False,
+                                    yout_soa=False, **kw):
+        """ Device-resident call (``ptr_kind=1``): every array argument is a device address (int,
+        e.g. ``tensor.data_ptr()``) on ``device``; nothing is copied.  Returns the timings array. """
+        atol = np.ascontiguousarray(np.atleast_1d(atol), dtype=np.float64)
+        if atol.size != 1 and atol.size != self.ny:
+            raise ValueError("atol needs to be of length 1 or %d" % self.ny)
+        mid = METHODS[(method or self.default_method()).lower()]
+        opts = self._options(xout_shared=xout_shared, **kw)
+        opts.yout_soa = int(bool(yout_soa))
+        opts.stream = stream
+        timings = np.zeros(NTIMINGS)
+        rc = self.lib.pyodesys_cuda_integrate_predefined(
+            device, n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size, float(rtol),
+            _ptr(dx0), _ptr(dx_min), _ptr(dx_max), int(mxsteps), mid, int(autorestart), 0,
+            _ptr(yout), _ptr(nreached, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(timings), 1,
+            ctypes.byref(opts))
+        self._check(rc)
+        return timings
+
     # -- reference-shaped entry points --------------------------------------------------------
     @staticmethod
     def _nfo(i, n, status, counters, timings, mode, nreached=None):
@@ -306,7 +328,13 @@ def _raise_on_failure(status, return_on_error):
                            (bad.size, status.size, i, STATUS_TEXT.get(int(status[i]), 'unknown')))
 
 
-_build_lock = threading.Lock()
+_build_locks = {}
+_build_locks_guard = threading.Lock()
+
+
+def _lock_for(tag):
+    with _build_locks_guard:
+        return _build_locks.setdefault(tag, threading.Lock())
 
 
 class NativeCudaCode:
@@ -337,7 +365,7 @@ class NativeCudaCode:
     def ensure_built(self):
         if os.path.exists(self.so_file):
             return self.so_file
-        with _build_lock:
+        with _lock_for(self.tag):
             if os.path.exists(self.so_file):
                 return self.so_file
             self.write_source()
@@ -414,15 +442,15 @@ class NativeCudaSys(SymbolicSys):
             binfo = BatchInfo('adaptive', status, None, counters, 0.0, 0.0, xs, ys, intern_p,
                               return_on_error, timings=_tdict(timings), method=method)
         else:
-            xout = np.ascontiguousarray(intern_x, dtype=np.float64)
-            if xout.shape[0] > 1 and intern_x.strides[0] == 0:
-                xout_arg = xout[0]  # one broadcast row: ship it once (options.xout_shared)
+            if intern_x.shape[0] > 1 and intern_x.strides[0] == 0:
+                # one broadcast row (core.to_arrays): ship it once (options.xout_shared)
+                xout_arg = np.ascontiguousarray(intern_x[0], dtype=np.float64)
             else:
-                xout_arg = xout
+                xout_arg = np.ascontiguousarray(intern_x, dtype=np.float64)
             yout, nreached, status, counters, timings = mod.integrate_predefined_arrays(
                 y0, xout_arg, params, atol, rtol, dx0=first_step, mxsteps=nsteps, **kwargs)
             binfo = BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, intern_p,
-                              return_on_error, nt=xout.shape[-1], timings=_tdict(timings), method=method)
+                              return_on_error, nt=intern_x.shape[-1], timings=_tdict(timings), method=method)
         n = len(binfo)
         binfo.time_wall = binfo.timings.get('kernel', 0.0)/max(n, 1)
         binfo.time_cpu = (time.time() - t0)/max(n, 1)

@@ -1,0 +1,118 @@
+# -*- coding: utf-8 -*-
+"""
+ODE systems that only the tests use.  ``__graft_entry__.build()`` imports :func:`all_systems` so
+that every library is compiled in the build container and merely loaded on the GPU box.
+"""
+import numpy as np
+import sympy as sp
+
+from pyodesys_b200 import systems
+from pyodesys_b200.native.cuda import NativeCudaSys
+
+_cache = {}
+
+
+def _get(key, mk):
+    if key not in _cache:
+        _cache[key] = mk()
+    return _cache[key]
+
+
+def decay3_rhs(x, y, p):
+    """ ``_decay3`` of pyodesys/tests/test_symbolic.py:40-49: every species decays """
+    return [-p[0]*y[0], p[0]*y[0] - p[1]*y[1], p[1]*y[1] - p[2]*y[2]]
+
+
+def expy(compile=True):
+    """ dy/dx = e^y (``pyodesys/tests/test_symbolic.py:274-286``, G9) """
+    return _get(('expy', compile), lambda: NativeCudaSys.from_callback(
+        lambda x, y, p, be: [be.exp(y[0])], 1, 0, compile=compile))
+
+
+def decay_err(compile=True):
+    """ G8: rhs that reports a recoverable error for x > 0.5 - the reference's own override snippet
+    (``pyodesys/native/tests/_tests.py:324-333``) compiled verbatim as device code. """
+    return _get(('decay_err', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_chain_rhs, 3, 2, compile=compile, namespace_override={
+            'p_rhs': """
+        f[0] = -m_p[0]*y[0];
+        f[1] = m_p[0]*y[0] - m_p[1]*y[1];
+        f[2] = m_p[1]*y[1];
+        if (x > 0.5) return AnyODE::Status::recoverable_error;
+        this->nfev++;
+        return AnyODE::Status::success;
+"""}))
+
+
+def decay3_dxmax(compile=True):
+    """ ``_test_NativeSys__get_dx_max_source_code`` (``_tests.py:275-292``) """
+    return _get(('decay3_dxmax', compile), lambda: NativeCudaSys.from_callback(
+        decay3_rhs, 3, 3, compile=compile, namespace_override={
+            'p_get_dx_max': "AnyODE::ignore(y); return (1.0e-4 * x + 1.0e-3);"}))
+
+
+def decay3_first_step(compile=True):
+    """ ``_test_NativeSys__first_step_cb`` (``_tests.py:230-240``): first_step_expr = y0*1e-30 """
+    return _get(('decay3_fs', compile), lambda: NativeCudaSys.from_callback(
+        decay3_rhs, 3, 3, compile=compile,
+        first_step_factory=lambda x, y, p, be: y[0]*1e-30))
+
+
+def decay3(compile=True):
+    return _get(('decay3', compile), lambda: NativeCudaSys.from_callback(
+        decay3_rhs, 3, 3, compile=compile))
+
+
+def decay_k43(compile=True):
+    """ ``_test_NativeSys_two`` second system (``_tests.py:32-50``): hard-coded k=[4,3], no params """
+    return _get(('decay_k43', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_dydt_factory([4, 3]), 3, 0, compile=compile))
+
+
+def decay_named(compile=True):
+    """ ``_test_NativeSys__dep_by_name__single_varied`` (``_tests.py:305-318``) """
+    def mk():
+        y = sp.symarray('y', 3)
+        f = systems.decay_dydt_factory([4, 3])(0, y)
+        return NativeCudaSys(zip(y, f), names='a b c'.split(), dep_by_name=True, compile=compile)
+    return _get(('decay_named', compile), mk)
+
+
+def forced(compile=True):
+    """ non-autonomous system: exercises df/dx in the Rosenbrock stepper """
+    return _get(('forced', compile), lambda: NativeCudaSys.from_callback(
+        lambda x, y, p, be: [-p[0]*(y[0] - be.sin(p[1]*x)), y[0] - y[1]], 2, 2, compile=compile))
+
+
+def lu6(compile=True):
+    """ any 6-variable system: gives the NY=6 instance of the register LU (AnyODE test_decomp.cpp:19-45) """
+    return _get(('lu6', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_chain_rhs, 6, 5, compile=compile))
+
+
+def nojac(compile=True):
+    return _get(('nojac', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_f, 2, 1, jac=False, compile=compile))
+
+
+def bounded(compile=True):
+    """ decay with lower bounds -> recoverable error branch of rhs (template:163-190) """
+    return _get(('bounded', compile), lambda: NativeCudaSys.from_callback(
+        decay3_rhs, 3, 3, lower_bounds=[0, 0, 0], compile=compile))
+
+
+def all_systems(compile=True):
+    fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
+           nojac, bounded]
+    return {f.__name__: f(compile=compile) for f in fns}
+
+
+def full_params(y0, p=None):
+    """ params as the native layer receives them: [p..., y0...] (append_iv, core.py:410-411) """
+    y0 = np.atleast_2d(np.asarray(y0, dtype=float))
+    if p is None:
+        return y0.copy()
+    p = np.atleast_2d(np.asarray(p, dtype=float))
+    if p.shape[0] == 1 and y0.shape[0] > 1:
+        p = np.tile(p, (y0.shape[0], 1))
+    return np.concatenate((p, y0), axis=1)

@@ -1,0 +1,385 @@
+# -*- coding: utf-8 -*-
+"""
+GPU parity tests (``-m gpu``): the CUDA path, called through the C ABI, against
+
+* the reference's own known answers (``tests/golden/golden.json``: G1-G9 of SURVEY.md §8c),
+* the CPU oracle (``oracle/``) on the same seeded inputs,
+* size independent properties (mass conservation, idempotence under tolerance tightening).
+
+Tolerance rule of BASELINE.json ``north_star``: final and tout states within
+``max(10*rtol*|y|, 10*atol)`` of the reference path; 1e-12 for the fixed-step RK4 mode.
+"""
+import numpy as np
+import pytest
+
+from pyodesys_b200 import systems
+from oracle import build_oracle, RefAnyodeLU
+
+import systems_for_tests as tsys
+from systems_for_tests import full_params
+
+pytestmark = pytest.mark.gpu
+
+
+def bateman_full(y0, lmbd, t):
+    """ analytic linear decay chain (restated from the Bateman equation; distinct rates) """
+    n = len(lmbd)
+    t = np.asarray(t, dtype=float)
+    N = [np.zeros_like(t) for _ in range(n)]
+    for i0, y00 in enumerate(y0):
+        if y00 == 0:
+            continue
+        lm = lmbd[i0:]
+        for i in range(len(lm)):
+            prod = np.prod(lm[:i]) if i > 0 else 1.0
+            s = np.zeros_like(t)
+            for k in range(i + 1):
+                den = 1.0
+                for l in range(i + 1):
+                    if l != k:
+                        den *= lm[l] - lm[k]
+                s += np.exp(-lm[k]*t)/den
+            N[i0 + i] = N[i0 + i] + y00*prod*s
+    return np.array(N).T
+
+
+def within(y, ref, rtol, atol, factor=10):
+    return np.abs(y - ref) <= np.maximum(factor*rtol*np.abs(ref), factor*atol)
+
+
+# ---- G1 --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+def test_vdp_blessed_values(cuda_device, golden, method):
+    """ ``_test_NativeSys`` (pyodesys/native/tests/_tests.py:20-29) """
+    native = systems.vdp()
+    assert native.ny == 2 and len(native.params) == 1
+    xout, yout, info = native.integrate([0, 1, 2], [1, 0], params=[2.0], method=method)
+    assert np.allclose(yout, golden['known_answers']['vdp_mu2_t012'])
+    assert info['nfev'] > 0 and info['success'] and info['mode'] == 'predefined' and info['nreached'] == 3
+
+
+# ---- G2 --------------------------------------------------------------------------------------------------
+def test_rk4_fixed_step_matches_reference_integrator(cuda_device, golden):
+    """ 1e-12 against pyodesys.integrators.RK4_example_integrator (test_core.py:149-166) """
+    g = golden['rk4_predefined']
+    native = systems.vdp()
+    res = native.integrate(np.array(g['xout']), [1, 0], params=[2.0], method='rk4')
+    assert np.abs(res.yout - np.array(g['yout'])).max() < 1e-12
+    assert res.info['nfev'] == g['nfev'] == 4*149
+    assert np.allclose(res.yout[-1], [-1.89021896, -0.71633577])
+    # the first_step=1e-2 variant through the adaptive API (the reference repeats the end point once)
+    g = golden['rk4_adaptive']
+    res = native.integrate([0, 2], [1, 0], params=[2.0], method='rk4', first_step=1e-2)
+    nrow = res.xout.size
+    assert nrow == 201
+    assert np.abs(res.xout - np.array(g['xout'])[:nrow]).max() < 1e-12
+    assert np.abs(res.yout - np.array(g['yout'])[:nrow]).max() < 1e-12
+    assert res.info['nfev'] == g['nfev'] == 800
+
+
+# ---- G3 / G4 ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+def test_multiple_predefined(cuda_device, method):
+    """ ``_test_integrate_multiple_predefined`` (test_core.py:182-193), atol=rtol=1e-10 (test_odeint.py:44-46) """
+    odes = systems.decay()
+    _xout = np.array([[0, 1, 2], [0, 1, 2], [0, 1, 2]])
+    _y0 = np.array([[1, 2], [2, 3], [3, 4]])
+    _params = np.array([[5], [6], [7]])
+    results = odes.integrate(_xout, _y0, params=_params, atol=1e-10, rtol=1e-10, method=method, nsteps=2000)
+    assert len(results) == 3
+    for idx in range(3):
+        xout, yout, info = results[idx]
+        ref = _y0[idx, 0]*np.exp(-_params[idx, 0]*xout)
+        assert np.allclose(yout[:, 0], ref)
+        assert np.allclose(yout[:, 1], _y0[idx, 0] - ref + _y0[idx, 1])
+        assert info['nfev'] > 0
+
+
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+def test_multiple_adaptive(cuda_device, method):
+    """ ``_test_integrate_multiple_adaptive`` (test_core.py:281-297): per-system spans """
+    odes = systems.sine()
+    _xout = np.array([[0, 1], [1, 2], [1, 7]])
+    Ak = [[2, 3], [3, 4], [4, 5]]
+    _y0 = [[0., A*k] for A, k in Ak]
+    _params = [[k] for A, k in Ak]
+    results = odes.integrate(_xout, _y0, _params, method=method, nsteps=5000, atol=1e-8, rtol=1e-8)
+    for idx in range(3):
+        xout, yout, info = results[idx]
+        A, k = Ak[idx]
+        assert xout[0] == _xout[idx, 0] and xout[-1] == _xout[idx, 1] and xout.size > 5
+        assert np.allclose(yout[:, 0], A*np.sin(k*(xout - xout[0])), atol=1e-5, rtol=1e-5)
+        assert np.allclose(yout[:, 1], A*np.cos(k*(xout - xout[0]))*k, atol=1e-5, rtol=1e-5)
+        assert info['nfev'] > 0 and info['mode'] == 'adaptive' and info['success']
+
+
+# ---- G5 --------------------------------------------------------------------------------------------------
+def test_two_systems_alive_and_bateman(cuda_device, golden):
+    """ ``_test_NativeSys_two`` (_tests.py:32-50) """
+    native1 = systems.vdp()
+    native2 = tsys.decay_k43()
+    tol = 1e-11
+    xout1, yout1, info1 = native1.integrate([0, 1, 2], [1, 0], params=[2.0], nsteps=500)
+    xout2, yout2, info2 = native2.integrate(2, (5, 4, 2), atol=tol, rtol=tol, nsteps=5000, method='dopri5')
+    assert np.allclose(yout1, golden['known_answers']['vdp_mu2_t012'])
+    ref2 = bateman_full((5, 4, 2), [4, 3, 0], xout2 - xout2[0])
+    assert np.allclose(yout2, ref2, rtol=150*tol, atol=150*tol)
+    g = golden['bateman']['k43']
+    res = native2.integrate(np.array(g['t']), g['y0'], atol=tol, rtol=tol, nsteps=5000)
+    assert np.allclose(res.yout, np.array(g['y']), rtol=150*tol, atol=150*tol)
+
+
+# ---- G6 --------------------------------------------------------------------------------------------------
+def test_robertson_1e11_batched(cuda_device, golden):
+    """ N=3 identical Robertson systems to t=1e11 (_test_robertson_native.py:52-71; test_robertson.py:15) """
+    rob = systems.robertson()
+    yref = golden['known_answers']['robertson_1e11']
+    res = rob.integrate([(0, 1e11)]*3, [[1, 0, 0]]*3, [[0.04, 1e4, 3e7]]*3, atol=1e-16, rtol=1e-8,
+                        nsteps=5000, method='rosenbrock4')
+    for r in res:
+        assert r.info['success'] and r.info['nfev'] > 100 and r.info['njev'] > 10
+        assert np.allclose(yref, r.yout[-1], atol=1e-16, rtol=0.02)
+        assert abs(r.yout[-1].sum() - 1) < 1e-9
+
+
+# ---- G8 --------------------------------------------------------------------------------------------------
+def test_return_on_error(cuda_device):
+    """ ``_test_return_on_error_success`` (_tests.py:321-340) """
+    k, y0 = [4, 3], (5, 4, 2)
+    native = tsys.decay_err()
+    xout = [0, 0.2, 0.4, 0.6, 0.8, 1.0]
+    result = native.integrate(xout, y0, k, atol=1e-11, rtol=1e-11, return_on_error=True, dx_max=.05,
+                              nsteps=2000, method='dopri5')
+    nreached = result.info['nreached']
+    assert nreached == 3
+    ref = bateman_full(y0, k + [0], result.xout[:nreached] - xout[0])
+    assert result.info['success'] is False
+    assert np.allclose(result.yout[:nreached, :], ref, rtol=1e-8, atol=1e-8)
+    with pytest.raises(RuntimeError):
+        native.integrate(xout, y0, k, atol=1e-11, rtol=1e-11, dx_max=.05, nsteps=2000, method='dopri5')
+
+
+# ---- G9 --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('method', ['rosenbrock4', 'dopri5'])
+def test_exp_y(cuda_device, method):
+    """ dy/dx = e^y, y(0)=1 -> y(0.1) = -ln(1/e - 0.1) to 4e-8 (test_symbolic.py:274-286) """
+    odesys = tsys.expy()
+    res = odesys.integrate(0.1, [1.0], atol=1e-10, rtol=1e-10, method=method, nsteps=1000)
+    assert abs(res.yout[-1, 0] - (-np.log(1/np.e - 0.1))) < 4e-8
+
+
+# ---- first step / dx_max overrides ---------------------------------------------------------------------------
+def test_first_step_expr(cuda_device):
+    """ ``_test_NativeSys__first_step_cb`` (_tests.py:230-240) """
+    odesys = tsys.decay3_first_step()
+    y0, k = [.7, 0, 0], [1e23, 2, 3.]
+    res = odesys.integrate(5, y0, k, atol=1e-8, rtol=1e-8, nsteps=5000)
+    ref = bateman_full(y0, k, res.xout - res.xout[0])
+    assert res.info['success'] and res.info['nfev'] > 10
+    assert np.allclose(res.yout, ref, atol=20e-8, rtol=20e-8)
+
+
+def test_get_dx_max_source_code(cuda_device):
+    """ ``_test_NativeSys__get_dx_max_source_code`` (_tests.py:275-292) """
+    odesys = tsys.decay3_dxmax()
+    y0, k = [.7, 0, 0], [7., 2, 3.]
+    res = odesys.integrate(1, y0, k, get_dx_max_factor=1.0, atol=1e-8, rtol=1e-8, nsteps=1000, method='dopri5')
+    ref = bateman_full(y0, k, res.xout - res.xout[0])
+    assert np.allclose(res.yout, ref, atol=20e-8, rtol=20e-8)
+    assert res.info['success'] and res.info['nfev'] > 10
+    assert 750 < res.info['n_steps'] <= 1000
+
+
+def test_dep_by_name_single_varied(cuda_device):
+    """ ``_test_NativeSys__dep_by_name__single_varied`` (_tests.py:305-318): N=7 by broadcasting """
+    tend, kf, y0 = 2, [4, 3], {'a': (5, 3, 7, 9, 1, 6, 11), 'b': 4, 'c': 2}
+    odesys = tsys.decay_named()
+    results = odesys.integrate(tend, y0)
+    assert len(results) == 7
+    for idx in range(7):
+        xout, yout, info = results[idx]
+        assert info['success']
+        assert xout.size == yout.shape[0] and yout.shape[1] == 3
+        ref = bateman_full([y0[k][idx] if k == 'a' else y0[k] for k in odesys.names], kf + [0], xout - xout[0])
+        assert np.allclose(yout, ref)
+
+
+# ---- generated device functions and the register LU -------------------------------------------------------------
+@pytest.mark.parametrize('name', ['robertson', 'vdp', 'lorenz'])
+def test_generated_rhs_and_jacobian(cuda_device, name):
+    sysobj = getattr(systems, name)()
+    mod = sysobj._native.mod
+    rng = np.random.default_rng(5)
+    n = 257
+    y = rng.uniform(0.1, 2.0, size=(n, sysobj.ny))
+    p = rng.uniform(0.5, 3.0, size=(n, len(sysobj.params)))
+    pf = full_params(y, p)
+    f, J, dfdt = mod.eval_rhs_jac(0.3, y, pf)
+    f_ref = sysobj.f_numeric(0.3, y, pf)
+    J_ref = sysobj.j_numeric(0.3, y, pf)
+    assert np.allclose(f, f_ref, rtol=1e-14, atol=1e-14)
+    assert np.allclose(J, J_ref, rtol=1e-14, atol=1e-14)
+    assert np.all(dfdt == 0)
+    fo, Jo, _ = build_oracle(sysobj._native).eval_rhs_jac(0.3, y, pf)
+    assert np.allclose(f, fo, rtol=1e-15, atol=1e-300) and np.allclose(J, Jo, rtol=1e-15, atol=1e-300)
+
+
+def test_register_lu_against_anyode(cuda_device):
+    """ the reference's own getrf/getrs (oracle/_ref) and its 6x6 known system (test_decomp.cpp:19-45 style) """
+    mod = tsys.lu6()._native.mod
+    rng = np.random.default_rng(6)
+    n = 1000
+    A = rng.standard_normal((n, 6, 6))
+    A[::7, 0, 0] = 0.0  # force pivoting
+    b = rng.standard_normal((n, 6))
+    x, ok = mod.lu_solve(A, b)
+    xr, info = RefAnyodeLU().solve(A, b)
+    assert ok.all() and (info == 0).all()
+    scale = np.abs(xr).max(axis=1, keepdims=True)
+    assert (np.abs(x - xr) <= 1e-9*scale).all()
+    assert np.allclose(np.einsum('nij,nj->ni', A, x), b, atol=1e-8)
+    x3, ok3 = systems.robertson()._native.mod.lu_solve(A[:, :3, :3], b[:, :3])
+    x3r, _ = RefAnyodeLU().solve(A[:, :3, :3], b[:, :3])
+    assert (np.abs(x3 - x3r) <= 1e-9*np.abs(x3r).max(axis=1, keepdims=True)).all()
+
+
+# ---- CUDA path vs CPU oracle on seeded batches ---------------------------------------------------------------------
+def test_robertson_batch_vs_oracle_and_lsoda(cuda_device, golden):
+    rob = systems.robertson()
+    orc = build_oracle(rob._native)
+    n = 4096
+    b = systems.batch_robertson(n=n, seed=3)
+    res = rob.integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                        method='rosenbrock4', force_predefined=True)
+    info = res.info
+    assert (info.status == 0).all() and (info.nreached == 2).all()
+    y_gpu = res.yout[:, -1, :]
+    y_cpu, nr, st, cn = orc.integrate_predefined(b['y0'], np.array([0.0, 1e5]), full_params(b['y0'], b['params']),
+                                                 b['atol'], b['rtol'], mxsteps=b['nsteps'], method='rosenbrock4')
+    assert (st == 0).all()
+    ok = within(y_gpu, y_cpu[:, -1, :], b['rtol'], b['atol'])
+    assert ok.all(), "worst err/tol %g" % (np.abs(y_gpu - y_cpu[:, -1]) /
+                                          np.maximum(10*b['rtol']*np.abs(y_cpu[:, -1]), 10*b['atol'])).max()
+    # same algorithm -> nearly the same amount of work
+    assert abs(info.counters[0].sum() - cn[0].sum()) <= 0.02*cn[0].sum()
+    assert np.abs(y_gpu.sum(axis=1) - 1).max() < 1e-9  # linear invariant A+B+C
+    # tight LSODA runs of the reference (first 48 systems of the same seeded batch)
+    g = golden['robertson_1e5']
+    ref = np.array(g['yout'])[:, -1, :]
+    assert np.allclose(np.array(g['y0']), b['y0'][:48]) and np.allclose(np.array(g['k']), b['params'][:48])
+    assert within(y_gpu[:48], ref, b['rtol'], b['atol'], factor=100).all()
+
+
+def test_robertson_dense_output_vs_lsoda(cuda_device, golden):
+    g = golden['robertson_1e5']
+    rob = systems.robertson()
+    y0, k = np.array(g['y0']), np.array(g['k'])
+    res = rob.integrate(np.array(g['xout']), y0, k, atol=1e-14, rtol=1e-9, nsteps=50000, method='rosenbrock4')
+    ref = np.array(g['yout'])
+    assert within(res.yout, ref, 1e-9, 1e-14, factor=1000).all()
+
+
+def test_vdp_batch_vs_oracle_and_lsoda(cuda_device, golden):
+    vd = systems.vdp()
+    orc = build_oracle(vd._native)
+    g = golden['vdp_lsoda']
+    y0 = np.array(g['y0'])
+    xo = np.array(g['xout'])
+    res = vd.integrate(xo, y0, [[1.0]]*len(y0), atol=1e-10, rtol=1e-10, nsteps=5000, method='dopri5')
+    assert within(res.yout, np.array(g['yout']), 1e-10, 1e-10, factor=1e4).all()
+    y_cpu, nr, st, cn = orc.integrate_predefined(y0, xo, full_params(y0, [[1.0]]), 1e-10, 1e-10, mxsteps=5000,
+                                                 method='dopri5')
+    assert within(res.yout, y_cpu, 1e-10, 1e-10, factor=100).all()
+    # C1 as specified: adaptive mode, 1e4 initial conditions, t=10
+    b = systems.batch_vdp(n=10000)
+    res = vd.integrate([b['x']]*10000, b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                       method='dopri5')
+    assert (res.info.status == 0).all()
+    xy, nrows, st, cn = orc.integrate_adaptive(b['y0'][:512], 0.0, 10.0, full_params(b['y0'][:512], b['params'][:512]),
+                                               b['atol'], b['rtol'], mxsteps=b['nsteps'], method='dopri5')
+    for i in range(0, 512, 17):
+        yo = xy[i, nrows[i] - 1, 1:]
+        assert within(res[i].yout[-1], yo, b['rtol'], b['atol'], factor=100).all()
+        assert res[i].xout[-1] == 10.0
+
+
+def test_lorenz_dense_output(cuda_device, golden):
+    g = golden['lorenz_lsoda']
+    lo = systems.lorenz()
+    res = lo.integrate(np.array(g['xout']), [g['y0']]*4, [g['p']]*4, atol=1e-11, rtol=1e-11, nsteps=5000,
+                       method='dopri5')
+    assert within(res.yout[0], np.array(g['yout']), 1e-11, 1e-11, factor=1e4).all()
+    assert np.array_equal(res.yout[0], res.yout[3])  # identical systems give identical bits
+    b = systems.batch_lorenz(n=20000, nt=100)
+    r = lo.integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'], method='dopri5')
+    assert (r.info.status == 0).all() and np.isfinite(r.yout).all()
+    orc = build_oracle(lo._native)
+    y_cpu, _, _, _ = orc.integrate_predefined(b['y0'][:256], b['x'], full_params(b['y0'][:256], b['params'][:256]),
+                                              b['atol'], b['rtol'], mxsteps=b['nsteps'], method='dopri5')
+    short = b['x'] <= 2.0  # chaotic: only the short horizon is comparable
+    assert within(r.yout[:256][:, short], y_cpu[:, short], 1e-8, 1e-8, factor=1000).all()
+
+
+def test_non_autonomous_rosenbrock(cuda_device):
+    fo = tsys.forced()
+    orc = build_oracle(fo._native)
+    y0 = np.array([[1.0, 0.5], [0.2, 0.1]])
+    p = np.array([[50.0, 3.0], [5.0, 1.0]])
+    xo = np.linspace(0, 3, 7)
+    res = fo.integrate(xo, y0, p, atol=1e-10, rtol=1e-10, nsteps=20000, method='rosenbrock4')
+    ref = fo.integrate(xo, y0, p, atol=1e-12, rtol=1e-12, nsteps=20000, method='dopri5')
+    assert within(res.yout, ref.yout, 1e-10, 1e-10, factor=1000).all()
+    y_cpu, _, st, _ = orc.integrate_predefined(y0, xo, full_params(y0, p), 1e-10, 1e-10, mxsteps=20000,
+                                               method='rosenbrock4')
+    assert within(res.yout, y_cpu, 1e-10, 1e-10, factor=100).all()
+
+
+# ---- error conventions and edge cases ---------------------------------------------------------------------------------
+def test_error_conventions(cuda_device):
+    odes = systems.decay()
+    with pytest.raises(ValueError, match="NaN found in y0"):
+        odes.integrate([0, 1], [np.nan, 1], [1.0])
+    with pytest.raises(ValueError, match="atol needs to be of length 1 or 2"):
+        odes.integrate([0, 1], [1, 1], [1.0], atol=[1e-8, 1e-8, 1e-8])
+    with pytest.raises(ValueError, match="incompatible kwargs integrator"):
+        odes.integrate([0, 1], [1, 1], [1.0], integrator='cvode')
+    with pytest.raises(ValueError, match="dx_max too short"):
+        odes.integrate([[0, 1]]*3, [[1, 1]]*3, [[1.0]]*3, dx_max=[0.1, 0.1])
+    with pytest.raises(RuntimeError):
+        tsys.nojac().integrate([0, 1], [1, 1], [1.0], method='rosenbrock4')
+    # vector atol is accepted
+    r = odes.integrate([0, 1, 2], [1, 1], [1.0], atol=[1e-9, 1e-8], rtol=1e-9, force_predefined=True)
+    assert np.allclose(r.yout[:, 0], np.exp(-r.xout))
+    # too few steps -> failure raised / reported
+    rob = systems.robertson()
+    with pytest.raises(RuntimeError, match="too many steps"):
+        rob.integrate([0, 1e5], [1, 0, 0], [0.04, 1e4, 3e7], nsteps=5, force_predefined=True)
+    r = rob.integrate([0, 1e5], [1, 0, 0], [0.04, 1e4, 3e7], nsteps=5, force_predefined=True, return_on_error=True)
+    assert r.info['success'] is False and r.info['nreached'] == 1 and np.isnan(r.yout[-1]).all()
+    # autorestart buys more budget
+    r = rob.integrate([0, 1e5], [1, 0, 0], [0.04, 1e4, 3e7], nsteps=50, autorestart=40, force_predefined=True)
+    assert r.info['success']
+
+
+def test_edge_cases(cuda_device):
+    odes = systems.decay()
+    # single output point, zero-length span, backward integration, ragged x handled per system
+    r = odes.integrate([[0.0], [1.0]], [[1, 2], [3, 4]], [[1.0], [2.0]], force_predefined=True)
+    assert np.array_equal(r.yout[:, 0, :], [[1, 2], [3, 4]])
+    r = odes.integrate([[0.0, 0.0]], [[1, 2]], [[1.0]], force_predefined=True)
+    assert np.array_equal(r.yout[0], [[1, 2], [1, 2]])
+    r = odes.integrate([0, -1, -2], [1, 0], [1.0], atol=1e-10, rtol=1e-10, method='dopri5')
+    assert np.allclose(r.yout[:, 0], np.exp(-r.xout))
+    # many more systems than threads in flight, odd sizes
+    for n in (1, 31, 33, 129, 70001):
+        y0 = np.ones((n, 2))
+        p = np.linspace(0.5, 2.0, n)[:, None]
+        rr = odes.integrate([0.0, 1.0], y0, p, force_predefined=True, atol=1e-10, rtol=1e-10)
+        assert np.allclose(rr.yout[:, -1, 0], np.exp(-p[:, 0]), rtol=1e-8)
+    # static and dynamic schedules give identical bits
+    b = systems.batch_robertson(n=5000, seed=9, tend=1e2)
+    rob = systems.robertson()
+    kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'], force_predefined=True)
+    r1 = rob.integrate(b['x'], b['y0'], b['params'], schedule='static', **kw)
+    r2 = rob.integrate(b['x'], b['y0'], b['params'], schedule='dynamic', **kw)
+    assert np.array_equal(r1.yout, r2.yout) and np.array_equal(r1.info.counters, r2.info.counters)
