@@ -16,6 +16,7 @@ import ctypes
 import hashlib
 import os
 import subprocess
+import threading
 
 import numpy as np
 
@@ -26,6 +27,7 @@ REFERENCE = os.environ.get('PYODESYS_REFERENCE_ROOT', '/root/reference')
 REF_DIR = os.path.join(_here, '_ref')
 REF_LU = os.path.join(REF_DIR, 'libanyode_blasless.so')
 
+_build_lock = threading.Lock()
 _d = ctypes.POINTER(ctypes.c_double)
 _i32 = ctypes.POINTER(ctypes.c_int32)
 
@@ -45,9 +47,11 @@ def build_oracle(native_code):
     tag = hashlib.sha256((native_code.gen.digest + _oracle_digest()).encode()).hexdigest()[:16]
     out_dir = os.path.join(_here, '_build', tag)
     so = os.path.join(out_dir, 'liboracle.so')
-    if not os.path.exists(so):
+    with _build_lock:
+        exists = os.path.exists(so)
+    if not exists:
         os.makedirs(out_dir, exist_ok=True)
-        tmp = so + '.%d.tmp' % os.getpid()
+        tmp = so + '.%d.%d.tmp' % (os.getpid(), threading.get_ident())
         cmd = ['g++', '-O2', '-std=c++17', '-fopenmp', '-shared', '-fPIC', '-I', native_code.build_dir,
                '-I', _csrc, os.path.join(_here, 'oracle.cpp'), '-o', tmp]
         proc = subprocess.run(cmd, capture_output=True, text=True)

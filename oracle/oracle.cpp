@@ -57,7 +57,9 @@ struct Work {
     const Settings *cfg;
     int nlu = 0, nsolve = 0;
     int rhs(double x, const double *y, double *f) {
+        const int nfev0 = sys.nfev;
         int st = sys.rhs(x, y, f);
+        sys.nfev = nfev0 + 1;  // every call counts (template:161 increments before the checks)
 #if ODESYS_HAS_BOUNDS
         if (cfg->error_outside_bounds && sys.outside_bounds(y)) st = 1;
 #endif

@@ -222,7 +222,8 @@ class ODESys:
         except TypeError:
             _x = 0*x, x
         else:
-            _x = (0*x[0], x[0]) if nx == 1 else x
+            # a lone end point means (0, xend) (core.py:247-252); a single ROW of points does not
+            _x = (0*x[0], x[0]) if nx == 1 and np.ndim(x[0]) == 0 else x
         _y = self._conditional_from_dict(y, self.dep_by_name, self.names)
         _p = self._conditional_from_dict(p, self.par_by_name, self.param_names)
         callbacks = callbacks or self.to_arrays_callbacks

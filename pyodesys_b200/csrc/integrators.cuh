@@ -92,7 +92,13 @@ __device__ __forceinline__ double fast_pow(double x, float e) {
 
 __device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs &a, double x, const double *y,
                                                    double *f) {
+    // Every call counts as one evaluation (the reference's template increments nfev before its
+    // bound checks, odesys_anyode_template.cpp:161).  The counter is advanced HERE rather than by the
+    // generated/user body: with a body that skips ``nfev++`` on its error path (the override snippet of
+    // pyodesys/native/tests/_tests.py:324-333) nvcc 12.9 -O3 folded the whole step into "always fails".
+    const int nfev0 = sys.nfev;
     AnyODE::Status st = sys.rhs(x, y, f);
+    sys.nfev = nfev0 + 1;
 #if ODESYS_HAS_BOUNDS
     if (a.error_outside_bounds && sys.outside_bounds(y)) st = AnyODE::Status::recoverable_error;
 #endif

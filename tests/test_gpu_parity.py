@@ -221,7 +221,10 @@ def test_generated_rhs_and_jacobian(cuda_device, name):
     assert np.allclose(J, J_ref, rtol=1e-14, atol=1e-14)
     assert np.all(dfdt == 0)
     fo, Jo, _ = build_oracle(sysobj._native).eval_rhs_jac(0.3, y, pf)
-    assert np.allclose(f, fo, rtol=1e-15, atol=1e-300) and np.allclose(J, Jo, rtol=1e-15, atol=1e-300)
+    # same generated text on both sides; nvcc contracts a*b+c into FMA, g++ (x86-64, no -mfma) does not,
+    # so agreement is to a few ulp of the largest term rather than bit-exact
+    assert np.allclose(f, fo, rtol=1e-13, atol=4e-16*np.abs(fo).max())
+    assert np.allclose(J, Jo, rtol=1e-13, atol=4e-16*np.abs(Jo).max())
 
 
 def test_register_lu_against_anyode(cuda_device):
