@@ -36,13 +36,14 @@
 #ifndef PYODESYS_CUDA_H
 #define PYODESYS_CUDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define PYODESYS_CUDA_ABI_VERSION 1
+#define PYODESYS_CUDA_ABI_VERSION 2
 
 /* integration methods (``method=`` keyword of the reference wrappers) */
 #define PYODESYS_CUDA_RK4 0        /* fixed step classical Runge-Kutta (pyodesys/integrators.py:17-61) */
@@ -85,6 +86,13 @@ typedef struct pyodesys_cuda_options {
     int32_t blocks_per_sm;           /* 0 = library default (persistent grid = SMs * this) */
     int32_t yout_soa;                /* nonzero (ptr_kind 1 only): yout laid out [nt,ny,n] */
     void *stream;                    /* cudaStream_t to launch on (ptr_kind 1); NULL = library stream */
+    /* ABI v2.  The reference appends the initial values to every parameter row on the host
+     * (``append_iv``: ``numpy.concatenate((p, y0), axis=-1)``, pyodesys/core.py:410-411; consumed by
+     * ``m_p.assign(params, params + len(params) + ny)``, odesys_anyode_template.cpp:102).  With
+     * iv_from_y0 != 0 ``params`` holds only the user's np columns ([n, np], or [n, params_ld]) and the
+     * kernels take m_p[np + i] from y0[i] themselves: no O(N) host concatenation, ny*8 B less H2D per system. */
+    int32_t iv_from_y0;
+    int32_t params_ld;               /* leading dimension of ``params`` in doubles; 0 = dense rows */
 } pyodesys_cuda_options;
 
 /* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */
@@ -132,6 +140,13 @@ int pyodesys_cuda_integrate_adaptive(
 int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params,
                        double *f, double *jac, double *dfdt);
 int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok);
+
+/* Page-locked host memory for inputs/outputs of the ptr_kind 0 calls (portable across devices).  D2H/H2D
+ * of pageable numpy memory runs at ~6 GB/s through the driver's staging buffer; pinned memory reaches
+ * PCIe speed.  The reference wrappers allocate ``yout`` themselves (numpy.empty, _odeint_wrapper.pyx:162);
+ * the binding uses this allocator for the same arrays.  Returns NULL on failure. */
+void *pyodesys_cuda_host_alloc(size_t bytes);
+void pyodesys_cuda_host_free(void *ptr);
 
 /* Number of kernel launches issued by this library since it was loaded (bench bookkeeping). */
 int64_t pyodesys_cuda_launch_count(void);

@@ -71,7 +71,7 @@ class BatchInfo:
     counter_names = ('n_steps', 'nfev', 'njev', 'nlu', 'nsolve', 'nreject')
 
     def __init__(self, mode, status, nreached, counters, time_wall, time_cpu, xout, yout, params,
-                 return_on_error, nt=None, timings=None, method=None):
+                 return_on_error, nt=None, timings=None, method=None, iv=None):
         self.mode = mode
         self.status = status
         self.nreached = nreached
@@ -80,11 +80,21 @@ class BatchInfo:
         self.time_cpu = time_cpu
         self.xout = xout
         self.yout = yout
-        self.params = params
+        self._params = params
+        self._iv = iv  # initial values still to be appended to the parameter rows (lazy append_iv)
         self.return_on_error = return_on_error
         self.nt = nt
         self.timings = timings or {}
         self.method = method
+
+    @property
+    def params(self):
+        """ internal parameter rows ``[p..., y0...]`` as the reference hands them to native code
+        (``core.py:410-411``); concatenated on first access only """
+        if self._iv is not None:
+            self._params = np.concatenate((self._params, self._iv), axis=-1)
+            self._iv = None
+        return self._params
 
     def __len__(self):
         return len(self.status)
@@ -282,7 +292,11 @@ class ODESys:
             raise ValueError("Pre-processor made ndims inconsistent?")
 
         if self.append_iv:
-            _p = np.concatenate((_p, _y), axis=-1)
+            if twodim and getattr(self, '_append_iv_on_device', False):
+                # the CUDA kernels read the appended initial values from y0 themselves (options.iv_from_y0)
+                kwargs['iv_from_y0'] = True
+            else:
+                _p = np.concatenate((_p, _y), axis=-1)
 
         if hasattr(self, 'ny') and _y.shape[-1] != self.ny:
             raise ValueError("Incorrect shape of intern_y0")

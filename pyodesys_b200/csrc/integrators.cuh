@@ -40,7 +40,9 @@ struct KernelArgs {
     int64_t n;
     int nt;                 // predefined: number of output points per system
     const double *y0;       // [n, NY]
-    const double *params;   // [n, NP_TOT]
+    const double *params;   // [n, params_ld]  (params_ld = NP_TOT, or the user's np columns with iv_from_y0)
+    int64_t params_ld;
+    int iv_from_y0;         // m_p[np + i] = y0[i] instead of a host-side concatenation (core.py:410-411)
     const double *xout;     // predefined: [n, nt] or [nt] (xout_stride == 0)
     int64_t xout_stride;
     const double *x0;       // adaptive: [n]
@@ -85,9 +87,25 @@ __device__ __forceinline__ bool finite_all(const double *v) {
 
 // x^(1/4), x^(-1/5), x^(-1/3) for step-size factors.  The factor only steers the step size, it
 // never enters the solution, so single precision SFU math (ex2/lg2) is ample.
-__device__ __forceinline__ double fast_pow(double x, float e) {
-    float xf = (float)fmin(fmax(x, 1e-30), 1e30);
-    return (double)exp2f(e * __log2f(xf));
+__device__ __forceinline__ float fast_powf(double x, float e) {
+    const float xf = (float)fmin(fmax(x, 1e-30), 1e30);
+    return exp2f(e * __log2f(xf));
+}
+__device__ __forceinline__ double fast_pow(double x, float e) { return (double)fast_powf(x, e); }
+
+// Reciprocal without the IEEE division's special-case slow path: MUFU.RCP64H seed (>= 20 bits) and
+// NEWTON Newton-Raphson steps (1: ~40 bits - step-size control; 2: full double to ~1 ulp - LU pivots,
+// 1/h).  Inputs are finite, non-zero and normal wherever this is used (checked by the callers'
+// ``ok`` / finite tests); a zero gives inf/NaN like the division would.
+template <int NEWTON> __device__ __forceinline__ double fast_rcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+#pragma unroll
+    for (int k = 0; k < NEWTON; ++k) {
+        const double e = fma(-x, r, 1.0);
+        r = fma(r, e, r);
+    }
+    return r;
 }
 
 __device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs &a, double x, const double *y,
@@ -114,6 +132,10 @@ __device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs
 // on the diagonal so the six triangular solves per Rosenbrock step are division free.
 // Same factorisation as AnyODE::getrf_callback (anyode_blasless.hpp:10-60): Doolittle, row
 // pivot = largest magnitude in the column (first one wins on ties).
+// Row interchanges are chains of 64-bit selects (2 FSEL each, ~14 % of the executed instructions for
+// ny = 3).  Guarding them with a warp vote (skip when no lane swaps - the common case for stiff
+// kinetics) was measured SLOWER on B200 (20.3 -> 21.4..22.5 ms per 1e6 Robertson systems): the
+// branches cost more issue slots and scheduling freedom than the selects they remove.
 template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) {
     bool ok = true;
 #pragma unroll
@@ -140,7 +162,7 @@ template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) 
             }
         }
         ok = ok && (amax > 0.0) && (amax <= DBL_MAX);
-        const double inv = 1.0 / a[k * N + k];
+        const double inv = fast_rcp<2>(a[k * N + k]);
         a[k * N + k] = inv;
 #pragma unroll
         for (int i = k + 1; i < N; ++i) {
@@ -155,6 +177,8 @@ template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) 
 
 // Solves L U x = P b in place (anyode_blasless.hpp:63-95).
 template <int N> __device__ __forceinline__ void lu_solve(const double *a, const int *piv, double *b) {
+    // the multipliers were swapped together with their rows (LAPACK convention), hence all row
+    // interchanges are applied to b before the forward substitution starts
 #pragma unroll
     for (int k = 0; k < N; ++k) {
 #pragma unroll
@@ -165,8 +189,6 @@ template <int N> __device__ __forceinline__ void lu_solve(const double *a, const
             b[i] = sw ? u : w;
         }
     }
-    // the multipliers were swapped together with their rows (LAPACK convention), hence all row
-    // interchanges are applied to b before the forward substitution starts
 #pragma unroll
     for (int k = 0; k < N; ++k) {
 #pragma unroll
@@ -351,18 +373,41 @@ template <> struct Stepper<M_DOPRI5> {
 
 #if ODESYS_HAS_JAC
 // ---- Rosenbrock 4(3), six stages (RODAS-type; coefficients proven by oracle/check_ros4_coeffs.py) ---
+// The coefficients live in constant memory: FP64 instructions take a constant-bank operand for free,
+// whereas 64-bit literals cost two UMOV each (14 % of all executed instructions in the first ncu capture).
+namespace ros4c {
+enum { A21, A31, A32, A41, A42, A43, A51, A52, A53, A54, C21, C31, C32, C41, C42, C43, C51, C52, C53, C54,
+       C61, C62, C63, C64, C65, D1, D2, D3, D4, C2X, C3X, C4X, D21, D22, D23, D24, D25, D31, D32, D33, D34, D35,
+       NCOEF };
+}
+__constant__ double kRos4[ros4c::NCOEF] = {
+    0.1544000000000000e+01, 0.9466785280815826e+00, 0.2557011698983284e+00, 0.3314825187068521e+01,
+    0.2896124015972201e+01, 0.9986419139977817e+00, 0.1221224509226641e+01, 0.6019134481288629e+01,
+    0.1253708332932087e+02, -0.6878860361058950e+00,
+    -0.5668800000000000e+01, -0.2430093356833875e+01, -0.2063599157091915e+00, -0.1073529058151375e+00,
+    -0.9594562251023355e+01, -0.2047028614809616e+02, 0.7496443313967647e+01, -0.1024680431464352e+02,
+    -0.3399990352819905e+02, 0.1170890893206160e+02, 0.8083246795921522e+01, -0.7981132988064893e+01,
+    -0.3152159432874371e+02, 0.1631930543123136e+02, -0.6058818238834054e+01,
+    0.2500000000000000e+00, -0.1043000000000000e+00, 0.1035000000000000e+00, -0.3620000000000023e-01,
+    0.386, 0.21, 0.63,
+    0.1012623508344586e+02, -0.7487995877610167e+01, -0.3480091861555747e+02, -0.7992771707568823e+01,
+    0.1025137723295662e+01, -0.6762803392801253e+00, 0.6087714651680015e+01, 0.1643084320892478e+02,
+    0.2476722511418386e+02, -0.6594389125716872e+01};
+#define RC(name) kRos4[ros4c::name]
+
 template <> struct Stepper<M_ROS4> {
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 4;
-    double c3[NY], c4[NY];  // dense output: cont3, cont4 of the last attempt
-    double h_old, err_old;  // predictive (Gustafsson) controller memory
+    double g1[NY], g2[NY], g3[NY], g4[NY], g5[NY];  // stage increments of the last attempt (dense output)
+    double h_old;                                   // predictive (Gustafsson) controller memory
+    float err_old;
     bool first, last_rejected;
 
     __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) {
         first = true;
         last_rejected = false;
         h_old = 0.0;
-        err_old = 1.0;
+        err_old = 1.0f;
         return 0;
     }
     __device__ __forceinline__ void auto_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t,
@@ -373,31 +418,14 @@ template <> struct Stepper<M_ROS4> {
     }
     __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
                                            double h, double *ynew, double &err, Counters &cnt) {
-        constexpr double gam = 0.25;
-        constexpr double a21 = 0.1544000000000000e+01, a31 = 0.9466785280815826e+00, a32 = 0.2557011698983284e+00,
-                         a41 = 0.3314825187068521e+01, a42 = 0.2896124015972201e+01, a43 = 0.9986419139977817e+00,
-                         a51 = 0.1221224509226641e+01, a52 = 0.6019134481288629e+01, a53 = 0.1253708332932087e+02,
-                         a54 = -0.6878860361058950e+00;
-        constexpr double c21 = -0.5668800000000000e+01, c31 = -0.2430093356833875e+01, c32 = -0.2063599157091915e+00,
-                         c41 = -0.1073529058151375e+00, c42 = -0.9594562251023355e+01, c43 = -0.2047028614809616e+02,
-                         c51 = 0.7496443313967647e+01, c52 = -0.1024680431464352e+02, c53 = -0.3399990352819905e+02,
-                         c54 = 0.1170890893206160e+02, c61 = 0.8083246795921522e+01, c62 = -0.7981132988064893e+01,
-                         c63 = -0.3152159432874371e+02, c64 = 0.1631930543123136e+02, c65 = -0.6058818238834054e+01;
-        constexpr double d1 = 0.2500000000000000e+00, d2 = -0.1043000000000000e+00, d3 = 0.1035000000000000e+00,
-                         d4 = -0.3620000000000023e-01;
-        constexpr double c2x = 0.386, c3x = 0.21, c4x = 0.63;
-        constexpr double d21 = 0.1012623508344586e+02, d22 = -0.7487995877610167e+01, d23 = -0.3480091861555747e+02,
-                         d24 = -0.7992771707568823e+01, d25 = 0.1025137723295662e+01, d31 = -0.6762803392801253e+00,
-                         d32 = 0.6087714651680015e+01, d33 = 0.1643084320892478e+02, d34 = 0.2476722511418386e+02,
-                         d35 = -0.6594389125716872e+01;
-        double W[NY * NY], dfdt[NY], f[NY], g1[NY], g2[NY], g3[NY], g4[NY], g5[NY], tmp[NY];
+        double W[NY * NY], dfdt[NY], f[NY], tmp[NY];
         int piv[NY];
         int bad = 0;
         bad |= eval_rhs(sys, a, t, y, f);
         bad |= sys.dense_jac_rmaj(t, y, f, W, NY, dfdt);
         // W = I/(gamma h) - J
-        const double ih = 1.0 / h;
-        const double diag = ih * (1.0 / gam);
+        const double ih = fast_rcp<2>(h);
+        const double diag = 4.0 * ih;  // 1/gamma = 4
 #pragma unroll
         for (int i = 0; i < NY; ++i)
 #pragma unroll
@@ -406,40 +434,44 @@ template <> struct Stepper<M_ROS4> {
         cnt.nlu += 1;
         cnt.nsolve += 6;
 #pragma unroll
-        for (int i = 0; i < NY; ++i) g1[i] = ODESYS_AUTONOMOUS ? f[i] : fma(h * d1, dfdt[i], f[i]);
+        for (int i = 0; i < NY; ++i) g1[i] = ODESYS_AUTONOMOUS ? f[i] : fma(h * RC(D1), dfdt[i], f[i]);
         lu_solve<NY>(W, piv, g1);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = fma(a21, g1[i], y[i]);
-        bad |= eval_rhs(sys, a, t + c2x * h, tmp, f);
+        for (int i = 0; i < NY; ++i) tmp[i] = fma(RC(A21), g1[i], y[i]);
+        bad |= eval_rhs(sys, a, fma(RC(C2X), h, t), tmp, f);
+        const double c21 = RC(C21) * ih;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g2[i] = fma(c21 * ih, g1[i], f[i]);
-            if (!ODESYS_AUTONOMOUS) g2[i] = fma(h * d2, dfdt[i], g2[i]);
+            g2[i] = fma(c21, g1[i], f[i]);
+            if (!ODESYS_AUTONOMOUS) g2[i] = fma(h * RC(D2), dfdt[i], g2[i]);
         }
         lu_solve<NY>(W, piv, g2);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a31 * g1[i] + a32 * g2[i];
-        bad |= eval_rhs(sys, a, t + c3x * h, tmp, f);
+        for (int i = 0; i < NY; ++i) tmp[i] = fma(RC(A32), g2[i], fma(RC(A31), g1[i], y[i]));
+        bad |= eval_rhs(sys, a, fma(RC(C3X), h, t), tmp, f);
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g3[i] = f[i] + ih * (c31 * g1[i] + c32 * g2[i]);
-            if (!ODESYS_AUTONOMOUS) g3[i] = fma(h * d3, dfdt[i], g3[i]);
+            g3[i] = fma(ih, fma(RC(C32), g2[i], RC(C31) * g1[i]), f[i]);
+            if (!ODESYS_AUTONOMOUS) g3[i] = fma(h * RC(D3), dfdt[i], g3[i]);
         }
         lu_solve<NY>(W, piv, g3);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a41 * g1[i] + a42 * g2[i] + a43 * g3[i];
-        bad |= eval_rhs(sys, a, t + c4x * h, tmp, f);
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = fma(RC(A43), g3[i], fma(RC(A42), g2[i], fma(RC(A41), g1[i], y[i])));
+        bad |= eval_rhs(sys, a, fma(RC(C4X), h, t), tmp, f);
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g4[i] = f[i] + ih * (c41 * g1[i] + c42 * g2[i] + c43 * g3[i]);
-            if (!ODESYS_AUTONOMOUS) g4[i] = fma(h * d4, dfdt[i], g4[i]);
+            g4[i] = fma(ih, fma(RC(C43), g3[i], fma(RC(C42), g2[i], RC(C41) * g1[i])), f[i]);
+            if (!ODESYS_AUTONOMOUS) g4[i] = fma(h * RC(D4), dfdt[i], g4[i]);
         }
         lu_solve<NY>(W, piv, g4);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + a51 * g1[i] + a52 * g2[i] + a53 * g3[i] + a54 * g4[i];
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = fma(RC(A54), g4[i], fma(RC(A53), g3[i], fma(RC(A52), g2[i], fma(RC(A51), g1[i], y[i]))));
         bad |= eval_rhs(sys, a, t + h, tmp, f);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) g5[i] = f[i] + ih * (c51 * g1[i] + c52 * g2[i] + c53 * g3[i] + c54 * g4[i]);
+        for (int i = 0; i < NY; ++i)
+            g5[i] = fma(ih, fma(RC(C54), g4[i], fma(RC(C53), g3[i], fma(RC(C52), g2[i], RC(C51) * g1[i]))), f[i]);
         lu_solve<NY>(W, piv, g5);
 #pragma unroll
         for (int i = 0; i < NY; ++i) tmp[i] += g5[i];
@@ -447,59 +479,73 @@ template <> struct Stepper<M_ROS4> {
         double xerr[NY];
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            xerr[i] = f[i] + ih * (c61 * g1[i] + c62 * g2[i] + c63 * g3[i] + c64 * g4[i] + c65 * g5[i]);
+            xerr[i] = fma(ih, fma(RC(C65), g5[i], fma(RC(C64), g4[i], fma(RC(C63), g3[i],
+                                  fma(RC(C62), g2[i], RC(C61) * g1[i])))), f[i]);
         lu_solve<NY>(W, piv, xerr);
         err = 0.0;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
             ynew[i] = tmp[i] + xerr[i];
-            const double sk = tol.atol[i] + tol.rtol * fmax(fabs(y[i]), fabs(ynew[i]));
-            err = fmax(err, fabs(xerr[i]) / sk);
-            c3[i] = d21 * g1[i] + d22 * g2[i] + d23 * g3[i] + d24 * g4[i] + d25 * g5[i];
-            c4[i] = d31 * g1[i] + d32 * g2[i] + d33 * g3[i] + d34 * g4[i] + d35 * g5[i];
+            // the error measure only steers the step size: ~40-bit reciprocal instead of an IEEE division
+            const double sk = fma(tol.rtol, fmax(fabs(y[i]), fabs(ynew[i])), tol.atol[i]) + 1e-300;
+            err = fmax(err, fabs(xerr[i]) * fast_rcp<1>(sk));
         }
         if (!(err <= DBL_MAX)) bad |= 1;
         return bad;
     }
     // odeint rosenbrock4_controller::try_step: fac in [1/6, 5], predictive correction after the
-    // first accepted step, no growth directly after a rejection.
+    // first accepted step, no growth directly after a rejection.  Single precision: the factor only
+    // chooses the next step size.
     __device__ __forceinline__ bool control(double err, double, double &hnext, double h) {
-        constexpr double safe = 0.9, fac1 = 5.0, fac2 = 1.0 / 6.0;
-        double fac = fmax(fac2, fmin(fac1, fast_pow(err, 0.25f) / safe));
-        double hn = h / fac;
+        constexpr float isafe = 1.0f / 0.9f, fac1 = 5.0f, fac2 = 1.0f / 6.0f;
+        const float ef = (float)fmin(fmax(err, 1e-30), 1e30);
+        const float lg = __log2f(ef);
+        float fac = fmaxf(fac2, fminf(fac1, exp2f(0.25f * lg) * isafe));
         if (err <= 1.0) {
             if (!first) {
-                double fp = (h_old / h) * fast_pow(err * err / err_old, 0.25f) / safe;
-                fp = fmax(fac2, fmin(fac1, fp));
-                fac = fmax(fac, fp);
-                hn = h / fac;
+                // (h_old/h) (err^2/err_old)^(1/4) / safe
+                const float ratio = (float)(h_old * fast_rcp<1>(h));
+                float fp = ratio * exp2f(0.25f * (2.0f * lg - __log2f(err_old))) * isafe;
+                fp = fmaxf(fac2, fminf(fac1, fp));
+                fac = fmaxf(fac, fp);
             }
+            double hn = h * (double)__frcp_rn(fac);
             first = false;
             h_old = h;
-            err_old = fmax(0.01, err);
+            err_old = fmaxf(0.01f, ef);
             if (last_rejected) hn = (h >= 0.0) ? fmin(hn, h) : fmax(hn, h);
             last_rejected = false;
             hnext = hn;
             return true;
         }
         last_rejected = true;
-        hnext = hn;
+        hnext = h * (double)__frcp_rn(fac);
         return false;
     }
     __device__ __forceinline__ void accepted(const double *) {}
+    // rosenbrock4_dense_output: the two continuation vectors are linear in the stage increments; they
+    // are formed here (only when an output point falls inside the step) instead of in every attempt.
     __device__ __forceinline__ void dense(double theta, double, const double *yold, const double *ynew, double *out) {
         const double s1 = 1.0 - theta;
 #pragma unroll
-        for (int i = 0; i < NY; ++i) out[i] = yold[i] * s1 + theta * (ynew[i] + s1 * (c3[i] + theta * c4[i]));
+        for (int i = 0; i < NY; ++i) {
+            const double c3 = fma(RC(D25), g5[i], fma(RC(D24), g4[i], fma(RC(D23), g3[i], fma(RC(D22), g2[i], RC(D21) * g1[i]))));
+            const double c4 = fma(RC(D35), g5[i], fma(RC(D34), g4[i], fma(RC(D33), g3[i], fma(RC(D32), g2[i], RC(D31) * g1[i]))));
+            out[i] = yold[i] * s1 + theta * (ynew[i] + s1 * (c3 + theta * c4));
+        }
     }
 };
+#undef RC
 #endif  // ODESYS_HAS_JAC
 
 // ----------------------------------------------------------------------------------------------
 // The persistent kernel.  MODE 0: predefined output points, MODE 1: every accepted step.
 // ----------------------------------------------------------------------------------------------
+#ifndef PYODESYS_MIN_BLOCKS
+#define PYODESYS_MIN_BLOCKS (ODESYS_NY <= 4 ? 4 : 1)
+#endif
 template <int METHOD, int MODE, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) integrate_kernel(const KernelArgs a) {
+__global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS) integrate_kernel(const KernelArgs a) {
     using St = Stepper<METHOD>;
     const unsigned lane = threadIdx.x & 31u;
     const int64_t nthreads = (int64_t)gridDim.x * BLOCK;
@@ -541,7 +587,10 @@ __global__ void __launch_bounds__(BLOCK) integrate_kernel(const KernelArgs a) {
 #pragma unroll
                 for (int i = 0; i < NY; ++i) y[i] = a.y0[s * NY + i];
 #pragma unroll
-                for (int i = 0; i < NP_USED; ++i) sys.m_p[i] = a.params[s * NP_TOT + i];
+                for (int i = 0; i < NP_USED; ++i) {
+                    if (i >= ODESYS_NPARAMS && a.iv_from_y0) sys.m_p[i] = y[i - ODESYS_NPARAMS];
+                    else sys.m_p[i] = a.params[s * a.params_ld + i];
+                }
                 sys.setup();
                 cnt = {0, 0, 0, 0};
                 restarts = a.autorestart;

@@ -129,7 +129,10 @@ int check_common(const Common &q) {
     if (q.natol != 1 && q.natol != NY) return fail("atol needs to be of length 1 or %d", NY);
     if (!q.atol) return fail("atol is NULL");
     if (!q.y0 && q.n > 0) return fail("y0 is NULL");
-    if (!q.params && NP_TOT > 0 && q.n > 0) return fail("params is NULL but the system has %d parameters", NP_TOT);
+    const bool ivy = q.opt && q.opt->iv_from_y0;
+    const int pcols = ivy ? ODESYS_NPARAMS : NP_TOT;
+    if (!q.params && pcols > 0 && q.n > 0) return fail("params is NULL but the system has %d parameters", pcols);
+    if (q.opt && q.opt->params_ld != 0 && q.opt->params_ld < pcols) return fail("params_ld %d < %d columns", q.opt->params_ld, pcols);
     if (!q.status && q.n > 0) return fail("status is NULL");
     if (q.ptr_kind != 0 && q.ptr_kind != 1) return fail("ptr_kind must be 0 (host) or 1 (device)");
     if (!(q.rtol >= 0.0)) return fail("rtol must be non-negative");
@@ -143,6 +146,8 @@ void fill_args(KernelArgs &a, const Common &q) {
     a.rtol = q.rtol;
     a.mxsteps = q.mxsteps;
     a.autorestart = q.autorestart;
+    a.iv_from_y0 = (q.opt && q.opt->iv_from_y0) ? 1 : 0;
+    a.params_ld = (q.opt && q.opt->params_ld > 0) ? q.opt->params_ld : (a.iv_from_y0 ? ODESYS_NPARAMS : NP_TOT);
     a.get_dx_max_factor = q.opt ? q.opt->get_dx_max_factor : 0.0;
     a.error_outside_bounds = q.opt ? q.opt->error_outside_bounds : 0;
 }
@@ -211,6 +216,21 @@ int64_t pyodesys_cuda_query(const char *key) {
 
 int64_t pyodesys_cuda_launch_count(void) { return g_launches.load(); }
 
+void *pyodesys_cuda_host_alloc(size_t bytes) {
+    void *ptr = nullptr;
+    if (bytes == 0) bytes = 8;
+    if (cudaHostAlloc(&ptr, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        fail("cudaHostAlloc(%zu) failed", bytes);
+        return nullptr;
+    }
+    return ptr;
+}
+
+void pyodesys_cuda_host_free(void *ptr) {
+    if (ptr) cudaFreeHost(ptr);
+}
+
 const char *pyodesys_cuda_last_error(void) { return g_err; }
 
 int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const double *y0, const double *xout,
@@ -265,7 +285,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
     const void *p;
     CU_CHECK(cudaEventRecord(c.ev[0], stream));
     if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
-    if (stage(c, B_PARAMS, NP_TOT ? params : nullptr, nn * NP_TOT * 8, &p)) return -1; a.params = (const double *)p;
+    if (stage(c, B_PARAMS, a.params_ld ? params : nullptr, nn * (size_t)a.params_ld * 8, &p)) return -1; a.params = (const double *)p;
     if (stage(c, B_XOUT, xout, (shared_x ? 1 : nn) * nt * 8, &p)) return -1; a.xout = (const double *)p;
     if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;
     if (stage(c, B_DXMIN, dx_min, nn * 8, &p)) return -1; a.dx_min = (const double *)p;
@@ -347,7 +367,7 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
     const void *p;
     CU_CHECK(cudaEventRecord(c.ev[0], stream));
     if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
-    if (stage(c, B_PARAMS, NP_TOT ? params : nullptr, nn * NP_TOT * 8, &p)) return -1; a.params = (const double *)p;
+    if (stage(c, B_PARAMS, a.params_ld ? params : nullptr, nn * (size_t)a.params_ld * 8, &p)) return -1; a.params = (const double *)p;
     if (stage(c, B_XOUT, x0, nn * 8, &p)) return -1; a.x0 = (const double *)p;
     if (stage(c, B_XEND, xend, nn * 8, &p)) return -1; a.xend = (const double *)p;
     if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;

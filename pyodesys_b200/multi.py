@@ -51,12 +51,12 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
     if adaptive:
         steps = int(nsteps) if nsteps else 500
         max_rows = kw.pop('max_rows', None) or steps*(1 + int(kw.get('autorestart', 0))) + 1
-        xyout = np.empty((n, max_rows, 1 + ny))
+        xyout = mod.pinned.empty((n, max_rows, 1 + ny), np.float64)
         nrows = np.empty(n, dtype=np.int32)
     else:
         xout = np.ascontiguousarray(intern_x, dtype=np.float64)
         nt = xout.shape[-1]
-        yout = np.empty((n, nt, ny))
+        yout = mod.pinned.empty((n, nt, ny), np.float64)
         nreached = np.empty(n, dtype=np.int32)
 
     def work(k):
@@ -91,11 +91,12 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
     tmax = timings.max(axis=0)
     roe = kwargs.get('return_on_error', False)
     method = kwargs.get('method') or mod.default_method()
+    iv = y0 if kwargs.get('iv_from_y0', False) else None
     if adaptive:
         return BatchInfo('adaptive', status, None, counters, 0.0, 0.0, _Ragged(xyout, nrows, 0),
-                         _Ragged(xyout, nrows, 1), params, roe, timings=_tdict(tmax), method=method)
+                         _Ragged(xyout, nrows, 1), params, roe, timings=_tdict(tmax), method=method, iv=iv)
     return BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, params, roe,
-                     nt=nt, timings=_tdict(tmax), method=method)
+                     nt=nt, timings=_tdict(tmax), method=method, iv=iv)
 
 
 def gather_to_rank0(local, n_total, dist=None):

@@ -54,7 +54,9 @@ class Options(ctypes.Structure):
                 ('block_size', ctypes.c_int32),
                 ('blocks_per_sm', ctypes.c_int32),
                 ('yout_soa', ctypes.c_int32),
-                ('stream', ctypes.c_void_p)]
+                ('stream', ctypes.c_void_p),
+                ('iv_from_y0', ctypes.c_int32),
+                ('params_ld', ctypes.c_int32)]
 
 
 def cache_dir():
@@ -77,8 +79,9 @@ def nvcc_command(src_dir, out, arch=None):
     arch = arch or os.environ.get('PYODESYS_CUDA_ARCH', 'sm_100a')
     comp = arch.replace('sm_', 'compute_')
     nvcc = os.environ.get('NVCC', shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc')
+    extra = os.environ.get('PYODESYS_CUDA_NVCC_FLAGS', '').split()
     return [nvcc, '-gencode', 'arch=%s,code=%s' % (comp, arch), '-O3', '-lineinfo', '-std=c++17',
-            '--shared', '-Xcompiler', '-fPIC', '-Xptxas', '-v',
+            '--shared', '-Xcompiler', '-fPIC', '-Xptxas', '-v'] + extra + [
             '-I', src_dir, '-I', _csrc, '-I', _include,
             os.path.join(_csrc, 'pyodesys_cuda_shim.cu'), '-o', out]
 
@@ -93,6 +96,62 @@ def _ptr(arr, tp=_d):
     if isinstance(arr, int):
         return ctypes.cast(ctypes.c_void_p(arr), tp)
     return arr.ctypes.data_as(tp)
+
+
+class _PinnedBlock:
+    """ Owner of one page-locked block; hands it back to its pool when the last numpy view dies. """
+
+    def __init__(self, pool, ptr, nbytes):
+        self.pool, self.ptr, self.nbytes = pool, ptr, nbytes
+
+    def __del__(self):
+        try:
+            self.pool._release(self.ptr, self.nbytes)
+        except Exception:  # interpreter shutdown
+            pass
+
+
+class PinnedPool:
+    """ numpy arrays in page-locked host memory (``pyodesys_cuda_host_alloc``), recycled by size.
+
+    Falls back to ordinary numpy memory when pinning fails (e.g. no CUDA device: the integrate call
+    that follows reports the real error).  Small arrays are not worth pinning.
+    """
+    min_bytes = 1 << 16
+    max_cached_bytes = 8 << 30
+
+    def __init__(self, lib):
+        self.lib = lib
+        self.free = {}
+        self.cached = 0
+        self.lock = threading.Lock()
+
+    def empty(self, shape, dtype):
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape, dtype=np.int64))*dtype.itemsize
+        if nbytes < self.min_bytes:
+            return np.empty(shape, dtype=dtype)
+        size = 1 << (nbytes - 1).bit_length() if nbytes < (1 << 26) else -(-nbytes // (1 << 26))*(1 << 26)
+        with self.lock:
+            lst = self.free.get(size)
+            ptr = lst.pop() if lst else None
+            if ptr is not None:
+                self.cached -= size
+        if ptr is None:
+            ptr = self.lib.pyodesys_cuda_host_alloc(size)
+            if not ptr:
+                return np.empty(shape, dtype=dtype)
+        buf = (ctypes.c_char*nbytes).from_address(ptr)
+        buf._owner = _PinnedBlock(self, ptr, size)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def _release(self, ptr, size):
+        with self.lock:
+            if self.cached + size <= self.max_cached_bytes:
+                self.free.setdefault(size, []).append(ptr)
+                self.cached += size
+                return
+        self.lib.pyodesys_cuda_host_free(ptr)
 
 
 class CudaModule:
@@ -125,6 +184,12 @@ class CudaModule:
         lib.pyodesys_cuda_eval.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d, _d]
         lib.pyodesys_cuda_lu_solve.restype = ctypes.c_int
         lib.pyodesys_cuda_lu_solve.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _i32]
+        lib.pyodesys_cuda_host_alloc.restype = ctypes.c_void_p
+        lib.pyodesys_cuda_host_alloc.argtypes = [ctypes.c_size_t]
+        lib.pyodesys_cuda_host_free.restype = None
+        lib.pyodesys_cuda_host_free.argtypes = [ctypes.c_void_p]
+        self.pinned = PinnedPool(lib)
+        self.nparams = int(self.query('nparams'))
         self.ny = int(self.query('ny'))
         self.np_tot = int(self.query('np_tot'))
         self.has_jac = bool(self.query('has_jac'))
@@ -143,7 +208,7 @@ class CudaModule:
         return 'rosenbrock4' if self.has_jac else 'dopri5'  # _odeint_wrapper.pyx:43
 
     # -- argument validation shared by both modes (``_odeint_wrapper.pyx:58-82``) -------------
-    def _prep(self, y0, params, atol, dx0, dx_min, dx_max, method):
+    def _prep(self, y0, params, atol, dx0, dx_min, dx_max, method, iv_from_y0=False):
         y0 = np.ascontiguousarray(y0, dtype=np.float64)
         if y0.ndim != 2 or y0.shape[1] != self.ny:
             raise ValueError("y0 needs to be of shape (N, %d)" % self.ny)
@@ -151,8 +216,9 @@ class CudaModule:
         if np.isnan(y0).any():
             raise ValueError("NaN found in y0")
         params = np.ascontiguousarray(params, dtype=np.float64)
-        if params.ndim != 2 or params.shape != (n, self.np_tot):
-            raise ValueError("params needs to be of shape (N, %d), got %s" % (self.np_tot, params.shape))
+        pcols = self.nparams if iv_from_y0 else self.np_tot
+        if params.ndim != 2 or params.shape != (n, pcols):
+            raise ValueError("params needs to be of shape (N, %d), got %s" % (pcols, params.shape))
         atol = np.ascontiguousarray(np.atleast_1d(atol), dtype=np.float64)
         if atol.size != 1 and atol.size != self.ny:
             raise ValueError("atol needs to be of length 1 or %d" % self.ny)
@@ -181,28 +247,31 @@ class CudaModule:
 
     @staticmethod
     def _options(get_dx_max_factor=0.0, error_outside_bounds=False, xout_shared=False, schedule=0,
-                 blocks_per_sm=0, max_invariant_violation=0.0, **unknown):
+                 blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, **unknown):
         if unknown:
             raise TypeError("Unknown keyword arguments: %s" % ', '.join(sorted(unknown)))
         sched = {'auto': 0, 'static': 1, 'dynamic': 2}.get(schedule, schedule)
         return Options(float(get_dx_max_factor or 0.0), float(max_invariant_violation or 0.0),
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
-                       int(blocks_per_sm), 0, None)
+                       int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0)
 
     def integrate_predefined_arrays(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                     mxsteps=0, method=None, autorestart=0, return_on_error=False,
                                     device=0, out=None, special_settings=None, **kw):
-        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method)
+        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
+                                                                   kw.get('iv_from_y0', False))
         xout = np.ascontiguousarray(xout, dtype=np.float64)
         shared = xout.ndim == 1
         if not shared and xout.shape[0] != n:
             raise ValueError("xout needs to be of shape (N, nt)")
         nt = xout.shape[-1]
         opts = self._options(xout_shared=shared, **kw)
-        yout = np.empty((n, nt, self.ny)) if out is None else out
-        nreached = np.empty(n, dtype=np.int32)
-        status = np.empty(n, dtype=np.int32)
-        counters = np.zeros((NCOUNTERS, n), dtype=np.int32)
+        # outputs live in page-locked memory (D2H at PCIe speed); the blocks return to the pool when the
+        # arrays are garbage collected
+        yout = self.pinned.empty((n, nt, self.ny), np.float64) if out is None else out
+        nreached = self.pinned.empty((n,), np.int32)
+        status = self.pinned.empty((n,), np.int32)
+        counters = self.pinned.empty((NCOUNTERS, n), np.int32)
         timings = np.zeros(NTIMINGS)
         rc = self.lib.pyodesys_cuda_integrate_predefined(
             device, n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size, float(rtol),
@@ -215,7 +284,8 @@ class CudaModule:
     def integrate_adaptive_arrays(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                   mxsteps=0, method=None, autorestart=0, return_on_error=False,
                                   device=0, max_rows=None, special_settings=None, **kw):
-        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method)
+        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
+                                                                   kw.get('iv_from_y0', False))
         x0 = np.ascontiguousarray(x0, dtype=np.float64).reshape(-1)
         xend = np.ascontiguousarray(xend, dtype=np.float64).reshape(-1)
         if x0.size != n or xend.size != n:
@@ -225,10 +295,10 @@ class CudaModule:
             steps = int(mxsteps) if mxsteps else 500
             max_rows = steps*(1 + int(autorestart)) + 1
         opts = self._options(**kw)
-        xyout = np.empty((n, max_rows, 1 + self.ny))
-        nrows = np.empty(n, dtype=np.int32)
-        status = np.empty(n, dtype=np.int32)
-        counters = np.zeros((NCOUNTERS, n), dtype=np.int32)
+        xyout = self.pinned.empty((n, max_rows, 1 + self.ny), np.float64)
+        nrows = self.pinned.empty((n,), np.int32)
+        status = self.pinned.empty((n,), np.int32)
+        counters = self.pinned.empty((NCOUNTERS, n), np.int32)
         timings = np.zeros(NTIMINGS)
         rc = self.lib.pyodesys_cuda_integrate_adaptive(
             device, n, _ptr(y0), _ptr(x0), _ptr(xend), _ptr(params), _ptr(atol), atol.size, float(rtol),
@@ -345,7 +415,8 @@ class NativeCudaCode:
         self.odesys = odesys
         self.gen = _codegen.generate(odesys, namespace_override, namespace_extend)
         tag = hashlib.sha256((self.gen.digest + _csrc_digest() +
-                              os.environ.get('PYODESYS_CUDA_ARCH', 'sm_100a')).encode()).hexdigest()[:16]
+                              os.environ.get('PYODESYS_CUDA_ARCH', 'sm_100a') +
+                              os.environ.get('PYODESYS_CUDA_NVCC_FLAGS', '')).encode()).hexdigest()[:16]
         self.tag = tag
         self.build_dir = os.path.join(cache_dir(), tag)
         self.header = os.path.join(self.build_dir, 'odesys_generated.h')
@@ -397,6 +468,7 @@ class NativeCudaSys(SymbolicSys):
 
     _NativeCode = NativeCudaCode
     _native_name = 'cuda'
+    _append_iv_on_device = True
 
     def __init__(self, *args, **kwargs):
         namespace_override = kwargs.pop('namespace_override', {})
@@ -425,6 +497,7 @@ class NativeCudaSys(SymbolicSys):
             raise ValueError("atol needs to be of length 1 or %d" % self.ny)
         return_on_error = kwargs.get('return_on_error', False)
         devices = kwargs.pop('devices', None)
+        iv = intern_y0 if kwargs.get('iv_from_y0', False) else None
         mod = self._native.mod
         method = kwargs.get('method') or mod.default_method()
         y0 = np.ascontiguousarray(intern_y0, dtype=np.float64)
@@ -440,7 +513,7 @@ class NativeCudaSys(SymbolicSys):
             xs = _Ragged(xyout, nrows, 0)
             ys = _Ragged(xyout, nrows, 1)
             binfo = BatchInfo('adaptive', status, None, counters, 0.0, 0.0, xs, ys, intern_p,
-                              return_on_error, timings=_tdict(timings), method=method)
+                              return_on_error, timings=_tdict(timings), method=method, iv=iv)
         else:
             if intern_x.shape[0] > 1 and intern_x.strides[0] == 0:
                 # one broadcast row (core.to_arrays): ship it once (options.xout_shared)
@@ -450,7 +523,7 @@ class NativeCudaSys(SymbolicSys):
             yout, nreached, status, counters, timings = mod.integrate_predefined_arrays(
                 y0, xout_arg, params, atol, rtol, dx0=first_step, mxsteps=nsteps, **kwargs)
             binfo = BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, intern_p,
-                              return_on_error, nt=intern_x.shape[-1], timings=_tdict(timings), method=method)
+                              return_on_error, nt=intern_x.shape[-1], timings=_tdict(timings), method=method, iv=iv)
         n = len(binfo)
         binfo.time_wall = binfo.timings.get('kernel', 0.0)/max(n, 1)
         binfo.time_cpu = (time.time() - t0)/max(n, 1)
