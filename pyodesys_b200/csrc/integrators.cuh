@@ -27,6 +27,7 @@
 namespace pyodesys_cuda {
 
 using odesys_anyode::OdeSys;
+using odesys_anyode::OdeSysT;
 constexpr int NY = ODESYS_NY;
 constexpr int NP_TOT = ODESYS_NP_TOT;
 constexpr int NP_USED = ODESYS_NP_USED;
@@ -108,7 +109,8 @@ template <int NEWTON> __device__ __forceinline__ double fast_rcp(double x) {
     return r;
 }
 
-__device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs &a, double x, const double *y,
+template <class Sys>
+__device__ __forceinline__ AnyODE::Status eval_rhs(Sys &sys, const KernelArgs &a, double x, const double *y,
                                                    double *f) {
     // Every call counts as one evaluation (the reference's template increments nfev before its
     // bound checks, odesys_anyode_template.cpp:161).  The counter is advanced HERE rather than by the
@@ -128,6 +130,12 @@ __device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs
     return st;
 }
 
+template <int N> struct RegArr {
+    double v[N];
+    __device__ __forceinline__ double &operator[](int i) { return v[i]; }
+    __device__ __forceinline__ const double &operator[](int i) const { return v[i]; }
+};
+
 // In-register LU with partial (row) pivoting, row-major a[N*N]; the reciprocal pivots are kept
 // on the diagonal so the six triangular solves per Rosenbrock step are division free.
 // Same factorisation as AnyODE::getrf_callback (anyode_blasless.hpp:10-60): Doolittle, row
@@ -136,7 +144,7 @@ __device__ __forceinline__ AnyODE::Status eval_rhs(OdeSys &sys, const KernelArgs
 // ny = 3).  Guarding them with a warp vote (skip when no lane swaps - the common case for stiff
 // kinetics) was measured SLOWER on B200 (20.3 -> 21.4..22.5 ms per 1e6 Robertson systems): the
 // branches cost more issue slots and scheduling freedom than the selects they remove.
-template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) {
+template <int N, bool BRANCH_SWAP, class Mat> __device__ __forceinline__ bool lu_factor(Mat &a, int *piv) {
     bool ok = true;
 #pragma unroll
     for (int k = 0; k < N; ++k) {
@@ -151,32 +159,67 @@ template <int N> __device__ __forceinline__ bool lu_factor(double *a, int *piv) 
             }
         }
         piv[k] = p;
+        if (BRANCH_SWAP) {
+            // shared-memory matrix: a real (rare) interchange instead of selects on every element
+            if (p != k) {
 #pragma unroll
-        for (int i = k + 1; i < N; ++i) {
-            const bool sw = (p == i);
+                for (int i = k + 1; i < N; ++i) {
+                    if (p == i) {
 #pragma unroll
-            for (int j = 0; j < N; ++j) {
-                const double u = a[k * N + j], w = a[i * N + j];
-                a[k * N + j] = sw ? w : u;
-                a[i * N + j] = sw ? u : w;
+                        for (int j = 0; j < N; ++j) {
+                            const double u = a[k * N + j];
+                            a[k * N + j] = a[i * N + j];
+                            a[i * N + j] = u;
+                        }
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = k + 1; i < N; ++i) {
+                const bool sw = (p == i);
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const double u = a[k * N + j], w = a[i * N + j];
+                    a[k * N + j] = sw ? w : u;
+                    a[i * N + j] = sw ? u : w;
+                }
             }
         }
         ok = ok && (amax > 0.0) && (amax <= DBL_MAX);
         const double inv = fast_rcp<2>(a[k * N + k]);
         a[k * N + k] = inv;
+        // The pivot row is read once into registers.  Every row below it is staged: all its loads, the
+        // arithmetic, all its stores - and the loads of row i+1 are issued before the stores of row i (the
+        // shared-memory variant runs one warp per scheduler, so the ILP has to come from the code itself;
+        // for the register variant the staging arrays vanish).
+        double prow[N], cur[N], nxt[N];
+#pragma unroll
+        for (int j = k + 1; j < N; ++j) prow[j] = a[k * N + j];
+        if (k + 1 < N) {
+#pragma unroll
+            for (int j = k; j < N; ++j) cur[j] = a[(k + 1) * N + j];
+        }
 #pragma unroll
         for (int i = k + 1; i < N; ++i) {
-            const double l = a[i * N + k] * inv;
+            if (i + 1 < N) {
+#pragma unroll
+                for (int j = k; j < N; ++j) nxt[j] = a[(i + 1) * N + j];
+            }
+            const double l = cur[k] * inv;
             a[i * N + k] = l;
 #pragma unroll
-            for (int j = k + 1; j < N; ++j) a[i * N + j] = fma(-l, a[k * N + j], a[i * N + j]);
+            for (int j = k + 1; j < N; ++j) a[i * N + j] = fma(-l, prow[j], cur[j]);
+#pragma unroll
+            for (int j = k; j < N; ++j) cur[j] = nxt[j];
         }
     }
     return ok;
 }
 
 // Solves L U x = P b in place (anyode_blasless.hpp:63-95).
-template <int N> __device__ __forceinline__ void lu_solve(const double *a, const int *piv, double *b) {
+template <int N, bool BRANCH_SWAP, class Mat>
+__device__ __forceinline__ void lu_solve(const Mat &a, const int *piv, double *b) {
     // the multipliers were swapped together with their rows (LAPACK convention), hence all row
     // interchanges are applied to b before the forward substitution starts
 #pragma unroll
@@ -205,7 +248,8 @@ template <int N> __device__ __forceinline__ void lu_solve(const double *a, const
 
 // Hairer's starting step-size heuristic (dopri5.f / rodas.f ``HINIT``) with the max norm that the
 // controllers below use.  ``f0`` = f(t0, y0).  Costs one rhs evaluation.
-__device__ __forceinline__ double initial_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t0,
+template <class Sys>
+__device__ __forceinline__ double initial_step(Sys &sys, const KernelArgs &a, const Tol &tol, double t0,
                                                const double *y, const double *f0, double span, int order) {
     double d0 = 0.0, d1 = 0.0;
 #pragma unroll
@@ -245,6 +289,7 @@ template <int METHOD> struct Stepper;
 
 // ---- classical RK4, fixed step -----------------------------------------------------------------
 template <> struct Stepper<M_RK4> {
+    typedef OdeSys Sys;
     static constexpr bool kAdaptive = false;
     static constexpr int kOrder = 4;
     __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) { return 0; }
@@ -283,6 +328,7 @@ template <> struct Stepper<M_RK4> {
 
 // ---- Dormand-Prince 5(4) -----------------------------------------------------------------------
 template <> struct Stepper<M_DOPRI5> {
+    typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 5;
     double k1[NY];                                   // f(t, y), FSAL
@@ -395,100 +441,138 @@ __constant__ double kRos4[ros4c::NCOEF] = {
     0.2476722511418386e+02, -0.6594389125716872e+01};
 #define RC(name) kRos4[ros4c::name]
 
-template <> struct Stepper<M_ROS4> {
+// ---- storage: everything in registers (ny <= ~8); larger systems use smem_integrators.cuh / group_integrators.cuh
+struct RegStore {
+    typedef OdeSys Sys;
+    typedef RegArr<NY> Vec;
+    typedef RegArr<NY * NY> Mat;
+    static constexpr bool kBranchSwap = false;
+    Vec g1, g2, g3, g4, g5;
+    __device__ __forceinline__ void attach(double *, Sys &) {}
+    __device__ __forceinline__ Mat matrix() const { return Mat(); }
+};
+// receives J_ij from the generated code and stores W_ij = delta_ij/(gamma h) - J_ij right away
+template <class Mat> struct JacSink {
+    Mat &w;
+    double *dfdt;
+    double diag;
+    __device__ __forceinline__ void setj(int i, int j, double v) { w[i * NY + j] = (i == j ? diag : 0.0) - v; }
+    __device__ __forceinline__ void setdfdt(int i, double v) { dfdt[i] = v; }
+};
+
+template <class Store> struct Ros4Stepper : Store {
+    typedef typename Store::Sys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 4;
-    double g1[NY], g2[NY], g3[NY], g4[NY], g5[NY];  // stage increments of the last attempt (dense output)
+    using Store::g1;
+    using Store::g2;
+    using Store::g3;
+    using Store::g4;
+    using Store::g5;
     double h_old;                                   // predictive (Gustafsson) controller memory
     float err_old;
     bool first, last_rejected;
 
-    __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) {
+    __device__ __forceinline__ int begin(Sys &, const KernelArgs &, const Tol &, double, const double *) {
         first = true;
         last_rejected = false;
         h_old = 0.0;
         err_old = 1.0f;
         return 0;
     }
-    __device__ __forceinline__ void auto_step(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t,
+    __device__ __forceinline__ void auto_step(Sys &sys, const KernelArgs &a, const Tol &tol, double t,
                                               const double *y, double span, double &h) {
         double f0[NY];
         eval_rhs(sys, a, t, y, f0);
         h = initial_step(sys, a, tol, t, y, f0, span, 4) * (span >= 0 ? 1.0 : -1.0);
     }
-    __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
+    __device__ __forceinline__ int attempt(Sys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
                                            double h, double *ynew, double &err, Counters &cnt) {
-        double W[NY * NY], dfdt[NY], f[NY], tmp[NY];
+        typename Store::Mat W = this->matrix();
+        double dfdt[NY], f[NY], tmp[NY];
         int piv[NY];
         int bad = 0;
         bad |= eval_rhs(sys, a, t, y, f);
-        bad |= sys.dense_jac_rmaj(t, y, f, W, NY, dfdt);
-        // W = I/(gamma h) - J
+        // W = I/(gamma h) - J, formed entry by entry as the generated code produces J
         const double ih = fast_rcp<2>(h);
-        const double diag = 4.0 * ih;  // 1/gamma = 4
-#pragma unroll
-        for (int i = 0; i < NY; ++i)
-#pragma unroll
-            for (int j = 0; j < NY; ++j) W[i * NY + j] = (i == j ? diag : 0.0) - W[i * NY + j];
-        if (!lu_factor<NY>(W, piv)) bad |= 1;
+        {
+            JacSink<typename Store::Mat> sink{W, dfdt, 4.0 * ih /* 1/gamma = 4 */};
+            const int njev0 = sys.njev;
+            bad |= sys.dense_jac_sink(t, y, sink);
+            sys.njev = njev0 + 1;
+        }
+        if (!lu_factor<NY, Store::kBranchSwap>(W, piv)) bad |= 1;
         cnt.nlu += 1;
         cnt.nsolve += 6;
+        double b[NY];
 #pragma unroll
-        for (int i = 0; i < NY; ++i) g1[i] = ODESYS_AUTONOMOUS ? f[i] : fma(h * RC(D1), dfdt[i], f[i]);
-        lu_solve<NY>(W, piv, g1);
+        for (int i = 0; i < NY; ++i) b[i] = ODESYS_AUTONOMOUS ? f[i] : fma(h * RC(D1), dfdt[i], f[i]);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = fma(RC(A21), g1[i], y[i]);
+        for (int i = 0; i < NY; ++i) {
+            g1[i] = b[i];
+            tmp[i] = fma(RC(A21), b[i], y[i]);
+        }
         bad |= eval_rhs(sys, a, fma(RC(C2X), h, t), tmp, f);
         const double c21 = RC(C21) * ih;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g2[i] = fma(c21, g1[i], f[i]);
-            if (!ODESYS_AUTONOMOUS) g2[i] = fma(h * RC(D2), dfdt[i], g2[i]);
+            b[i] = fma(c21, g1[i], f[i]);
+            if (!ODESYS_AUTONOMOUS) b[i] = fma(h * RC(D2), dfdt[i], b[i]);
         }
-        lu_solve<NY>(W, piv, g2);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = fma(RC(A32), g2[i], fma(RC(A31), g1[i], y[i]));
+        for (int i = 0; i < NY; ++i) {
+            g2[i] = b[i];
+            tmp[i] = fma(RC(A32), b[i], fma(RC(A31), g1[i], y[i]));
+        }
         bad |= eval_rhs(sys, a, fma(RC(C3X), h, t), tmp, f);
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g3[i] = fma(ih, fma(RC(C32), g2[i], RC(C31) * g1[i]), f[i]);
-            if (!ODESYS_AUTONOMOUS) g3[i] = fma(h * RC(D3), dfdt[i], g3[i]);
+            b[i] = fma(ih, fma(RC(C32), g2[i], RC(C31) * g1[i]), f[i]);
+            if (!ODESYS_AUTONOMOUS) b[i] = fma(h * RC(D3), dfdt[i], b[i]);
         }
-        lu_solve<NY>(W, piv, g3);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
 #pragma unroll
-        for (int i = 0; i < NY; ++i)
-            tmp[i] = fma(RC(A43), g3[i], fma(RC(A42), g2[i], fma(RC(A41), g1[i], y[i])));
+        for (int i = 0; i < NY; ++i) {
+            g3[i] = b[i];
+            tmp[i] = fma(RC(A43), b[i], fma(RC(A42), g2[i], fma(RC(A41), g1[i], y[i])));
+        }
         bad |= eval_rhs(sys, a, fma(RC(C4X), h, t), tmp, f);
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            g4[i] = fma(ih, fma(RC(C43), g3[i], fma(RC(C42), g2[i], RC(C41) * g1[i])), f[i]);
-            if (!ODESYS_AUTONOMOUS) g4[i] = fma(h * RC(D4), dfdt[i], g4[i]);
+            b[i] = fma(ih, fma(RC(C43), g3[i], fma(RC(C42), g2[i], RC(C41) * g1[i])), f[i]);
+            if (!ODESYS_AUTONOMOUS) b[i] = fma(h * RC(D4), dfdt[i], b[i]);
         }
-        lu_solve<NY>(W, piv, g4);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
 #pragma unroll
-        for (int i = 0; i < NY; ++i)
-            tmp[i] = fma(RC(A54), g4[i], fma(RC(A53), g3[i], fma(RC(A52), g2[i], fma(RC(A51), g1[i], y[i]))));
+        for (int i = 0; i < NY; ++i) {
+            g4[i] = b[i];
+            tmp[i] = fma(RC(A54), b[i], fma(RC(A53), g3[i], fma(RC(A52), g2[i], fma(RC(A51), g1[i], y[i]))));
+        }
         bad |= eval_rhs(sys, a, t + h, tmp, f);
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            g5[i] = fma(ih, fma(RC(C54), g4[i], fma(RC(C53), g3[i], fma(RC(C52), g2[i], RC(C51) * g1[i]))), f[i]);
-        lu_solve<NY>(W, piv, g5);
+            b[i] = fma(ih, fma(RC(C54), g4[i], fma(RC(C53), g3[i], fma(RC(C52), g2[i], RC(C51) * g1[i]))), f[i]);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] += g5[i];
+        for (int i = 0; i < NY; ++i) {
+            g5[i] = b[i];
+            tmp[i] += b[i];
+        }
         bad |= eval_rhs(sys, a, t + h, tmp, f);
-        double xerr[NY];
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            xerr[i] = fma(ih, fma(RC(C65), g5[i], fma(RC(C64), g4[i], fma(RC(C63), g3[i],
-                                  fma(RC(C62), g2[i], RC(C61) * g1[i])))), f[i]);
-        lu_solve<NY>(W, piv, xerr);
+            b[i] = fma(ih, fma(RC(C65), g5[i], fma(RC(C64), g4[i], fma(RC(C63), g3[i],
+                               fma(RC(C62), g2[i], RC(C61) * g1[i])))), f[i]);
+        lu_solve<NY, Store::kBranchSwap>(W, piv, b);
         err = 0.0;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            ynew[i] = tmp[i] + xerr[i];
+            ynew[i] = tmp[i] + b[i];
             // the error measure only steers the step size: ~40-bit reciprocal instead of an IEEE division
             const double sk = fma(tol.rtol, fmax(fabs(y[i]), fabs(ynew[i])), tol.atol[i]) + 1e-300;
-            err = fmax(err, fabs(xerr[i]) * fast_rcp<1>(sk));
+            err = fmax(err, fabs(b[i]) * fast_rcp<1>(sk));
         }
         if (!(err <= DBL_MAX)) bad |= 1;
         return bad;
@@ -535,6 +619,7 @@ template <> struct Stepper<M_ROS4> {
         }
     }
 };
+template <> struct Stepper<M_ROS4> : Ros4Stepper<RegStore> {};  // instantiated for ny <= 16 only (shim)
 #undef RC
 #endif  // ODESYS_HAS_JAC
 
@@ -551,7 +636,7 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS) integrate_kernel(c
     const int64_t nthreads = (int64_t)gridDim.x * BLOCK;
     int64_t s = (int64_t)blockIdx.x * BLOCK + threadIdx.x - nthreads;  // static schedule cursor
 
-    OdeSys sys;
+    typename St::Sys sys;
     St st;
     Tol tol;
     tol.rtol = a.rtol;
@@ -823,20 +908,23 @@ __global__ void eval_kernel(int64_t n, const double *x, const double *y, const d
 #endif
 }
 
+#if ODESYS_NY <= 16
 __global__ void lu_kernel(int64_t n, const double *A, const double *b, double *xsol, int32_t *ok) {
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
-    double a[NY * NY], v[NY];
+    RegArr<NY * NY> a;
+    double v[NY];
     int piv[NY];
 #pragma unroll
     for (int i = 0; i < NY * NY; ++i) a[i] = A[s * NY * NY + i];
 #pragma unroll
     for (int i = 0; i < NY; ++i) v[i] = b[s * NY + i];
-    const bool good = lu_factor<NY>(a, piv);
-    lu_solve<NY>(a, piv, v);
+    const bool good = lu_factor<NY, false>(a, piv);
+    lu_solve<NY, false>(a, piv, v);
 #pragma unroll
     for (int i = 0; i < NY; ++i) xsol[s * NY + i] = v[i];
     ok[s] = good ? 1 : 0;
 }
+#endif
 
 }  // namespace pyodesys_cuda

@@ -9,6 +9,16 @@
 #include "odesys_generated.h"
 
 #include "integrators.cuh"
+// Kernel families are only compiled where they can matter (the fully unrolled register code explodes for large ny):
+#define ODESYS_THREAD_ROS4 (ODESYS_HAS_JAC && ODESYS_NY <= 16)
+#define ODESYS_SMEM_KERNEL (ODESYS_HAS_JAC && ODESYS_NY >= 9)
+#define ODESYS_GROUP_KERNEL (ODESYS_HAS_JAC && ODESYS_NY >= 6)
+#if ODESYS_SMEM_KERNEL
+#include "smem_integrators.cuh"
+#endif
+#if ODESYS_GROUP_KERNEL
+#include "group_integrators.cuh"
+#endif
 #include "pyodesys_cuda.h"
 
 #include <atomic>
@@ -95,12 +105,85 @@ template <int METHOD, int MODE> int launch(DevCtx &c, const KernelArgs &a, cudaS
     return 0;
 }
 
-template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cudaStream_t stream, int bps) {
+#if ODESYS_GROUP_KERNEL
+constexpr int kGroup = PYODESYS_GROUP_G;
+template <int MODE> int launch_group(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
+    auto kern = group_ros4_kernel<kGroup, MODE, kBlock>;
+    const size_t smem = (size_t)(kBlock / kGroup) * kGroupSmemDoubles * sizeof(double);
+    if (smem > 48 * 1024) CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kBlock, smem));
+    if (occ < 1) occ = 1;
+    if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
+    int64_t grid = (int64_t)c.sm_count * occ;
+    const int64_t need = (a.n + (kBlock / kGroup) - 1) / (kBlock / kGroup);
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kBlock, smem, stream>>>(a);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+#endif
+
+#if ODESYS_SMEM_KERNEL
+// one system per thread, W / vectors / parameters in shared memory, rolled loops (one warp per block)
+template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
+    auto kern = smem_ros4_kernel<MODE>;
+    const size_t smem = (size_t)kSmemDoublesPerThread * kSB * sizeof(double);
+    if (smem > 227 * 1024) return fail("ny = %d needs %zu bytes of shared memory per warp; use kernel='group'", NY, smem);
+    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kSB, smem));
+    if (occ < 1) occ = 1;
+    if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
+    int64_t grid = (int64_t)c.sm_count * occ;
+    const int64_t need = (a.n + kSB - 1) / kSB;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kSB, smem, stream>>>(a);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+#endif
+
+// Which kernel family integrates this call: 1 = one system per thread in registers, 2 = one system per
+// lane group, 3 = one system per thread with its arrays in shared memory.  Auto rule from measurements on
+// B200 (radiolysis ny = 14: family 1 105 ms, 2 113 ms, 3 198 ms per 1e5 systems; profiles/r1_c4_kernels.md):
+// family 1 while its spills stay moderate (ny <= 16), the lane-group kernel above.
+int pick_kernel(int method, const pyodesys_cuda_options *opt) {
+    const int want = opt ? opt->kernel : 0;
+    if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3) ? -1 : 1;
+#if ODESYS_SMEM_KERNEL
+    if (want == 3) return 3;
+#endif
+#if ODESYS_GROUP_KERNEL
+    if (want == 2) return 2;
+    if (want == 0 && NY > 16) return 2;
+#endif
+    return (want == 0 || want == 1) ? 1 : -1;
+}
+
+template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cudaStream_t stream, int bps,
+                                 const pyodesys_cuda_options *opt) {
+    const int family = pick_kernel(method, opt);
+    if (family < 0)
+        return fail("kernel=%d is not available for this system/method (lane-group kernel: rosenbrock4, Jacobian, ny >= 6; "
+                    "shared-memory thread kernel: rosenbrock4, Jacobian, ny >= 9)", opt ? opt->kernel : 0);
+#if ODESYS_GROUP_KERNEL
+    if (family == 2) return launch_group<MODE>(c, a, stream, bps);
+#endif
+#if ODESYS_SMEM_KERNEL
+    if (family == 3) return launch_smem<MODE>(c, a, stream, bps);
+#endif
     switch (method) {
     case PYODESYS_CUDA_RK4: return launch<M_RK4, MODE>(c, a, stream, bps);
     case PYODESYS_CUDA_DOPRI5: return launch<M_DOPRI5, MODE>(c, a, stream, bps);
-#if ODESYS_HAS_JAC
+#if ODESYS_THREAD_ROS4
     case PYODESYS_CUDA_ROSENBROCK4: return launch<M_ROS4, MODE>(c, a, stream, bps);
+#elif ODESYS_HAS_JAC
+    case PYODESYS_CUDA_ROSENBROCK4: return fail("the register Rosenbrock kernel is limited to ny <= 16; use kernel 0 (auto) or 2");
 #else
     case PYODESYS_CUDA_ROSENBROCK4: return fail("rosenbrock4 needs a Jacobian but the system was generated with jac=False");
 #endif
@@ -194,7 +277,15 @@ int64_t pyodesys_cuda_query(const char *key) {
         {"np_used", NP_USED}, {"npcse", ODESYS_NPCSE}, {"has_jac", ODESYS_HAS_JAC}, {"autonomous", ODESYS_AUTONOMOUS},
         {"nroots", ODESYS_NROOTS}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
         {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
-        {"ncounters", NCOUNT}, {"has_first_step", ODESYS_HAS_FIRST_STEP}, {"has_dx_max", ODESYS_HAS_DX_MAX},
+        {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL},
+        {"has_smem_kernel", ODESYS_SMEM_KERNEL},
+#if ODESYS_SMEM_KERNEL
+        {"smem_doubles_per_thread", kSmemDoublesPerThread},
+#endif
+#if ODESYS_GROUP_KERNEL
+        {"group_size", kGroup}, {"group_smem_doubles", kGroupSmemDoubles},
+#endif
+        {"has_first_step", ODESYS_HAS_FIRST_STEP}, {"has_dx_max", ODESYS_HAS_DX_MAX},
     };
     for (const auto &e : kv)
         if (strcmp(e.k, key) == 0) return e.v;
@@ -205,7 +296,7 @@ int64_t pyodesys_cuda_query(const char *key) {
         cudaError_t e = cudaErrorInvalidValue;
         if (m == PYODESYS_CUDA_RK4) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_RK4, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_RK4, 0, kBlock>);
         if (m == PYODESYS_CUDA_DOPRI5) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 0, kBlock>);
-#if ODESYS_HAS_JAC
+#if ODESYS_THREAD_ROS4
         if (m == PYODESYS_CUDA_ROSENBROCK4) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 0, kBlock>);
 #endif
         if (e != cudaSuccess) { cudaGetLastError(); return -1; }
@@ -271,7 +362,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         a.yout = yout; a.nreached = nreached; a.status = status; a.counters = counters;
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));
-        if (dispatch<0>(c, a, method, stream, bps)) return -1;
+        if (dispatch<0>(c, a, method, stream, bps, opt)) return -1;
         CU_CHECK(cudaEventRecord(c.ev[1], stream));
         CU_CHECK(cudaStreamSynchronize(stream));
         float ms = 0;
@@ -300,7 +391,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
     }
     if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
     CU_CHECK(cudaEventRecord(c.ev[1], stream));
-    if (dispatch<0>(c, a, method, stream, bps)) return -1;
+    if (dispatch<0>(c, a, method, stream, bps, opt)) return -1;
     CU_CHECK(cudaEventRecord(c.ev[2], stream));
     CU_CHECK(cudaMemcpyAsync(yout, a.yout, nn * nt * NY * 8, cudaMemcpyDeviceToHost, stream));
     CU_CHECK(cudaMemcpyAsync(nreached, a.nreached, nn * 4, cudaMemcpyDeviceToHost, stream));
@@ -355,7 +446,7 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         a.xyout = xyout; a.nrows = nrows; a.status = status; a.counters = counters;
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));
-        if (dispatch<1>(c, a, method, stream, bps)) return -1;
+        if (dispatch<1>(c, a, method, stream, bps, opt)) return -1;
         CU_CHECK(cudaEventRecord(c.ev[1], stream));
         CU_CHECK(cudaStreamSynchronize(stream));
         float ms = 0;
@@ -383,7 +474,7 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
     }
     if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
     CU_CHECK(cudaEventRecord(c.ev[1], stream));
-    if (dispatch<1>(c, a, method, stream, bps)) return -1;
+    if (dispatch<1>(c, a, method, stream, bps, opt)) return -1;
     CU_CHECK(cudaEventRecord(c.ev[2], stream));
     CU_CHECK(cudaMemcpyAsync(xyout, a.xyout, out_bytes, cudaMemcpyDeviceToHost, stream));
     CU_CHECK(cudaMemcpyAsync(nrows, a.nrows, nn * 4, cudaMemcpyDeviceToHost, stream));
@@ -429,6 +520,9 @@ int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, 
 
 int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok) {
     if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+#if ODESYS_NY > 16
+    return fail("the register LU hook is limited to ny <= 16");
+#else
     if (n <= 0) return 0;
     CU_CHECK(cudaSetDevice(device));
     const size_t nn = (size_t)n;
@@ -447,6 +541,7 @@ int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double 
     CU_CHECK(cudaMemcpy(ok, dok, nn * 4, cudaMemcpyDeviceToHost));
     cudaFree(dA); cudaFree(db); cudaFree(dx); cudaFree(dok);
     return 0;
+#endif
 }
 
 }  // extern "C"

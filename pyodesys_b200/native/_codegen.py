@@ -108,6 +108,78 @@ def _body(cses, assigns, ret='return AnyODE::Status::success;', indent='        
     return '\n'.join(lines)
 
 
+def _lazy_lines(cses, outs, cc, indent='        '):
+    """ Statements for ``outs`` = [(format-with-%s, expr)] where every CSE temporary is defined right before
+    the first output that needs it: short live ranges instead of sympy's "all temporaries first" order
+    (101 temporaries up front cost ~200 registers for the radiolysis Jacobian). """
+    defs = {sy: e for sy, e in cses}
+    order = [sy for sy, _e in cses]
+    pos = {sy: k for k, sy in enumerate(order)}
+    done = set()
+    lines = []
+
+    def need(expr):
+        todo = sorted((sy for sy in expr.free_symbols if sy in defs and sy not in done), key=pos.get)
+        for sy in todo:
+            if sy in done:
+                continue
+            need(defs[sy])
+            done.add(sy)
+            lines.append('%sconst double %s = %s;' % (indent, sy.name, cc(defs[sy])))
+
+    for fmt, expr in outs:
+        expr = sympy.sympify(expr)
+        need(expr)
+        lines.append(indent + fmt % cc(expr))
+    return lines
+
+
+def _accumulate_lines(cses, exprs, cc, prefix='acc', indent='        '):
+    """ Sum-of-rates form: every output is an accumulator; a temporary that enters outputs as a plain
+    additive term (numeric coefficient times the temporary - a reaction rate in mass-action kinetics) is
+    added to them right after its definition and can die immediately.  Returns (lines, accumulator names). """
+    temps = [sy for sy, _e in cses]
+    tempset = set(temps)
+    uses = {sy: [] for sy in temps}
+    leftovers = []
+    for i, expr in enumerate(exprs):
+        expr = sympy.sympify(expr)
+        rest_terms = []
+        for term in sympy.Add.make_args(expr):
+            c, rest = term.as_coeff_Mul()
+            if rest in tempset and c.is_number:
+                uses[rest].append((i, c))
+            else:
+                rest_terms.append(term)
+        leftovers.append(rest_terms)
+    lines = []
+    started = [False]*len(exprs)
+
+    def add(i, text, negative=False):
+        # the first contribution declares the accumulator (no ``0.0 +`` left for the FP64 pipe)
+        if not started[i]:
+            started[i] = True
+            lines.append('%sdouble %s%d = %s%s;' % (indent, prefix, i, '-' if negative else '', text))
+        else:
+            lines.append('%s%s%d %s= %s;' % (indent, prefix, i, '-' if negative else '+', text))
+
+    for sy, e in cses:
+        lines.append('%sconst double %s = %s;' % (indent, sy.name, cc(e)))
+        for i, c in uses[sy]:
+            if c == 1:
+                add(i, sy.name)
+            elif c == -1:
+                add(i, sy.name, negative=True)
+            else:
+                add(i, '(%s)' % cc(c*sy))
+    for i, terms in enumerate(leftovers):
+        if terms:
+            add(i, '(%s)' % cc(sympy.Add(*terms)))
+        elif not started[i]:
+            add(i, '0.0')
+    return lines, ['%s%d' % (prefix, i) for i in range(len(exprs))]
+
+
 def generate(odesys, namespace_override=None, namespace_extend=None):
     """ Build the header for ``odesys`` (a :class:`pyodesys_b200.symbolic.SymbolicSys`). """
     ns_over = dict(namespace_override or {})
@@ -212,22 +284,50 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     if 'p_rhs' in ns_over:
         rhs_body = ns_over['p_rhs']
     else:
-        rhs_body = _body([(s.name, cc(e)) for s, e in rhs_cses],
-                         [('f[%d]' % i, cc(e)) for i, e in enumerate(rhs_exprs)],
-                         ret='this->nfev++;\n        return AnyODE::Status::success;')
+        acc_lines, acc_names = _accumulate_lines(rhs_cses, rhs_exprs, cc)
+        rhs_body = '\n'.join(acc_lines + ['        f[%d] = %s;' % (i, nm) for i, nm in enumerate(acc_names)] +
+                             ['        this->nfev++;', '        return AnyODE::Status::success;'])
 
     if 'p_jac' in ns_over:
         jac_body = ns_over['p_jac']
     elif nj:
-        assigns = [('jac[ldim*%d + %d]' % (idx // ny, idx % ny), cc(e))
-                   for idx, e in enumerate(jac_exprs[:ny*ny])]
-        dfdt_assigns = '\n'.join('            dfdt[%d] = %s;' % (i, cc(e))
-                                 for i, e in enumerate(jac_exprs[ny*ny:]))
-        jac_body = _body([(s.name, cc(e)) for s, e in jac_cses], assigns, ret=None)
-        jac_body += '\n        if (dfdt) {\n%s\n        }\n' % dfdt_assigns
+        dfdt_nz = [(i, e) for i, e in enumerate(jac_exprs[ny*ny:]) if e != 0]
+        outs = [('jac[ldim*%d + %d] = %%s;' % (idx // ny, idx % ny), e) for idx, e in enumerate(jac_exprs[:ny*ny])]
+        outs += [('if (dfdt) dfdt[%d] = %%s;' % i, e) for i, e in dfdt_nz]
+        jac_body = '\n'.join(_lazy_lines(jac_cses, outs, cc))
+        jac_body += '\n        if (dfdt) {\n%s\n        }\n' % '\n'.join(
+            '            dfdt[%d] = 0.0;' % i for i, e in enumerate(jac_exprs[ny*ny:]) if e == 0)
         jac_body += '        this->njev++;\n        return AnyODE::Status::success;'
     else:
         jac_body = '        return AnyODE::Status::unrecoverable_error;'
+
+    # "sink" variants for the group-per-system kernels: every lane of a group evaluates the expressions
+    # and the sink keeps the rows that lane owns (``s.set(i, v)`` with literal i, resolved at compile time)
+    if 'p_rhs' in ns_over:
+        rhs_sink_body = '''        double f_all[ODESYS_NY];
+        const AnyODE::Status st = rhs(x, y, f_all);
+#pragma unroll
+        for (int i = 0; i < ODESYS_NY; ++i) s.set(i, f_all[i]);
+        return st;'''
+    else:
+        acc_lines, acc_names = _accumulate_lines(rhs_cses, rhs_exprs, cc)
+        rhs_sink_body = '\n'.join(acc_lines + ['        s.set(%d, %s);' % (i, nm) for i, nm in enumerate(acc_names)] +
+                                  ['        this->nfev++;', '        return AnyODE::Status::success;'])
+    if 'p_jac' in ns_over or not nj:
+        jac_sink_body = '''        double j_all[ODESYS_NY*ODESYS_NY], d_all[ODESYS_NY];
+        const AnyODE::Status st = dense_jac_rmaj(x, y, nullptr, j_all, ODESYS_NY, d_all);
+#pragma unroll
+        for (int i = 0; i < ODESYS_NY; ++i) {
+#pragma unroll
+            for (int j = 0; j < ODESYS_NY; ++j) s.setj(i, j, j_all[i*ODESYS_NY + j]);
+            s.setdfdt(i, d_all[i]);
+        }
+        return st;'''
+    else:
+        outs = [('s.setj(%d, %d, %%s);' % (idx // ny, idx % ny), e) for idx, e in enumerate(jac_exprs[:ny*ny])]
+        outs += [('s.setdfdt(%d, %%s);' % i, e) for i, e in enumerate(jac_exprs[ny*ny:])]
+        jac_sink_body = '\n'.join(_lazy_lines(jac_cses, outs, cc))
+        jac_sink_body += '\n        this->njev++;\n        return AnyODE::Status::success;'
 
     if 'p_first_step' in ns_over:
         fs_body = '        ' + ns_over['p_first_step']
@@ -274,19 +374,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         ('ODESYS_HAS_BOUNDS', int(lb is not None or ub is not None)),
         ('ODESYS_NONNEGATIVE', int(bool(getattr(odesys, '_nonnegative', False)))),
     ]
-    text = '''// -*- mode: read-only -*-
-// Generated by pyodesys_b200.native._codegen (CUDA counterpart of
-// pyodesys/native/sources/odesys_anyode_template.cpp).  Do not edit.
-#pragma once
-%(macros)s
-#include "odesys_prelude.h"
-%(includes)s
-%(anon)s
-
-namespace odesys_anyode {
-struct OdeSys {
-    double m_p[ODESYS_NP_TOT > 0 ? ODESYS_NP_TOT : 1];
-    double m_p_cse[ODESYS_NPCSE > 0 ? ODESYS_NPCSE : 1];
+    struct_body = '''
     int nfev, njev;
 
     // template:163-190 - true when a lower/upper bound is violated
@@ -313,6 +401,15 @@ struct OdeSys {
         AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(fy); AnyODE::ignore(ldim);
 %(jac)s
     }
+    // same expressions, results handed to a sink: s.set(i, f_i) / s.setj(i, j, J_ij) / s.setdfdt(i, .)
+    template <class Sink> ODESYS_FN AnyODE::Status rhs_sink(double x, const double * const y, Sink &s) {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(rhs_sink)s
+    }
+    template <class Sink> ODESYS_FN AnyODE::Status dense_jac_sink(double x, const double * const y, Sink &s) {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(jac_sink)s
+    }
     // template:295-309
     ODESYS_FN double get_dx0(double x, const double * const y) {
         AnyODE::ignore(x); AnyODE::ignore(y);
@@ -328,14 +425,35 @@ struct OdeSys {
         AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(out);
 %(roots)s
     }
-};
+''' % dict(bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
+           rhs_sink=rhs_sink_body, jac_sink=jac_sink_body, fs=fs_body, dxmax=dxmax_body, roots=roots_body)
+
+    text = '''// -*- mode: read-only -*-
+// Generated by pyodesys_b200.native._codegen (CUDA counterpart of
+// pyodesys/native/sources/odesys_anyode_template.cpp).  Do not edit.
+#pragma once
+%(macros)s
+#include "odesys_prelude.h"
+%(includes)s
+%(anon)s
+
+namespace odesys_anyode {
+// parameters held by value (registers): one system per thread, CPU oracle
+struct OdeSys {
+    double m_p[ODESYS_NP_TOT > 0 ? ODESYS_NP_TOT : 1];
+    double m_p_cse[ODESYS_NPCSE > 0 ? ODESYS_NPCSE : 1];
+%(body)s};
+// parameters behind an array-like handle (shared memory): ``double *`` for one system per lane group,
+// a strided view (element i of thread t at base[i*BLOCK + t]) for the shared-memory thread kernels
+template <class Arr> struct OdeSysT {
+    Arr m_p;
+    Arr m_p_cse;
+%(body)s};
+typedef OdeSysT<double *> OdeSysRef;
 }  // namespace odesys_anyode
 ''' % dict(
         macros='\n'.join('#define %s %d' % kv for kv in macros),
-        includes=includes, anon=anon,
-        bounds=bounds_body,
-        setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body, fs=fs_body,
-        dxmax=dxmax_body, roots=roots_body)
+        includes=includes, anon=anon, body=struct_body)
 
     return GeneratedCode(text, ny, nparams, np_tot, np_used, npcse, flops,
                          has_jac=bool(nj) or 'p_jac' in ns_over,

@@ -56,7 +56,9 @@ class Options(ctypes.Structure):
                 ('yout_soa', ctypes.c_int32),
                 ('stream', ctypes.c_void_p),
                 ('iv_from_y0', ctypes.c_int32),
-                ('params_ld', ctypes.c_int32)]
+                ('params_ld', ctypes.c_int32),
+                ('kernel', ctypes.c_int32),
+                ('reserved', ctypes.c_int32)]
 
 
 def cache_dir():
@@ -65,7 +67,7 @@ def cache_dir():
 
 def _csrc_digest():
     h = hashlib.sha256()
-    for fn in ('integrators.cuh', 'warp_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
+    for fn in ('integrators.cuh', 'group_integrators.cuh', 'smem_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
         path = os.path.join(_csrc, fn)
         if os.path.exists(path):
             with open(path, 'rb') as fh:
@@ -247,13 +249,14 @@ class CudaModule:
 
     @staticmethod
     def _options(get_dx_max_factor=0.0, error_outside_bounds=False, xout_shared=False, schedule=0,
-                 blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, **unknown):
+                 blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, kernel=0, **unknown):
         if unknown:
             raise TypeError("Unknown keyword arguments: %s" % ', '.join(sorted(unknown)))
         sched = {'auto': 0, 'static': 1, 'dynamic': 2}.get(schedule, schedule)
         return Options(float(get_dx_max_factor or 0.0), float(max_invariant_violation or 0.0),
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
-                       int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0)
+                       int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
+                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0)
 
     def integrate_predefined_arrays(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                     mxsteps=0, method=None, autorestart=0, return_on_error=False,

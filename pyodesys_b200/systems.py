@@ -148,6 +148,40 @@ def radiolysis(**kw):
     return _get(('radiolysis', tuple(sorted(kw.items()))), mk)
 
 
+def radiolysis2(**kw):
+    """ C4(ii), SURVEY.md 8d: 28 species = two copies of the reference network coupled by four first-order
+    exchange reactions (H2O2, O2, H2, OH- of copy one <-> copy two); 112 rate parameters.  Exercises ny > 16. """
+    def mk():
+        d = load_radiolysis()
+        ns, nr = len(d['names']), len(d['reac'])
+        z = [0]*ns
+        reac = [r + z for r in d['reac']] + [z + r for r in d['reac']]
+        prod = [r + z for r in d['prod']] + [z + r for r in d['prod']]
+        inact = [r + z for r in d['inact_reac']] + [z + r for r in d['inact_reac']]
+        for name in ('H2O2', 'O2', 'H2', 'OH-'):
+            i = d['names'].index(name)
+            for a, b in ((i, ns + i), (ns + i, i)):
+                rr, pp = [0]*(2*ns), [0]*(2*ns)
+                rr[a], pp[b] = 1, 1
+                reac.append(rr)
+                prod.append(pp)
+                inact.append([0]*(2*ns))
+        names = tuple(d['names']) + tuple(n + "'" for n in d['names'])
+        return NativeCudaSys.from_callback(mass_action_rhs(reac, prod, inact), 2*ns, len(reac), names=names, **kw)
+    return _get(('radiolysis2', tuple(sorted(kw.items()))), mk)
+
+
+def batch_radiolysis2(n=10**4, seed=5, tend=1e3):
+    b1 = batch_radiolysis(n=n, seed=seed, tend=tend)
+    b2 = batch_radiolysis(n=n, seed=seed + 1000, tend=tend)
+    rng = np.random.default_rng(seed + 7)
+    kx = 1e-2*10.0**rng.uniform(-1, 1, size=(n, 8))
+    out = dict(b1)
+    out['y0'] = np.concatenate((b1['y0'], b2['y0']), axis=1)
+    out['params'] = np.concatenate((b1['params'], b2['params'], kx), axis=1)
+    return out
+
+
 # --- synthetic batches (SURVEY.md §8d) -----------------------------------------------------------------------
 def batch_vdp(n=10**4, seed=1):
     """ C1: mu=1, y0 ~ U([-3,3]^2), t in [0,10] """

@@ -386,3 +386,74 @@ def test_edge_cases(cuda_device):
     r1 = rob.integrate(b['x'], b['y0'], b['params'], schedule='static', **kw)
     r2 = rob.integrate(b['x'], b['y0'], b['params'], schedule='dynamic', **kw)
     assert np.array_equal(r1.yout, r2.yout) and np.array_equal(r1.info.counters, r2.info.counters)
+
+
+# ---- larger systems: the three Rosenbrock kernel families ------------------------------------------------------------
+@pytest.mark.parametrize('kernel', ['thread', 'group', 'thread_smem'])
+def test_radiolysis_kernel_families_vs_oracle(cuda_device, kernel):
+    """ C4 (radiolysis network of examples/_chem_kinet.py:57-85, ny=14, 54 rate parameters): register, lane-group and
+    shared-memory kernels against the CPU oracle on the same seeded batch, dense output included """
+    rad = systems.radiolysis()
+    assert rad.ny == 14 and len(rad.params) == 54
+    orc = build_oracle(rad._native)
+    n = 777
+    b = systems.batch_radiolysis(n=n, seed=4)
+    xo = np.array([0.0, 1e-3, 1.0, 40.0, 1e3])
+    res = rad.integrate(xo, b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                        method='rosenbrock4', kernel=kernel)
+    assert (res.info.status == 0).all() and (res.info.nreached == xo.size).all()
+    y_cpu, nr, st, cn = orc.integrate_predefined(b['y0'], xo, full_params(b['y0'], b['params']), b['atol'], b['rtol'],
+                                                 mxsteps=b['nsteps'], method='rosenbrock4')
+    assert (st == 0).all()
+    assert within(res.yout, y_cpu, b['rtol'], b['atol']).all()
+    assert abs(int(res.info.counters[0].sum()) - int(cn[0].sum())) <= 0.02*cn[0].sum()
+    # adaptive mode: every accepted step, last row = final state of the predefined run
+    m = 40
+    ra = rad.integrate([(0.0, 1e3)]*m, b['y0'][:m], b['params'][:m], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                       method='rosenbrock4', kernel=kernel)
+    for i in range(0, m, 7):
+        assert ra[i].xout[0] == 0.0 and ra[i].xout[-1] == 1e3 and ra[i].info['success']
+        assert ra[i].xout.size == ra[i].info['n_steps'] - ra[i].info['n_err_test_fails'] + 1
+        assert within(ra[i].yout[-1], y_cpu[i, -1], b['rtol'], b['atol']).all()
+
+
+def test_lane_group_kernel_small_system_and_failures(cuda_device):
+    """ ny=6 decay chain on 4-lane groups (two rows per lane, padding rows): analytic Bateman solution, and the
+    per-system failure semantics of the group kernel """
+    ch = tsys.lu6()
+    k = np.array([7.0, 5e3, 3.0, 2e5, 1.0])
+    y0 = np.array([1.0, 0, 0, 0, 0, 0])
+    xo = np.linspace(0, 2, 6)
+    n = 37
+    scale = np.linspace(0.5, 2.0, n)[:, None]
+    res = ch.integrate(xo, np.tile(y0, (n, 1)), k*scale, atol=1e-12, rtol=1e-10, nsteps=20000, method='rosenbrock4',
+                       kernel='group')
+    thr = ch.integrate(xo, np.tile(y0, (n, 1)), k*scale, atol=1e-12, rtol=1e-10, nsteps=20000, method='rosenbrock4',
+                       kernel='thread')
+    for i in (0, 11, 36):
+        ref = bateman_full(y0, list(k*scale[i, 0]) + [0], xo)
+        assert np.allclose(res.yout[i], ref, rtol=1e-7, atol=1e-10)
+        assert within(res.yout[i], thr.yout[i], 1e-10, 1e-12, factor=100).all()
+    assert np.abs(res.yout.sum(axis=2) - 1).max() < 1e-9
+    r = ch.integrate(xo, [y0, y0], [k, k], atol=1e-12, rtol=1e-10, nsteps=3, method='rosenbrock4', kernel='group',
+                     return_on_error=True)
+    assert (r.info.status == 1).all() and (r.info.nreached == 1).all() and np.isnan(r.yout[:, 1:]).all()
+    with pytest.raises(RuntimeError, match="not available"):
+        systems.robertson().integrate([0, 1], [1, 0, 0], [0.04, 1e4, 3e7], kernel='group', force_predefined=True)
+
+
+def test_coupled_network_ny28_auto_selects_group_kernel(cuda_device):
+    """ C4(ii): 28 species (two coupled copies of the reference network), 32-lane groups, vs the CPU oracle """
+    net = systems.radiolysis2()
+    assert net.ny == 28
+    orc = build_oracle(net._native)
+    n = 300
+    b = systems.batch_radiolysis2(n=n)
+    res = net.integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                        method='rosenbrock4', force_predefined=True)
+    assert (res.info.status == 0).all()
+    y_cpu, nr, st, cn = orc.integrate_predefined(b['y0'], np.array(b['x']), full_params(b['y0'], b['params']),
+                                                 b['atol'], b['rtol'], mxsteps=b['nsteps'], method='rosenbrock4')
+    assert within(res.yout, y_cpu, b['rtol'], b['atol']).all()
+    with pytest.raises(RuntimeError, match="ny <= 16"):
+        net.integrate(b['x'], b['y0'][:2], b['params'][:2], kernel='thread', force_predefined=True, method='rosenbrock4')
