@@ -1,0 +1,219 @@
+# -*- coding: utf-8 -*-
+"""
+CPU tests (``-m "not gpu"``) of the host side: code generation, argument shaping, the C-ABI library (loads and
+exports every symbol ``include/pyodesys_cuda.h`` declares - no compute calls without a GPU), sharding and the
+world_size-2 gloo gather.  The reference behaviours they mirror are cited per test.
+"""
+import ctypes
+import os
+import re
+import socket
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+
+from pyodesys_b200 import systems, native_sys
+from pyodesys_b200.core import ODESys, BatchInfo, BatchResult
+from pyodesys_b200.multi import shard_range
+from pyodesys_b200.native import _codegen
+
+_root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    with open(os.path.join(_root, 'include', 'pyodesys_cuda.h')) as fh:
+        text = fh.read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(pyodesys_cuda_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    names = _declared_symbols()
+    assert {'pyodesys_cuda_integrate_predefined', 'pyodesys_cuda_integrate_adaptive', 'pyodesys_cuda_info',
+            'pyodesys_cuda_query', 'pyodesys_cuda_last_error', 'pyodesys_cuda_eval', 'pyodesys_cuda_lu_solve',
+            'pyodesys_cuda_launch_count', 'pyodesys_cuda_host_alloc', 'pyodesys_cuda_host_free'} <= set(names)
+    for sysobj in (systems.robertson(), systems.vdp(), systems.radiolysis()):
+        lib = ctypes.CDLL(sysobj._native.so_file)
+        for nm in names:
+            assert hasattr(lib, nm), nm
+        lib.pyodesys_cuda_query.restype = ctypes.c_int64
+        lib.pyodesys_cuda_query.argtypes = [ctypes.c_char_p]
+        assert lib.pyodesys_cuda_query(b'abi_version') == 2
+        assert lib.pyodesys_cuda_query(b'ny') == sysobj.ny
+        assert lib.pyodesys_cuda_query(b'np_tot') == len(sysobj.params) + sysobj.ny  # append_iv, core.py:410-411
+        assert lib.pyodesys_cuda_query(b'no such key') == -1
+        ny, npt = ctypes.c_int(), ctypes.c_int()
+        assert lib.pyodesys_cuda_info(ctypes.byref(ny), ctypes.byref(npt), None, None, None) == 0
+        assert (ny.value, npt.value) == (sysobj.ny, len(sysobj.params) + sysobj.ny)
+    lib = ctypes.CDLL(systems.radiolysis()._native.so_file)
+    lib.pyodesys_cuda_query.restype = ctypes.c_int64
+    assert lib.pyodesys_cuda_query(b'has_group_kernel') == 1 and lib.pyodesys_cuda_query(b'group_size') == 8
+
+
+def test_product_path_has_no_cpu_fallback_and_never_imports_the_oracle():
+    """ without a CUDA device the integrate call must fail loudly; the package must not reference oracle/ """
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(RuntimeError, match="pyodesys_cuda"):
+        systems.decay().integrate([0, 1], [1.0, 0.0], [1.0])
+    pkg = os.path.join(_root, 'pyodesys_b200')
+    for dirpath, _d, files in os.walk(pkg):
+        if '_build' in dirpath:
+            continue
+        for fn in files:
+            if fn.endswith(('.py', '.cu', '.cuh', '.h')):
+                with open(os.path.join(dirpath, fn)) as fh:
+                    src = fh.read()
+                assert not re.search(r'^\s*(from|import)\s+oracle\b', src, flags=re.M), fn
+                assert 'liboracle' not in src, fn
+
+
+def test_native_sys_registry_and_constructors():
+    """ ``native_sys`` (pyodesys/native/__init__.py:18-22) gains 'cuda'; from_callback / from_other as symbolic.py:384-508 """
+    cls = native_sys['cuda']
+    a = cls.from_callback(systems.vdp_f, 2, 1, compile=False)
+    b = cls.from_other(a, compile=False)
+    assert a.ny == b.ny == 2 and a._native.gen.digest == b._native.gen.digest
+    assert a.append_iv and a._native.gen.np_tot == 3
+    with pytest.raises(ValueError, match="incompatible kwargs integrator"):
+        a.integrate([0, 1], [1, 0], [1.0], integrator='cvode')
+
+
+def test_codegen_two_level_cse_and_flop_counts():
+    """ ``_NativeCodeBase.variables`` (native/_base.py:126-281): parameter-only CSE goes to m_p_cse and is evaluated
+    once per system (template:104-110); PYODESYS_NATIVE_CSE=0 disables CSE (_base.py:175-179) """
+    def f(x, y, p, be):
+        k = be.exp(p[0])/(1 + p[1]**2)
+        return [-k*y[0], k*y[0] - p[1]*y[1]]
+    s = native_sys['cuda'].from_callback(f, 2, 2, compile=False)
+    gen = s._native.gen
+    assert gen.npcse >= 1 and 'm_p_cse[0] =' in gen.text and 'exp(' in gen.text.split('ODESYS_FN void setup()')[1].split('}')[0]
+    rhs_body = gen.text.split('ODESYS_FN AnyODE::Status rhs(')[1].split('this->nfev++')[0]
+    assert 'exp(' not in rhs_body  # hoisted out of the per-step code
+    assert gen.flops['rhs'] > 0 and gen.flops['jac'] > 0 and gen.has_jac and gen.autonomous
+    os.environ['PYODESYS_NATIVE_CSE'] = '0'
+    try:
+        s0 = native_sys['cuda'].from_callback(f, 2, 2, compile=False)
+        assert s0._native.gen.npcse == 0 and s0._native.gen.digest != gen.digest
+    finally:
+        del os.environ['PYODESYS_NATIVE_CSE']
+    rob = systems.robertson(compile=False)._native.gen
+    assert (rob.ny, rob.nparams, rob.np_tot, rob.np_used, rob.jac_nnz) == (3, 3, 6, 3, 7)
+    with pytest.raises(NotImplementedError):  # _base.py:128-129
+        s.band = (1, 1)
+        _codegen.generate(s)
+
+
+def test_generated_header_compiles_as_plain_cxx_and_matches_sympy():
+    """ the same generated text feeds the CUDA kernels and the oracle; checked here against lambdified sympy """
+    from oracle import build_oracle
+    rad = systems.radiolysis(compile=False)
+    orc = build_oracle(rad._native)
+    rng = np.random.default_rng(0)
+    y = rng.uniform(0.1, 2, size=(5, 14))
+    p = rng.uniform(0.1, 2, size=(5, 54))
+    pf = np.concatenate((p, y), axis=1)
+    f, J, dfdt = orc.eval_rhs_jac(0.0, y, pf)
+    assert np.allclose(f, rad.f_numeric(0.0, y, pf), rtol=1e-12, atol=1e-12)
+    assert np.allclose(J, rad.j_numeric(0.0, y, pf), rtol=1e-12, atol=1e-12)
+    assert (dfdt == 0).all()
+
+
+def test_to_arrays_broadcasting_table():
+    """ pyodesys/tests/test_core.py:80-98 """
+    odes = ODESys()
+    x, y, p = odes.to_arrays(3.0, [1, 2], [5])
+    assert x.tolist() == [0, 3] and y.tolist() == [1, 2] and p.tolist() == [5]
+    x, y, p = odes.to_arrays([1, 2, 3], [[1, 2], [3, 4]], [5])
+    assert x.shape == (2, 3) and y.shape == (2, 2) and p.shape == (2, 1)
+    x, y, p = odes.to_arrays([[0, 1], [0, 2], [0, 3]], [1, 2], [[5], [6], [7]])
+    assert x.shape == (3, 2) and y.shape == (3, 2) and p[:, 0].tolist() == [5, 6, 7]
+    with pytest.raises(ValueError):
+        odes.to_arrays([1, 2], [[1, 2], [3, 4]], [[5], [6], [7]])
+    named = ODESys(names=('a', 'b'), param_names=('k',), dep_by_name=True, par_by_name=True)
+    x, y, p = named.to_arrays(1.0, {'a': [1, 2, 3], 'b': 4}, {'k': 2})
+    assert y.tolist() == [[1, 4], [2, 4], [3, 4]] and p.shape == (3, 1)
+
+
+def test_batch_result_is_lazy_and_list_like():
+    n, nt, ny = 5, 3, 2
+    counters = np.arange(6*n, dtype=np.int32).reshape(6, n)
+    info = BatchInfo('predefined', np.array([0, 0, 1, 0, 0], dtype=np.int32), np.full(n, nt, dtype=np.int32), counters,
+                     1e-6, 2e-6, np.tile(np.linspace(0, 1, nt), (n, 1)), np.zeros((n, nt, ny)), np.ones((n, 1)), True,
+                     nt=nt, iv=np.full((n, ny), 7.0))
+    res = BatchResult(info, ODESys())
+    assert len(res) == n and len(list(res)) == n and len(res[1:3]) == 2
+    xout, yout, nfo = res[2]
+    assert nfo['success'] is False and nfo['nreached'] == nt and nfo['mode'] == 'predefined'
+    assert nfo['nfev'] == counters[1, 2] and nfo['njev'] == counters[2, 2] and nfo['n_steps'] == counters[0, 2]
+    assert nfo['internal_params'].tolist() == [1.0, 7.0, 7.0]  # lazily appended initial values (core.py:410-411)
+    assert res[-1].info['nfev'] == counters[1, 4]
+    with pytest.raises(IndexError):
+        info[n]
+
+
+def test_shard_ranges_cover_the_batch():
+    for n in (0, 1, 7, 8, 1000003):
+        for g in (1, 2, 3, 8):
+            spans = [shard_range(n, g, k) for k in range(g)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            assert max(hi - lo for lo, hi in spans) <= -(-n // g)
+    with pytest.raises(ValueError):
+        shard_range(10, 2, 2)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def test_two_rank_gloo_sharding_and_gather():
+    """ N>1 path on CPU: two processes, gloo, each takes its contiguous shard (here integrated by the CPU oracle, which
+    stands in for the device), rank 0 gathers; result must equal the single-process run """
+    script = textwrap.dedent('''
+        import os, sys
+        sys.path.insert(0, %r)
+        import numpy as np, torch.distributed as dist
+        from pyodesys_b200 import systems
+        from pyodesys_b200.multi import shard_range, gather_to_rank0
+        from oracle import build_oracle
+        dist.init_process_group('gloo')
+        rank, world = dist.get_rank(), dist.get_world_size()
+        n = 101
+        b = systems.batch_robertson(n=n, seed=3, tend=10.0)
+        lo, hi = shard_range(n, world, rank)
+        orc = build_oracle(systems.robertson(compile=False)._native)
+        p = np.concatenate((b['params'], b['y0']), axis=1)
+        y, nr, st, cn = orc.integrate_predefined(b['y0'][lo:hi], np.array([0.0, 10.0]), p[lo:hi], b['atol'], b['rtol'],
+                                                 mxsteps=b['nsteps'], method='rosenbrock4', nthreads=1)
+        full = gather_to_rank0(y[:, -1, :], n)
+        steps = gather_to_rank0(cn[0].astype(np.int64)[:, None], n)
+        if rank == 0:
+            yref, _, _, cref = orc.integrate_predefined(b['y0'], np.array([0.0, 10.0]), p, b['atol'], b['rtol'],
+                                                        mxsteps=b['nsteps'], method='rosenbrock4', nthreads=1)
+            assert full.shape == (n, 3) and np.array_equal(full, yref[:, -1, :])
+            assert np.array_equal(steps[:, 0], cref[0])
+            print('GATHER_OK', world)
+        else:
+            assert full is None
+        dist.destroy_process_group()
+    ''') % _root
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2', '--master-addr', '127.0.0.1',
+           '--master-port', str(_free_port()), '-c', script]
+    path = os.path.join(_root, 'tests', '_gloo_worker.py')
+    with open(path, 'w') as fh:
+        fh.write(script)
+    try:
+        cmd = cmd[:-2] + [path]
+        proc = subprocess.run(cmd, capture_output=True, text=True, timeout=300,
+                              env=dict(os.environ, OMP_NUM_THREADS='1', MASTER_ADDR='127.0.0.1'))
+    finally:
+        os.remove(path)
+    assert proc.returncode == 0, proc.stderr[-3000:]
+    assert 'GATHER_OK 2' in proc.stdout
