@@ -100,7 +100,7 @@ class RefAnyodeLU:
         return x, info
 
 
-METHODS = {'rk4': 0, 'dopri5': 1, 'rosenbrock4': 2}
+METHODS = {'rk4': 0, 'dopri5': 1, 'rosenbrock4': 2, 'bdf': 3}
 
 
 class OracleModule:

@@ -629,8 +629,10 @@ template <> struct Stepper<M_ROS4> : Ros4Stepper<RegStore> {};  // instantiated 
 #ifndef PYODESYS_MIN_BLOCKS
 #define PYODESYS_MIN_BLOCKS (ODESYS_NY <= 4 ? 4 : 1)
 #endif
+// BDF carries 8 difference vectors + J + LU per lane: give it the full register file (2 blocks of 128 per SM)
+#define PYODESYS_MIN_BLOCKS_FOR(METHOD) ((METHOD) == M_BDF ? (ODESYS_NY <= 4 ? 2 : 1) : PYODESYS_MIN_BLOCKS)
 template <int METHOD, int MODE, int BLOCK>
-__global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS) integrate_kernel(const KernelArgs a) {
+__global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integrate_kernel(const KernelArgs a) {
     using St = Stepper<METHOD>;
     const unsigned lane = threadIdx.x & 31u;
     const int64_t nthreads = (int64_t)gridDim.x * BLOCK;

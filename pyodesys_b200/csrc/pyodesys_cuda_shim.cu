@@ -9,6 +9,11 @@
 #include "odesys_generated.h"
 
 #include "integrators.cuh"
+// BDF keeps 8 difference vectors + J + LU per lane in registers
+#define ODESYS_THREAD_BDF (ODESYS_HAS_JAC && ODESYS_NY <= 8)
+#if ODESYS_THREAD_BDF
+#include "bdf_integrator.cuh"
+#endif
 // Kernel families are only compiled where they can matter (the fully unrolled register code explodes for large ny):
 #define ODESYS_THREAD_ROS4 (ODESYS_HAS_JAC && ODESYS_NY <= 16)
 #define ODESYS_SMEM_KERNEL (ODESYS_HAS_JAC && ODESYS_NY >= 9)
@@ -187,6 +192,13 @@ template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cud
 #else
     case PYODESYS_CUDA_ROSENBROCK4: return fail("rosenbrock4 needs a Jacobian but the system was generated with jac=False");
 #endif
+#if ODESYS_THREAD_BDF
+    case PYODESYS_CUDA_BDF: return launch<M_BDF, MODE>(c, a, stream, bps);
+#elif ODESYS_HAS_JAC
+    case PYODESYS_CUDA_BDF: return fail("the BDF kernel keeps its difference table in registers and is limited to ny <= 8; use rosenbrock4");
+#else
+    case PYODESYS_CUDA_BDF: return fail("bdf needs a Jacobian but the system was generated with jac=False");
+#endif
     default: return fail("unknown method id %d", method);
     }
 }
@@ -278,7 +290,7 @@ int64_t pyodesys_cuda_query(const char *key) {
         {"nroots", ODESYS_NROOTS}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
         {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
         {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL},
-        {"has_smem_kernel", ODESYS_SMEM_KERNEL},
+        {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF},
 #if ODESYS_SMEM_KERNEL
         {"smem_doubles_per_thread", kSmemDoublesPerThread},
 #endif
@@ -298,6 +310,9 @@ int64_t pyodesys_cuda_query(const char *key) {
         if (m == PYODESYS_CUDA_DOPRI5) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_DOPRI5, 0, kBlock>);
 #if ODESYS_THREAD_ROS4
         if (m == PYODESYS_CUDA_ROSENBROCK4) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_ROS4, 0, kBlock>);
+#endif
+#if ODESYS_THREAD_BDF
+        if (m == PYODESYS_CUDA_BDF) e = mode ? cudaFuncGetAttributes(&fa, integrate_kernel<M_BDF, 1, kBlock>) : cudaFuncGetAttributes(&fa, integrate_kernel<M_BDF, 0, kBlock>);
 #endif
         if (e != cudaSuccess) { cudaGetLastError(); return -1; }
         return fa.numRegs;

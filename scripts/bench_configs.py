@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Secondary measurements for the BASELINE.json configs that are not bench.py's headline (C1 van der Pol,
-C2 Lorenz dense output, C4 radiolysis).  Prints one JSON line per config; run on the GPU box:
+C2 Lorenz dense output, C4 radiolysis; c3 = the headline workload with each stiff method).  Prints one JSON line per config; run on the GPU box:
 
     python scripts/bench_configs.py [c1] [c2] [c4] [--n N] [--reps K]
 """
@@ -17,6 +17,8 @@ def flops(counters, ny, f_rhs, f_jac, method, nt_out):
         f_step = 2*ny*10 + 2*ny*15 + ny*ny + ny + 4*ny
     elif method == 'dopri5':
         f_step = 2*ny*(1 + 2 + 3 + 4 + 5 + 6) + 2*ny*7 + 4*ny
+    elif method == 'bdf':
+        f_step = 2*ny*6 + 4*ny*3 + 4*ny  # predictor + psi, difference-table update, error norm (Newton work: nfev/nsolve)
     else:
         f_step = 16*ny
     return nsteps*f_step + nfev*f_rhs + njev*f_jac + nlu*f_lu + nsolve*f_solve + counters.shape[1]*nt_out*10*ny
@@ -50,7 +52,7 @@ def run(name, sysobj, b, n, reps, x, check=None, **extra):
 def main():
     from pyodesys_b200 import systems
     args = sys.argv[1:]
-    which = [a for a in args if a in ('c1', 'c2', 'c4')] or ['c1', 'c2', 'c4']
+    which = [a for a in args if a in ('c1', 'c2', 'c3', 'c4')] or ['c1', 'c2', 'c4']
     n_override = int(args[args.index('--n') + 1]) if '--n' in args else None
     reps = int(args[args.index('--reps') + 1]) if '--reps' in args else 3
     if 'c1' in which:
@@ -61,6 +63,12 @@ def main():
         n = n_override or 10**6
         b = systems.batch_lorenz(n=n, nt=100)
         run('C2 Lorenz dopri5 100 dense samples', systems.lorenz(), b, n, reps, b['x'])
+    if 'c3' in which:
+        n = n_override or 10**6
+        b = systems.batch_robertson(n=n)
+        for m in os.environ.get('C3_METHODS', 'rosenbrock4,bdf').split(','):
+            b['method'] = m
+            run('C3 Robertson %s final state' % m, systems.robertson(), b, n, reps, b['x'])
     if 'c4' in which:
         n = n_override or 10**5
         b = systems.batch_radiolysis(n=n)

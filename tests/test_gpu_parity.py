@@ -48,7 +48,7 @@ def within(y, ref, rtol, atol, factor=10):
 
 
 # ---- G1 --------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4', 'bdf'])
 def test_vdp_blessed_values(cuda_device, golden, method):
     """ ``_test_NativeSys`` (pyodesys/native/tests/_tests.py:20-29) """
     native = systems.vdp()
@@ -78,14 +78,14 @@ def test_rk4_fixed_step_matches_reference_integrator(cuda_device, golden):
 
 
 # ---- G3 / G4 ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4', 'bdf'])
 def test_multiple_predefined(cuda_device, method):
     """ ``_test_integrate_multiple_predefined`` (test_core.py:182-193), atol=rtol=1e-10 (test_odeint.py:44-46) """
     odes = systems.decay()
     _xout = np.array([[0, 1, 2], [0, 1, 2], [0, 1, 2]])
     _y0 = np.array([[1, 2], [2, 3], [3, 4]])
     _params = np.array([[5], [6], [7]])
-    results = odes.integrate(_xout, _y0, params=_params, atol=1e-10, rtol=1e-10, method=method, nsteps=2000)
+    results = odes.integrate(_xout, _y0, params=_params, atol=1e-10, rtol=1e-10, method=method, nsteps=20000)
     assert len(results) == 3
     for idx in range(3):
         xout, yout, info = results[idx]
@@ -95,7 +95,7 @@ def test_multiple_predefined(cuda_device, method):
         assert info['nfev'] > 0
 
 
-@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4'])
+@pytest.mark.parametrize('method', ['dopri5', 'rosenbrock4', 'bdf'])
 def test_multiple_adaptive(cuda_device, method):
     """ ``_test_integrate_multiple_adaptive`` (test_core.py:281-297): per-system spans """
     odes = systems.sine()
@@ -457,3 +457,55 @@ def test_coupled_network_ny28_auto_selects_group_kernel(cuda_device):
     assert within(res.yout, y_cpu, b['rtol'], b['atol']).all()
     with pytest.raises(RuntimeError, match="ny <= 16"):
         net.integrate(b['x'], b['y0'][:2], b['params'][:2], kernel='thread', force_predefined=True, method='rosenbrock4')
+
+
+# ---- BDF (cvode ``method='BDF'`` role): CUDA stepper vs oracle restatement and the reference's known answers ------------
+def test_bdf_robertson_batch_vs_oracle_and_lsoda(cuda_device, golden):
+    rob = systems.robertson()
+    orc = build_oracle(rob._native)
+    n = 4096
+    b = systems.batch_robertson(n=n, seed=3)
+    res = rob.integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'],
+                        method='bdf', force_predefined=True)
+    info = res.info
+    assert (info.status == 0).all() and (info.nreached == 2).all()
+    y_gpu = res.yout[:, -1, :]
+    y_cpu, nr, st, cn = orc.integrate_predefined(b['y0'], np.array([0.0, 1e5]), full_params(b['y0'], b['params']),
+                                                 b['atol'], b['rtol'], mxsteps=b['nsteps'], method='bdf')
+    assert (st == 0).all()
+    ok = within(y_gpu, y_cpu[:, -1, :], b['rtol'], b['atol'])
+    assert ok.all(), "worst err/tol %g" % (np.abs(y_gpu - y_cpu[:, -1]) /
+                                          np.maximum(10*b['rtol']*np.abs(y_cpu[:, -1]), 10*b['atol'])).max()
+    # same algorithm -> about the same amount of work (the step-size factors use fp32 powers on the device)
+    assert abs(info.counters[0].sum() - cn[0].sum()) <= 0.05*cn[0].sum()
+    assert info.counters[2].sum() < 0.1*info.counters[0].sum()  # the Jacobian is reused across many steps
+    assert np.abs(y_gpu.sum(axis=1) - 1).max() < 1e-9
+    g = golden['robertson_1e5']
+    ref = np.array(g['yout'])[:, -1, :]
+    assert within(y_gpu[:48], ref, b['rtol'], b['atol'], factor=10).all()
+    # dense output rows against the tight LSODA runs of the reference
+    y0, k = np.array(g['y0']), np.array(g['k'])
+    res = rob.integrate(np.array(g['xout']), y0, k, atol=1e-14, rtol=1e-9, nsteps=50000, method='bdf')
+    assert within(res.yout, np.array(g['yout']), 1e-9, 1e-14, factor=1000).all()
+
+
+def test_bdf_robertson_1e11_batched(cuda_device, golden):
+    """ G6 with the BDF stepper: tolerances and assertions of _test_robertson_native.py:52-71 """
+    rob = systems.robertson()
+    res = rob.integrate([0, 1e11], [[1.0, 0, 0]]*3, [[0.04, 1e4, 3e7]]*3, atol=1e-10, rtol=1e-14, nsteps=5000,
+                        method='bdf', force_predefined=True)
+    for r in res:
+        assert r.info['success'] and r.info['nfev'] > 100 and r.info['njev'] > 10
+        assert np.allclose(golden['known_answers']['robertson_1e11'], r.yout[-1], atol=1e-16, rtol=0.02)
+
+
+def test_bdf_failure_modes(cuda_device):
+    rob = systems.robertson()
+    b = systems.batch_robertson(n=64, seed=5)
+    res = rob.integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], nsteps=20, method='bdf',
+                        force_predefined=True, return_on_error=True)
+    assert (res.info.status == 1).all() and (res.info.nreached == 1).all() and np.isnan(res.yout[:, 1]).all()
+    with pytest.raises(RuntimeError, match="limited to ny <= 8"):
+        b = systems.batch_radiolysis(n=4)
+        systems.radiolysis().integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], method='bdf',
+                                       force_predefined=True)

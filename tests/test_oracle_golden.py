@@ -211,3 +211,58 @@ def test_oracle_header_says_test_only():
                 with open(os.path.join(dirpath, fn)) as fh:
                     src = fh.read()
                 assert 'import oracle' not in src and 'from oracle' not in src, fn
+
+
+# ---- BDF (cvode ``method='BDF'`` role) ---------------------------------------------------------------------
+def test_bdf_oracle_against_known_answers(golden):
+    """ restated variable-order BDF/NDF vs the reference's known answers: G1 (vdP blessed values), G3 (batched
+    decay), G6 (Robertson t=1e11, tolerances of _test_robertson_native.py:52-71), tight LSODA fixtures at t=1e5 """
+    orc = _orc(systems.vdp(compile=False))
+    y, nr, st, cn = orc.integrate_predefined([[1.0, 0]], [[0, 1., 2]], [[2.0, 1, 0]], 1e-8, 1e-8, mxsteps=5000,
+                                             method='bdf')
+    assert st[0] == 0 and nr[0] == 3
+    assert np.allclose(y[0], golden['known_answers']['vdp_mu2_t012'])
+    orc = _orc(systems.decay(compile=False))
+    xout = np.array([[0, 1, 2.]]*3)
+    y0 = np.array([[1., 2], [2, 3], [3, 4]])
+    p = np.array([[5.], [6], [7]])
+    y, nr, st, cn = orc.integrate_predefined(y0, xout, full_params(y0, p), 1e-10, 1e-10, mxsteps=20000, method='bdf')
+    for i in range(3):
+        ref = y0[i, 0]*np.exp(-p[i, 0]*xout[i])
+        assert np.allclose(y[i, :, 0], ref) and np.allclose(y[i, :, 1], y0[i, 0] - ref + y0[i, 1])
+    orc = _orc(systems.robertson(compile=False))
+    y0 = np.array([[1.0, 0, 0]]*3)
+    k = np.array([[0.04, 1e4, 3e7]]*3)
+    y, nr, st, cn = orc.integrate_predefined(y0, [0, 1e11], full_params(y0, k), 1e-10, 1e-14, mxsteps=5000, method='bdf')
+    assert (st == 0).all()
+    assert np.allclose(golden['known_answers']['robertson_1e11'], y[0, -1], atol=1e-16, rtol=0.02)
+    assert cn[1, 0] > 100 and cn[2, 0] > 10  # nfev, njev as asserted by the reference test
+    g = golden['robertson_1e5']
+    y0, k, ref = np.array(g['y0']), np.array(g['k']), np.array(g['yout'])
+    y, nr, st, cn = orc.integrate_predefined(y0, g['xout'], full_params(y0, k), 1e-12, 1e-8, mxsteps=50000, method='bdf')
+    assert (st == 0).all()
+    assert within(y, ref, 1e-8, 1e-12, factor=10).all()
+    assert np.abs(y.sum(axis=2) - 1).max() < 1e-10
+    # the two stiff methods agree with each other far inside the band when both run tight
+    ya, _, sa, _ = orc.integrate_predefined(y0, g['xout'], full_params(y0, k), 1e-15, 1e-11, mxsteps=500000, method='bdf')
+    yb, _, sb, _ = orc.integrate_predefined(y0, g['xout'], full_params(y0, k), 1e-15, 1e-11, mxsteps=500000,
+                                            method='rosenbrock4')
+    assert (sa == 0).all() and (sb == 0).all()
+    assert within(ya, yb, 1e-9, 1e-14, factor=10).all()
+
+
+def test_bdf_oracle_adaptive_rows_and_dense_output():
+    """ adaptive mode returns every accepted step; interpolated rows equal landing on the points """
+    orc = _orc(systems.sine(compile=False))
+    y0 = np.array([[0., 6.0]])
+    p = np.array([[3.0]])
+    xy, nrows, st, cn = orc.integrate_adaptive(y0, [0.], [2.], full_params(y0, p), 1e-9, 1e-9, mxsteps=50000,
+                                               method='bdf', max_rows=50001)
+    n = nrows[0]
+    x = xy[0, :n, 0]
+    assert st[0] == 0 and x[0] == 0 and x[-1] == 2.0 and np.all(np.diff(x) > 0) and n == cn[0, 0] - cn[5, 0] + 1
+    assert np.allclose(xy[0, :n, 1], 2*np.sin(3*x), atol=2e-6, rtol=0)
+    xo = np.linspace(0, 2, 41)
+    y, nr, st, cn = orc.integrate_predefined(y0, xo, full_params(y0, p), 1e-9, 1e-9, mxsteps=50000, method='bdf')
+    assert st[0] == 0 and nr[0] == 41
+    assert np.allclose(y[0, :, 0], 2*np.sin(3*xo), atol=2e-6, rtol=0)
