@@ -55,7 +55,10 @@ int fail(const char *fmt, ...) {
     } while (0)
 
 constexpr int kMaxDev = 64;
-constexpr int kBlock = 128;
+#ifndef PYODESYS_BLOCK
+#define PYODESYS_BLOCK 128
+#endif
+constexpr int kBlock = PYODESYS_BLOCK;
 
 enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, NBUF };
 

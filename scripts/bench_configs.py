@@ -66,9 +66,23 @@ def main():
     if 'c3' in which:
         n = n_override or 10**6
         b = systems.batch_robertson(n=n)
+        from oracle import build_oracle
+        rob = systems.robertson()
         for m in os.environ.get('C3_METHODS', 'rosenbrock4,bdf').split(','):
             b['method'] = m
-            run('C3 Robertson %s final state' % m, systems.robertson(), b, n, reps, b['x'])
+
+            def check(res, m=m):
+                k = min(n, 4096)
+                orc = build_oracle(rob._native)
+                p = np.concatenate((b['params'][:k], b['y0'][:k]), axis=1)
+                y, nr, st, cn = orc.integrate_predefined(b['y0'][:k], np.array([0.0, b['x'][1]]), p, b['atol'], b['rtol'],
+                                                         mxsteps=b['nsteps'], method=m)
+                err = np.abs(res.yout[:k, -1] - y[:, -1])
+                tol = np.maximum(10*b['rtol']*np.abs(y[:, -1]), 10*b['atol'])
+                return {"vs_oracle_max_err_over_tol": float((err/tol).max()),
+                        "max_mass_error": float(np.abs(res.yout[:, -1].sum(axis=1) - 1).max()),
+                        "flags": os.environ.get('PYODESYS_CUDA_NVCC_FLAGS', '')}
+            run('C3 Robertson %s final state' % m, rob, b, n, reps, b['x'], check=check)
     if 'c4' in which:
         n = n_override or 10**5
         b = systems.batch_radiolysis(n=n)
