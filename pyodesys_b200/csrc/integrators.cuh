@@ -63,7 +63,8 @@ struct KernelArgs {
     int32_t *nrows;         // adaptive
     int32_t *nreached;      // predefined
     int32_t *status;
-    int32_t *counters;      // [NCOUNT, n] or nullptr
+    int32_t *counters;      // [NCOUNT, counters_ld] or nullptr
+    int64_t counters_ld;    // row length of ``counters`` (= n of the whole call; a chunk sees a column window)
     unsigned long long *work_counter;  // dynamic scheduling (nullptr = static grid-stride)
 };
 
@@ -339,6 +340,8 @@ template <> struct Stepper<M_RK4> {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = false;
     static constexpr int kOrder = 4;
+    static constexpr int kSharedDoublesPerThread = 0;
+    __device__ __forceinline__ void bind_shared(double *, int, int) {}
     __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) { return 0; }
     __device__ __forceinline__ void auto_step(OdeSys &, const KernelArgs &, const Tol &, double, const double *,
                                               double, double &) {}  // the nominal step never changes
@@ -378,6 +381,8 @@ template <> struct Stepper<M_DOPRI5> {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 5;
+    static constexpr int kSharedDoublesPerThread = 0;
+    __device__ __forceinline__ void bind_shared(double *, int, int) {}
     double k1[NY];                                   // f(t, y), FSAL
     double k7[NY];                                   // f(t+h, ynew) of the last attempt
     double r3[NY], r4[NY], r5[NY];                   // dense output polynomial of the last attempt
@@ -511,6 +516,8 @@ template <class Store> struct Ros4Stepper : Store {
     typedef typename Store::Sys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 4;
+    static constexpr int kSharedDoublesPerThread = 0;
+    __device__ __forceinline__ void bind_shared(double *, int, int) {}
     using Store::g1;
     using Store::g2;
     using Store::g3;
@@ -757,6 +764,10 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
 
     typename St::Sys sys;
     St st;
+    if (St::kSharedDoublesPerThread > 0) {
+        extern __shared__ double stepper_smem[];
+        st.bind_shared(stepper_smem, threadIdx.x, BLOCK);
+    }
     Tol tol;
     tol.rtol = a.rtol;
 #pragma unroll
@@ -992,12 +1003,12 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                 a.nrows[s] = k_out;
             }
             if (a.counters) {
-                a.counters[C_NSTEPS * a.n + s] = cnt.nsteps;
-                a.counters[C_NFEV * a.n + s] = sys.nfev;
-                a.counters[C_NJEV * a.n + s] = sys.njev;
-                a.counters[C_NLU * a.n + s] = cnt.nlu;
-                a.counters[C_NSOLVE * a.n + s] = cnt.nsolve;
-                a.counters[C_NREJECT * a.n + s] = cnt.nreject;
+                a.counters[C_NSTEPS * a.counters_ld + s] = cnt.nsteps;
+                a.counters[C_NFEV * a.counters_ld + s] = sys.nfev;
+                a.counters[C_NJEV * a.counters_ld + s] = sys.njev;
+                a.counters[C_NLU * a.counters_ld + s] = cnt.nlu;
+                a.counters[C_NSOLVE * a.counters_ld + s] = cnt.nsolve;
+                a.counters[C_NREJECT * a.counters_ld + s] = cnt.nreject;
             }
             active = false;
         }

@@ -66,7 +66,9 @@ struct DevCtx {
     std::mutex mtx;
     bool ready = false;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // second lane of the chunk pipeline (host-pointer calls)
     cudaEvent_t ev[4];
+    cudaEvent_t ev_k0, ev_k1, ev_fork, ev_join;
     void *buf[NBUF] = {};
     size_t cap[NBUF] = {};
     int sm_count = 0;
@@ -80,7 +82,12 @@ int ctx_init(DevCtx &c, int device) {
     CU_CHECK(cudaGetDeviceProperties(&prop, device));
     c.sm_count = prop.multiProcessorCount;
     CU_CHECK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    CU_CHECK(cudaStreamCreateWithFlags(&c.stream2, cudaStreamNonBlocking));
     for (auto &e : c.ev) CU_CHECK(cudaEventCreate(&e));
+    CU_CHECK(cudaEventCreate(&c.ev_k0));
+    CU_CHECK(cudaEventCreate(&c.ev_k1));
+    CU_CHECK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
+    CU_CHECK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
     c.ready = true;
     return 0;
 }
@@ -98,8 +105,11 @@ int ensure(DevCtx &c, Buf b, size_t bytes) {
 
 template <int METHOD, int MODE> int launch(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
     auto kern = integrate_kernel<METHOD, MODE, kBlock>;
+    // steppers whose state is addressed dynamically (BDF difference table) keep it in shared memory
+    const size_t smem = (size_t)Stepper<METHOD>::kSharedDoublesPerThread * kBlock * sizeof(double);
+    if (smem > 48 * 1024) CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kBlock, 0));
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kBlock, smem));
     if (occ < 1) occ = 1;
     if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
     // persistent grid: a multiple of the SM count, never more blocks than there is work
@@ -107,7 +117,7 @@ template <int METHOD, int MODE> int launch(DevCtx &c, const KernelArgs &a, cudaS
     const int64_t need = (a.n + kBlock - 1) / kBlock;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    kern<<<(unsigned)grid, kBlock, 0, stream>>>(a);
+    kern<<<(unsigned)grid, kBlock, smem, stream>>>(a);
     g_launches.fetch_add(1);
     CU_CHECK(cudaGetLastError());
     return 0;
@@ -240,6 +250,7 @@ int check_common(const Common &q) {
 void fill_args(KernelArgs &a, const Common &q) {
     memset(&a, 0, sizeof(a));
     a.n = q.n;
+    a.counters_ld = q.n;
     for (int i = 0; i < NY; ++i) a.atol[i] = q.atol[q.natol == 1 ? 0 : i];
     a.rtol = q.rtol;
     a.mxsteps = q.mxsteps;
@@ -268,6 +279,75 @@ int stage(DevCtx &c, Buf b, const void *src, size_t bytes, const void **dst) {
     if (ensure(c, b, bytes)) return -1;
     CU_CHECK(cudaMemcpyAsync(c.buf[b], src, bytes, cudaMemcpyHostToDevice, c.stream));
     *dst = c.buf[b];
+    return 0;
+}
+
+// ---- chunk pipeline of the host-pointer calls ------------------------------------------------------------------
+// The batch is cut into up to kMaxChunks index ranges that alternate between two streams: the H2D copy of chunk
+// i+1 and the D2H copy of chunk i-1 overlap the kernel of chunk i, and because consecutive kernels sit on different
+// streams the blocks of chunk i+1 move onto the SMs as the persistent blocks of chunk i drain (the tail of one
+// chunk is filled by the head of the next).  Device buffers span the whole batch; a chunk is a window into them.
+// Whether to cut at all is decided by the bytes that cross PCIe per system: with a few hundred bytes (final state
+// only: C3, 128 B/system) the copies are ~10 % of the call and every extra kernel boundary costs more than that
+// in load balance (measured: 8 chunks of 125k Robertson systems 18.8 ms against 15.3 ms in one launch); with
+// dense output (C2: 2.4 KB/system, D2H 47 ms against a 33 ms kernel) the pipeline hides the kernel behind D2H.
+constexpr int kMaxChunks = 16;
+constexpr int64_t kMinChunk = 32768;
+constexpr size_t kPipelineBytesPerSystem = 512;
+constexpr size_t kChunkBytes = 32u << 20;
+
+struct ChunkPlan {
+    int nchunks;
+    int64_t per;
+    int64_t lo(int k) const { return (int64_t)k * per; }
+    int64_t len(int k, int64_t n) const { return (k + 1) * per > n ? n - k * per : per; }
+};
+
+ChunkPlan plan_chunks(int64_t n, size_t bytes_per_system) {
+    ChunkPlan p;
+    p.nchunks = 1;
+    p.per = n;
+    if (bytes_per_system < kPipelineBytesPerSystem) return p;
+    int64_t per = (int64_t)(kChunkBytes / bytes_per_system);
+    if (per * kMaxChunks < n) per = (n + kMaxChunks - 1) / kMaxChunks;
+    if (per < kMinChunk) per = kMinChunk;
+    per = (per + 1023) / 1024 * 1024;
+    if (per >= n) return p;
+    p.per = per;
+    p.nchunks = (int)((n + per - 1) / per);
+    return p;
+}
+
+// device window (cap check + pointer) without a copy
+int reserve(DevCtx &c, Buf b, const void *src, size_t bytes) {
+    if (!src) return 0;
+    return ensure(c, b, bytes);
+}
+int h2d(DevCtx &c, Buf b, const void *src, size_t elem_bytes, int64_t lo, int64_t len, cudaStream_t st) {
+    if (!src || len <= 0) return 0;
+    CU_CHECK(cudaMemcpyAsync((char *)c.buf[b] + (size_t)lo * elem_bytes, (const char *)src + (size_t)lo * elem_bytes,
+                             (size_t)len * elem_bytes, cudaMemcpyHostToDevice, st));
+    return 0;
+}
+int d2h(DevCtx &c, Buf b, void *dst, size_t elem_bytes, int64_t lo, int64_t len, cudaStream_t st) {
+    if (!dst || len <= 0) return 0;
+    CU_CHECK(cudaMemcpyAsync((char *)dst + (size_t)lo * elem_bytes, (const char *)c.buf[b] + (size_t)lo * elem_bytes,
+                             (size_t)len * elem_bytes, cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+template <class T> const T *dev_or_null(DevCtx &c, Buf b, const void *src, int64_t lo, size_t elems_per_row = 1) {
+    return src ? (const T *)c.buf[b] + (size_t)lo * elems_per_row : nullptr;
+}
+
+// timings of a pipelined call: h2d = start .. first kernel start, kernel = first kernel start .. last kernel end
+// (copies of the neighbouring chunks run underneath), d2h = last kernel end .. everything on the host
+int pipeline_timings(DevCtx &c, double *timings, double t_begin) {
+    if (!timings) return 0;
+    float ms = 0;
+    CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev_k0)); timings[PYODESYS_CUDA_T_H2D] = ms * 1e-3;
+    CU_CHECK(cudaEventElapsedTime(&ms, c.ev_k0, c.ev_k1)); timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3;
+    CU_CHECK(cudaEventElapsedTime(&ms, c.ev_k1, c.ev[3])); timings[PYODESYS_CUDA_T_D2H] = ms * 1e-3;
+    timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin;
     return 0;
 }
 
@@ -369,7 +449,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
     a.yout_soa = (opt && ptr_kind == 1) ? opt->yout_soa : 0;
     cudaStream_t stream = c.stream;
     if (want_dynamic(q)) {
-        if (ensure(c, B_WORK, sizeof(unsigned long long))) return -1;
+        if (ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long))) return -1;
         a.work_counter = (unsigned long long *)c.buf[B_WORK];
     }
     const int bps = opt ? opt->blocks_per_sm : 0;
@@ -389,42 +469,60 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         return 0;
     }
 
-    // ---- host pointers: H2D, kernel, D2H ---------------------------------------------------------
+    // ---- host pointers: chunked H2D / kernel / D2H pipeline on two streams ---------------------------------
     const size_t nn = (size_t)n;
-    const void *p;
-    CU_CHECK(cudaEventRecord(c.ev[0], stream));
-    if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
-    if (stage(c, B_PARAMS, a.params_ld ? params : nullptr, nn * (size_t)a.params_ld * 8, &p)) return -1; a.params = (const double *)p;
-    if (stage(c, B_XOUT, xout, (shared_x ? 1 : nn) * nt * 8, &p)) return -1; a.xout = (const double *)p;
-    if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;
-    if (stage(c, B_DXMIN, dx_min, nn * 8, &p)) return -1; a.dx_min = (const double *)p;
-    if (stage(c, B_DXMAX, dx_max, nn * 8, &p)) return -1; a.dx_max = (const double *)p;
-    if (ensure(c, B_YOUT, nn * nt * NY * 8) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4)) return -1;
-    a.yout = (double *)c.buf[B_YOUT];
-    a.nreached = (int32_t *)c.buf[B_NREACHED];
-    a.status = (int32_t *)c.buf[B_STATUS];
-    if (counters) {
-        if (ensure(c, B_COUNTERS, nn * NCOUNT * 4)) return -1;
-        a.counters = (int32_t *)c.buf[B_COUNTERS];
+    const size_t prow = (size_t)a.params_ld;
+    if (reserve(c, B_Y0, y0, nn * NY * 8) || reserve(c, B_PARAMS, prow ? params : nullptr, nn * prow * 8) ||
+        reserve(c, B_XOUT, xout, (shared_x ? 1 : nn) * nt * 8) || reserve(c, B_DX0, dx0, nn * 8) ||
+        reserve(c, B_DXMIN, dx_min, nn * 8) || reserve(c, B_DXMAX, dx_max, nn * 8) ||
+        ensure(c, B_YOUT, nn * nt * NY * 8) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4) ||
+        (counters && ensure(c, B_COUNTERS, nn * NCOUNT * 4)) ||
+        ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long)))
+        return -1;
+    const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + (shared_x ? 0 : nt) + (size_t)nt * NY) * 8 + 32);
+    const bool dynamic = a.work_counter != nullptr;
+    cudaStream_t lanes[2] = {c.stream, c.stream2};
+    CU_CHECK(cudaEventRecord(c.ev[0], c.stream));
+    CU_CHECK(cudaMemsetAsync(c.buf[B_WORK], 0, kMaxChunks * sizeof(unsigned long long), c.stream));
+    if (shared_x) CU_CHECK(cudaMemcpyAsync(c.buf[B_XOUT], xout, (size_t)nt * 8, cudaMemcpyHostToDevice, c.stream));
+    CU_CHECK(cudaEventRecord(c.ev_fork, c.stream));
+    CU_CHECK(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+    for (int k = 0; k < plan.nchunks; ++k) {
+        cudaStream_t st = lanes[k & 1];
+        const int64_t lo = plan.lo(k), len = plan.len(k, n);
+        if (h2d(c, B_Y0, y0, NY * 8, lo, len, st) || h2d(c, B_PARAMS, prow ? params : nullptr, prow * 8, lo, len, st) ||
+            (!shared_x && h2d(c, B_XOUT, xout, (size_t)nt * 8, lo, len, st)) || h2d(c, B_DX0, dx0, 8, lo, len, st) ||
+            h2d(c, B_DXMIN, dx_min, 8, lo, len, st) || h2d(c, B_DXMAX, dx_max, 8, lo, len, st))
+            return -1;
+        KernelArgs ak = a;
+        ak.n = len;
+        ak.y0 = (const double *)c.buf[B_Y0] + (size_t)lo * NY;
+        ak.params = prow ? (const double *)c.buf[B_PARAMS] + (size_t)lo * prow : nullptr;
+        ak.xout = (const double *)c.buf[B_XOUT] + (shared_x ? 0 : (size_t)lo * nt);
+        ak.dx0 = dev_or_null<double>(c, B_DX0, dx0, lo);
+        ak.dx_min = dev_or_null<double>(c, B_DXMIN, dx_min, lo);
+        ak.dx_max = dev_or_null<double>(c, B_DXMAX, dx_max, lo);
+        ak.yout = (double *)c.buf[B_YOUT] + (size_t)lo * nt * NY;
+        ak.nreached = (int32_t *)c.buf[B_NREACHED] + lo;
+        ak.status = (int32_t *)c.buf[B_STATUS] + lo;
+        ak.counters = counters ? (int32_t *)c.buf[B_COUNTERS] + lo : nullptr;
+        ak.counters_ld = n;
+        ak.work_counter = dynamic ? (unsigned long long *)c.buf[B_WORK] + k : nullptr;
+        if (k == 0) CU_CHECK(cudaEventRecord(c.ev_k0, st));
+        if (dispatch<0>(c, ak, method, st, bps, opt)) return -1;
+        if (k == plan.nchunks - 1) CU_CHECK(cudaEventRecord(c.ev_k1, st));
+        if (d2h(c, B_YOUT, yout, (size_t)nt * NY * 8, lo, len, st) || d2h(c, B_NREACHED, nreached, 4, lo, len, st) ||
+            d2h(c, B_STATUS, status, 4, lo, len, st))
+            return -1;
+        if (counters)
+            CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+                                       (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
     }
-    if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
-    CU_CHECK(cudaEventRecord(c.ev[1], stream));
-    if (dispatch<0>(c, a, method, stream, bps, opt)) return -1;
-    CU_CHECK(cudaEventRecord(c.ev[2], stream));
-    CU_CHECK(cudaMemcpyAsync(yout, a.yout, nn * nt * NY * 8, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaMemcpyAsync(nreached, a.nreached, nn * 4, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaMemcpyAsync(status, a.status, nn * 4, cudaMemcpyDeviceToHost, stream));
-    if (counters) CU_CHECK(cudaMemcpyAsync(counters, a.counters, nn * NCOUNT * 4, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaEventRecord(c.ev[3], stream));
-    CU_CHECK(cudaStreamSynchronize(stream));
-    if (timings) {
-        float ms = 0;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1])); timings[PYODESYS_CUDA_T_H2D] = ms * 1e-3;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[1], c.ev[2])); timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[2], c.ev[3])); timings[PYODESYS_CUDA_T_D2H] = ms * 1e-3;
-        timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin;
-    }
-    return 0;
+    CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
+    CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+    CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
+    CU_CHECK(cudaStreamSynchronize(c.stream));
+    return pipeline_timings(c, timings, t_begin);
 }
 
 int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, const double *x0, const double *xend,
@@ -451,7 +549,7 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
     a.max_rows = max_rows;
     cudaStream_t stream = c.stream;
     if (want_dynamic(q)) {
-        if (ensure(c, B_WORK, sizeof(unsigned long long))) return -1;
+        if (ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long))) return -1;
         a.work_counter = (unsigned long long *)c.buf[B_WORK];
     }
     const int bps = opt ? opt->blocks_per_sm : 0;
@@ -473,41 +571,60 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         return 0;
     }
 
-    const void *p;
-    CU_CHECK(cudaEventRecord(c.ev[0], stream));
-    if (stage(c, B_Y0, y0, nn * NY * 8, &p)) return -1; a.y0 = (const double *)p;
-    if (stage(c, B_PARAMS, a.params_ld ? params : nullptr, nn * (size_t)a.params_ld * 8, &p)) return -1; a.params = (const double *)p;
-    if (stage(c, B_XOUT, x0, nn * 8, &p)) return -1; a.x0 = (const double *)p;
-    if (stage(c, B_XEND, xend, nn * 8, &p)) return -1; a.xend = (const double *)p;
-    if (stage(c, B_DX0, dx0, nn * 8, &p)) return -1; a.dx0 = (const double *)p;
-    if (stage(c, B_DXMIN, dx_min, nn * 8, &p)) return -1; a.dx_min = (const double *)p;
-    if (stage(c, B_DXMAX, dx_max, nn * 8, &p)) return -1; a.dx_max = (const double *)p;
-    if (ensure(c, B_YOUT, out_bytes) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4)) return -1;
-    a.xyout = (double *)c.buf[B_YOUT];
-    a.nrows = (int32_t *)c.buf[B_NREACHED];
-    a.status = (int32_t *)c.buf[B_STATUS];
-    if (counters) {
-        if (ensure(c, B_COUNTERS, nn * NCOUNT * 4)) return -1;
-        a.counters = (int32_t *)c.buf[B_COUNTERS];
+    const size_t prow = (size_t)a.params_ld;
+    const size_t row_bytes = (size_t)max_rows * (1 + NY) * 8;
+    if (reserve(c, B_Y0, y0, nn * NY * 8) || reserve(c, B_PARAMS, prow ? params : nullptr, nn * prow * 8) ||
+        ensure(c, B_XOUT, nn * 8) || ensure(c, B_XEND, nn * 8) || reserve(c, B_DX0, dx0, nn * 8) ||
+        reserve(c, B_DXMIN, dx_min, nn * 8) || reserve(c, B_DXMAX, dx_max, nn * 8) || ensure(c, B_YOUT, out_bytes) ||
+        ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4) ||
+        (counters && ensure(c, B_COUNTERS, nn * NCOUNT * 4)) ||
+        ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long)))
+        return -1;
+    const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + 2) * 8 + row_bytes + 32);
+    const bool dynamic = a.work_counter != nullptr;
+    cudaStream_t lanes[2] = {c.stream, c.stream2};
+    CU_CHECK(cudaEventRecord(c.ev[0], c.stream));
+    CU_CHECK(cudaMemsetAsync(c.buf[B_WORK], 0, kMaxChunks * sizeof(unsigned long long), c.stream));
+    CU_CHECK(cudaEventRecord(c.ev_fork, c.stream));
+    CU_CHECK(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+    for (int k = 0; k < plan.nchunks; ++k) {
+        cudaStream_t st = lanes[k & 1];
+        const int64_t lo = plan.lo(k), len = plan.len(k, n);
+        if (h2d(c, B_Y0, y0, NY * 8, lo, len, st) || h2d(c, B_PARAMS, prow ? params : nullptr, prow * 8, lo, len, st) ||
+            h2d(c, B_XOUT, x0, 8, lo, len, st) || h2d(c, B_XEND, xend, 8, lo, len, st) ||
+            h2d(c, B_DX0, dx0, 8, lo, len, st) || h2d(c, B_DXMIN, dx_min, 8, lo, len, st) ||
+            h2d(c, B_DXMAX, dx_max, 8, lo, len, st))
+            return -1;
+        KernelArgs ak = a;
+        ak.n = len;
+        ak.y0 = (const double *)c.buf[B_Y0] + (size_t)lo * NY;
+        ak.params = prow ? (const double *)c.buf[B_PARAMS] + (size_t)lo * prow : nullptr;
+        ak.x0 = (const double *)c.buf[B_XOUT] + lo;
+        ak.xend = (const double *)c.buf[B_XEND] + lo;
+        ak.dx0 = dev_or_null<double>(c, B_DX0, dx0, lo);
+        ak.dx_min = dev_or_null<double>(c, B_DXMIN, dx_min, lo);
+        ak.dx_max = dev_or_null<double>(c, B_DXMAX, dx_max, lo);
+        ak.xyout = (double *)c.buf[B_YOUT] + (size_t)lo * max_rows * (1 + NY);
+        ak.nrows = (int32_t *)c.buf[B_NREACHED] + lo;
+        ak.status = (int32_t *)c.buf[B_STATUS] + lo;
+        ak.counters = counters ? (int32_t *)c.buf[B_COUNTERS] + lo : nullptr;
+        ak.counters_ld = n;
+        ak.work_counter = dynamic ? (unsigned long long *)c.buf[B_WORK] + k : nullptr;
+        if (k == 0) CU_CHECK(cudaEventRecord(c.ev_k0, st));
+        if (dispatch<1>(c, ak, method, st, bps, opt)) return -1;
+        if (k == plan.nchunks - 1) CU_CHECK(cudaEventRecord(c.ev_k1, st));
+        if (d2h(c, B_YOUT, xyout, row_bytes, lo, len, st) || d2h(c, B_NREACHED, nrows, 4, lo, len, st) ||
+            d2h(c, B_STATUS, status, 4, lo, len, st))
+            return -1;
+        if (counters)
+            CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+                                       (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
     }
-    if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
-    CU_CHECK(cudaEventRecord(c.ev[1], stream));
-    if (dispatch<1>(c, a, method, stream, bps, opt)) return -1;
-    CU_CHECK(cudaEventRecord(c.ev[2], stream));
-    CU_CHECK(cudaMemcpyAsync(xyout, a.xyout, out_bytes, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaMemcpyAsync(nrows, a.nrows, nn * 4, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaMemcpyAsync(status, a.status, nn * 4, cudaMemcpyDeviceToHost, stream));
-    if (counters) CU_CHECK(cudaMemcpyAsync(counters, a.counters, nn * NCOUNT * 4, cudaMemcpyDeviceToHost, stream));
-    CU_CHECK(cudaEventRecord(c.ev[3], stream));
-    CU_CHECK(cudaStreamSynchronize(stream));
-    if (timings) {
-        float ms = 0;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[0], c.ev[1])); timings[PYODESYS_CUDA_T_H2D] = ms * 1e-3;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[1], c.ev[2])); timings[PYODESYS_CUDA_T_KERNEL] = ms * 1e-3;
-        CU_CHECK(cudaEventElapsedTime(&ms, c.ev[2], c.ev[3])); timings[PYODESYS_CUDA_T_D2H] = ms * 1e-3;
-        timings[PYODESYS_CUDA_T_TOTAL] = now_s() - t_begin;
-    }
-    return 0;
+    CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
+    CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+    CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
+    CU_CHECK(cudaStreamSynchronize(c.stream));
+    return pipeline_timings(c, timings, t_begin);
 }
 
 int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params, double *f,

@@ -560,12 +560,12 @@ __global__ void __launch_bounds__(kSB) smem_ros4_kernel(const KernelArgs a) {
                 a.nrows[s] = k_out;
             }
             if (a.counters) {
-                a.counters[C_NSTEPS * a.n + s] = cnt.nsteps;
-                a.counters[C_NFEV * a.n + s] = st.nfev;
-                a.counters[C_NJEV * a.n + s] = st.njev;
-                a.counters[C_NLU * a.n + s] = cnt.nlu;
-                a.counters[C_NSOLVE * a.n + s] = cnt.nsolve;
-                a.counters[C_NREJECT * a.n + s] = cnt.nreject;
+                a.counters[C_NSTEPS * a.counters_ld + s] = cnt.nsteps;
+                a.counters[C_NFEV * a.counters_ld + s] = st.nfev;
+                a.counters[C_NJEV * a.counters_ld + s] = st.njev;
+                a.counters[C_NLU * a.counters_ld + s] = cnt.nlu;
+                a.counters[C_NSOLVE * a.counters_ld + s] = cnt.nsolve;
+                a.counters[C_NREJECT * a.counters_ld + s] = cnt.nreject;
             }
             active = false;
         }

@@ -215,7 +215,8 @@ class CudaModule:
         if y0.ndim != 2 or y0.shape[1] != self.ny:
             raise ValueError("y0 needs to be of shape (N, %d)" % self.ny)
         n = y0.shape[0]
-        if np.isnan(y0).any():
+        # one pass without a temporary: a NaN anywhere makes the sum NaN; inf - inf is settled by the exact test
+        if not np.isfinite(y0.sum()) and np.isnan(y0).any():
             raise ValueError("NaN found in y0")
         params = np.ascontiguousarray(params, dtype=np.float64)
         pcols = self.nparams if iv_from_y0 else self.np_tot
