@@ -298,14 +298,17 @@ __device__ __forceinline__ void lu_solve(const Mat &a, const int *piv, double *b
 template <class Sys>
 __device__ __forceinline__ double initial_step(Sys &sys, const KernelArgs &a, const Tol &tol, double t0,
                                                const double *y, const double *f0, double span, int order) {
-    double d0 = 0.0, d1 = 0.0;
+    // Division free: this runs once per system on the refill path, where a single lane of the warp is active
+    // (ncu: IEEE divisions with their zero-operand slow path made the refill path 8 % of all issued instructions).
+    // It is a heuristic - ~40-bit reciprocals are ample.
+    double d0 = 0.0, d1 = 0.0, isk[NY];
 #pragma unroll
     for (int i = 0; i < NY; ++i) {
-        const double sk = tol.atol[i] + tol.rtol * fabs(y[i]);
-        d0 = fmax(d0, fabs(y[i]) / sk);
-        d1 = fmax(d1, fabs(f0[i]) / sk);
+        isk[i] = fast_rcp<1>(tol.atol[i] + tol.rtol * fabs(y[i]) + 1e-300);
+        d0 = fmax(d0, fabs(y[i]) * isk[i]);
+        d1 = fmax(d1, fabs(f0[i]) * isk[i]);
     }
-    double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 * fast_rcp<1>(d1);
     h0 = fmin(h0, fabs(span));
     const double dir = span >= 0 ? 1.0 : -1.0;
     double y1[NY], f1[NY];
@@ -314,15 +317,12 @@ __device__ __forceinline__ double initial_step(Sys &sys, const KernelArgs &a, co
     AnyODE::Status st = eval_rhs(sys, a, t0 + dir * h0, y1, f1);
     double d2 = 0.0;
 #pragma unroll
-    for (int i = 0; i < NY; ++i) {
-        const double sk = tol.atol[i] + tol.rtol * fabs(y[i]);
-        d2 = fmax(d2, fabs(f1[i] - f0[i]) / sk);
-    }
-    d2 /= h0;
+    for (int i = 0; i < NY; ++i) d2 = fmax(d2, fabs(f1[i] - f0[i]) * isk[i]);
+    d2 *= fast_rcp<1>(h0);
     if (st != AnyODE::Status::success || !(d2 <= DBL_MAX)) d2 = 0.0;
     const double dmax = fmax(d1, d2);
     // the starting step is a heuristic: single precision exp2/log2 instead of the double precision pow
-    const double h1 = (dmax <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : fast_pow(0.01 / dmax, 1.0f / (float)order);
+    const double h1 = (dmax <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : fast_pow(0.01 * fast_rcp<1>(dmax), 1.0f / (float)order);
     return fmin(fmin(100.0 * h0, h1), fabs(span));
 }
 

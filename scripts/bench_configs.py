@@ -39,8 +39,8 @@ def run(name, sysobj, b, n, reps, x, check=None, **extra):
     fl = flops(info.counters, sysobj.ny, gen.flops['rhs'], gen.flops['jac'], b['method'], nt)
     ker = info.timings['kernel']
     out = {"config": name, "n": n, "method": b['method'], "ok": int((info.status == 0).sum()),
-           "kernel_ms": ker*1e3, "systems_per_s_kernel": n/ker, "e2e_ms": min(ts[2:])*1e3,
-           "systems_per_s_e2e": n/min(ts[2:]), "fp64_tflops_algorithmic": fl/ker*1e-12,
+           "kernel_ms": ker*1e3, "systems_per_s_kernel": n/ker, "e2e_ms": min(ts[2:] or ts)*1e3,
+           "systems_per_s_e2e": n/min(ts[2:] or ts), "fp64_tflops_algorithmic": fl/ker*1e-12,
            "mean_steps": float(info.counters[0].mean()), "max_steps": int(info.counters[0].max()),
            "yout_GBps": n*nt*sysobj.ny*8/ker*1e-9, "phases_ms": {k: v*1e3 for k, v in info.timings.items()}}
     if check is not None:
