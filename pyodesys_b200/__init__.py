@@ -6,11 +6,13 @@ pyodesys: ``NativeSys.from_callback(...).integrate(x, y0[N,ny], params[N,np], at
 Only that path is provided: symbolic definition -> CUDA code generation ->
 hand-written integrator kernels behind a C ABI -> ``Result`` / ``info`` in the reference's layout.
 """
-from .core import ODESys, Result, BatchResult, BatchInfo
+from .core import ODESys, Result, BatchResult, BatchInfo, integrate_auto_switch, integrate_chained
 from .symbolic import SymbolicSys
+from .transforms import TransformedSys, ScaledSys, symmetricsys
 
 __version__ = '0.1.0'
-__all__ = ['ODESys', 'Result', 'BatchResult', 'BatchInfo', 'SymbolicSys', 'native_sys']
+__all__ = ['ODESys', 'Result', 'BatchResult', 'BatchInfo', 'SymbolicSys', 'TransformedSys', 'ScaledSys',
+           'symmetricsys', 'integrate_auto_switch', 'integrate_chained', 'native_sys']
 
 
 def __getattr__(name):

@@ -179,6 +179,12 @@ class BatchResult:
         for i in range(len(self)):
             yield self[i]
 
+    def processed(self):
+        """ ``(xout, yout, params)`` of the WHOLE batch after the system's post-processors (one vectorised call,
+        e.g. the back-transformation of a :class:`~pyodesys_b200.transforms.TransformedSys`) instead of one
+        ``Result`` at a time. """
+        return self.odesys.post_process(self.info.xout, self.info.yout, self.info.params)
+
 
 class ODESys:
     """ Argument shaping + dispatch of the reference's ``ODESys`` for the native path. """
@@ -320,3 +326,65 @@ class ODESys:
         self._internal = (np.array(nfo['internal_xout']), np.array(nfo['internal_yout']), _p.copy())
         return Result(*(tuple(self.post_process(nfo['internal_xout'], nfo['internal_yout'], _p))
                         + (nfo, self)))
+
+
+def integrate_auto_switch(odes, kw, x, y0, params=(), **kwargs):
+    """ Switch between formulations of one ODE system (``pyodesys/core.py:824-915``).
+
+    ``odes[0]`` integrates first with its entry of every iterable in ``kw`` (typically a small ``nsteps`` and
+    ``return_on_error=True``); systems that did not reach the end are restarted from where they stopped with
+    ``odes[1]`` and so on.  Adaptive mode only (``x`` = (x0, xend) per system), like the reference.  The
+    restart is one batched call per formulation: systems that already finished go through it as zero-length
+    spans.  Returns one :class:`Result` (or a list for a batch) whose ``info`` sums ``nfev, njev, time_cpu,
+    time_wall`` and carries ``nsys`` = number of formulations used.
+    """
+    x_arr = np.asarray(x, dtype=np.float64)
+    if x_arr.shape[-1] > 2:
+        raise NotImplementedError("Only adaptive support return_on_error for now")
+    batch = x_arr.ndim == 2
+    X = np.atleast_2d(x_arr).copy()
+    n = X.shape[0]
+    Y0 = np.array(np.broadcast_to(np.asarray(y0, dtype=np.float64), (n,) + np.shape(y0)[-1:]))
+    sum_keys = ('nfev', 'njev', 'time_cpu', 'time_wall')
+    autonomous = lambda o: bool(getattr(o, 'autonomous_interface', False) == True)  # noqa: E712,E731
+    nxt_aut = autonomous(odes[0])
+    offset = X[:, 0].copy() if nxt_aut else np.zeros(n)      # what has to be added to xout of an autonomous leg
+    xs = [[np.array([0.0 if nxt_aut else X[i, 0]])] for i in range(n)]
+    ys = [[Y0[i:i + 1].copy()] for i in range(n)]
+    tot = [dict.fromkeys(sum_keys, 0) for _ in range(n)]
+    last_params = None
+    used = 0
+    for oi, ode in enumerate(odes):
+        used = oi + 1
+        if oi < len(odes) - 1:
+            nxt_aut = autonomous(odes[oi + 1])
+        call_kw = dict(kwargs)
+        call_kw.update({k: v[oi] for k, v in kw.items()})
+        res = ode.integrate(X if batch else X[0], Y0 if batch else Y0[0], params, **call_kw)
+        legs = res if batch else [res]
+        done = True
+        for i, r in enumerate(legs):
+            xs[i].append(np.asarray(r.xout)[1:] + offset[i])
+            ys[i].append(np.asarray(r.yout)[1:])
+            for k in sum_keys:
+                if k in r.info:
+                    tot[i][k] += r.info[k]
+            tot[i]['success'] = r.info['success']
+            done = done and bool(r.info['success'])
+        last_params = [r.params for r in legs]
+        if done or oi == len(odes) - 1:
+            break
+        for i, r in enumerate(legs):
+            xlast = np.asarray(r.xout)[-1]
+            if nxt_aut:
+                X[i] = (0.0, abs(X[i, -1] - xlast))
+                offset[i] += xlast
+            else:
+                X[i, 0] = xlast
+            Y0[i] = np.asarray(r.yout)[-1]
+    out = [Result(np.concatenate(xs[i]), np.concatenate(ys[i], axis=0), last_params[i], dict(nsys=used, **tot[i]),
+                  odes[0]) for i in range(n)]
+    return out if batch else out[0]
+
+
+integrate_chained = integrate_auto_switch  # the reference keeps the old name (core.py:918)

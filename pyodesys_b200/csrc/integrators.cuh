@@ -424,13 +424,14 @@ template <> struct Stepper<M_DOPRI5> {
                                   2187.0 / 6784.0 * k5[i] + 11.0 / 84.0 * k6[i]);
         bad |= eval_rhs(sys, a, t + h, ynew, k7);
         // error estimate and odeint's measure: |err_i| / (atol + rtol (|y_i| + |h| |y'_i|))
-        err = 0.0;
+        // the error measure only steers the step size: formed in single precision (see Ros4Stepper::attempt)
+        float ef = 0.0f;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
             const double e = h * (71.0 / 57600.0 * k1[i] - 71.0 / 16695.0 * k3[i] + 71.0 / 1920.0 * k4[i] -
                                   17253.0 / 339200.0 * k5[i] + 22.0 / 525.0 * k6[i] - 1.0 / 40.0 * k7[i]);
-            const double sc = tol.atol[i] + tol.rtol * (fabs(y[i]) + fabs(h) * fabs(k1[i]));
-            err = fmax(err, fabs(e) / sc);
+            const double sc = fma(tol.rtol, fabs(y[i]) + fabs(h * k1[i]), tol.atol[i]);
+            ef = fmaxf(ef, fabsf((float)e) * rcp_ftz(fmaxf((float)sc, 1e-37f)));
             // continuous extension (Hairer, Norsett, Wanner: Solving ODEs I, II.6; dopri5.f CONTD5)
             const double ydiff = ynew[i] - y[i];
             const double bspl = h * k1[i] - ydiff;
@@ -440,20 +441,22 @@ template <> struct Stepper<M_DOPRI5> {
                          10690763975.0 / 1880347072.0 * k4[i] + 701980252875.0 / 199316789632.0 * k5[i] -
                          1453857185.0 / 822651844.0 * k6[i] + 69997945.0 / 29380423.0 * k7[i]);
         }
-        if (!(err <= DBL_MAX)) bad |= 1;
+        if (!(ef <= 3.0e38f)) bad |= 1;
+        err = (double)ef;
         return bad;
     }
     // odeint default_step_adjuster: shrink by max(0.9 err^-1/3, 1/5); grow (only if err < 0.5) by
     // 0.9 err^-1/5 capped at 5.
     __device__ __forceinline__ bool control(double err, double, double &hnext, double h) {
-        if (err > 1.0) {
-            hnext = h * fmax(0.9 * fast_pow(err, -1.0f / 3.0f), 0.2);
+        const float ef = (float)err;
+        if (ef > 1.0f) {
+            hnext = h * (double)fmaxf(0.9f * ex2_ftz((-1.0f / 3.0f) * lg2_ftz(fminf(ef, 1e30f))), 0.2f);
             return false;
         }
         hnext = h;
-        if (err < 0.5) {
-            const double e = fmax(3.2e-4 /* 5^-5 */, err);
-            hnext = h * fmin(0.9 * fast_pow(e, -0.2f), 5.0);
+        if (ef < 0.5f) {
+            const float e = fmaxf(3.2e-4f /* 5^-5 */, ef);
+            hnext = h * (double)fminf(0.9f * ex2_ftz(-0.2f * lg2_ftz(e)), 5.0f);
         }
         return true;
     }

@@ -8,6 +8,7 @@ import sympy as sp
 
 from pyodesys_b200 import systems
 from pyodesys_b200.native.cuda import NativeCudaSys
+from pyodesys_b200.transforms import TransformedSys, symmetricsys
 
 _cache = {}
 
@@ -101,9 +102,44 @@ def bounded(compile=True):
         decay3_rhs, 3, 3, lower_bounds=[0, 0, 0], compile=compile))
 
 
+def decay_rhs(t, y, k):
+    """ linear decay chain, last species stable (``decay_rhs`` of pyodesys/native/tests/_tests.py) """
+    ny = len(y)
+    dydt = [0]*ny
+    for idx in range(ny):
+        if idx < ny - 1:
+            dydt[idx] -= y[idx]*k[idx]
+        if idx > 0:
+            dydt[idx] += y[idx - 1]*k[idx - 1]
+    return dydt
+
+
+class TransformedCudaSys(TransformedSys, NativeCudaSys):
+    """ the mixin the reference's tests build (``class TransformedNativeSys(TransformedSys, NativeSys)``) """
+
+
+_logexp = (sp.log, sp.exp)
+
+
+def loglog_decay4(compile=True):
+    """ log-log transformed 4-species chain (``_test_symmetricsys_nativesys`` / ``_test_multiple_adaptive_chained``) """
+    SS = symmetricsys(_logexp, _logexp, SuperClass=TransformedCudaSys)
+    return _get(('loglog_decay4', compile), lambda: SS.from_callback(decay_rhs, 4, 3, compile=compile))
+
+
+def lin_decay4(compile=True):
+    return _get(('lin_decay4', compile), lambda: NativeCudaSys.from_callback(decay_rhs, 4, 3, compile=compile))
+
+
+def loglog_robertson(compile=True):
+    """ Robertson in log(c), log(t) (``_test_chained_multi_native`` with logc=logt=True) """
+    SS = symmetricsys(_logexp, _logexp, SuperClass=TransformedCudaSys)
+    return _get(('loglog_robertson', compile), lambda: SS.from_callback(systems.robertson_f, 3, 3, compile=compile))
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
-           nojac, bounded]
+           nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson]
     return {f.__name__: f(compile=compile) for f in fns}
 
 

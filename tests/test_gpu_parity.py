@@ -509,3 +509,85 @@ def test_bdf_failure_modes(cuda_device):
         b = systems.batch_radiolysis(n=4)
         systems.radiolysis().integrate(b['x'], b['y0'], b['params'], atol=b['atol'], rtol=b['rtol'], method='bdf',
                                        force_predefined=True)
+
+
+# ---- transformed systems + formulation switching ----------------------------------------------
+def test_symmetricsys_native(cuda_device):
+    """ ``_test_symmetricsys_nativesys`` (pyodesys/native/tests/_tests.py:75-100): log-log transformed chain """
+    from pyodesys_b200 import integrate_chained
+    ts = tsys.loglog_decay4()
+    k = [7., 3, 2]
+    y0 = [1e-20]*4
+    y0[0] = 1
+    rtol = atol = 1e-7
+    xout, yout, info = ts.integrate([1e-12, 1], y0, k, atol=atol, rtol=rtol, first_step=1e-4, nsteps=800)
+    ref = bateman_full(y0, k + [0], xout - xout[0])
+    assert info['success'] and abs(xout[0]/1e-12 - 1) < 1e-13 and abs(xout[-1] - 1) < 1e-13  # exp(log(x)) round trip
+    assert np.allclose(yout, ref, rtol=rtol*150, atol=atol*150)
+    # a batch goes through the vectorised processors: same numbers as one system at a time
+    res = ts.integrate(np.array([[1e-12, .25, .5, 1.0]]*3), [y0]*3, [k, [5., 3, 2], [7., 1, 2]], atol=atol, rtol=rtol,
+                       first_step=1e-4, nsteps=800)
+    xb, yb, pb = res.processed()
+    assert np.allclose(xb, [[1e-12, .25, .5, 1.0]]*3, rtol=1e-13, atol=0)
+    for i, kk in enumerate([k, [5., 3, 2], [7., 1, 2]]):
+        assert np.allclose(yb[i], bateman_full(y0, list(kk) + [0], xb[i] - xb[i, 0]), rtol=rtol*150, atol=atol*150)
+        assert np.array_equal(res[i].yout, yb[i])
+
+
+def test_multiple_adaptive_chained(cuda_device):
+    """ ``_test_multiple_adaptive_chained`` (pyodesys/native/tests/_tests.py:198-227) with the tolerances the
+    odeint variant of the reference runs it at (test_odeint.py: rosenbrock4, atol 1e-8 / rtol 1e-10 scale) """
+    from pyodesys_b200 import integrate_chained
+    rtol, atol = 1e-10, 1e-10
+    ks = [[7e13, 3, 2], [2e5, 3e4, 12.7]]
+    y0s = [[1.0, 3.0, 2.0, 5.0], [2.0, 1.0, 3.0, 4.0]]
+    t0, tend = 1e-16, 7
+    touts = [(t0, tend)]*2
+    tsys_, osys = tsys.loglog_decay4(), tsys.lin_decay4()
+    comb = integrate_chained([tsys_, osys], {'nsteps': [30, 5000], 'return_on_error': [True, False]}, touts, y0s, ks,
+                             atol=atol, rtol=rtol, first_step=1e-14)
+    for y0, k, res in zip(y0s, ks, comb):
+        xout, yout = res.xout, res.yout
+        assert abs(xout[0]/t0 - 1) < 1e-13 and abs(xout[-1] - tend) < 1e-12 and np.all(np.diff(xout) >= 0)
+        ref = bateman_full(y0, k + [0], xout - xout[0])
+        assert np.allclose(yout, ref, rtol=rtol*1000, atol=atol*1000)
+        assert 0 <= res.info['time_cpu'] < 100 and 0 <= res.info['time_wall'] < 100
+        assert res.info['success'] is True and res.info['nsys'] == 2 and res.info['nfev'] > 10
+
+
+def test_robertson_chained_log_then_linear(cuda_device, golden):
+    """ ``_test_chained_multi_native`` (pyodesys/native/tests/_test_robertson_native.py:12-71), logc = logt = True:
+    N = 3 systems start in log(c), log(t), switch to the linear formulation, reach t = 1e11 """
+    from pyodesys_b200 import integrate_chained
+    k = (.04, 1e4, 3e7)
+    init = (1, 1e-20, 1e-20)
+    for odes, kw in [([tsys.loglog_robertson(), systems.robertson()],
+                      {'nsteps': [100, 5000], 'return_on_error': [True, False]}),
+                     ([systems.robertson()], {'nsteps': [5000]})]:
+        results = integrate_chained(odes, kw, [(1e-10, 1e11)]*3, [init]*3, [k]*3, atol=1e-10, rtol=1e-14)
+        for res in results:
+            x, y, nfo = res
+            assert np.allclose(golden['known_answers']['robertson_1e11'], y[-1, :], atol=1e-16, rtol=0.02)
+            assert nfo['success'] is True and nfo['nfev'] > 100 and nfo['njev'] > 10 and nfo['nsys'] in (1, 2)
+
+
+def test_chunk_pipeline_is_invisible(cuda_device):
+    """ output-heavy batches are cut into chunks that alternate between two streams (H2D / kernel / D2H overlap);
+    systems are independent, so every row must equal the row of an un-chunked call bit for bit """
+    lo = systems.lorenz()
+    n = 100000  # 100 samples x 3 doubles per system -> 4 chunks of 32768 rows
+    b = systems.batch_lorenz(n=n, nt=100)
+    kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'], method='dopri5')
+    full = lo.integrate(b['x'], b['y0'], b['params'], **kw)
+    assert (full.info.status == 0).all() and (full.info.nreached == 100).all()
+    for sl in (slice(0, 5000), slice(32768 - 100, 32768 + 100), slice(n - 3000, n)):
+        part = lo.integrate(b['x'], b['y0'][sl], b['params'][sl], **kw)
+        assert np.array_equal(part.yout, full.yout[sl])
+        assert np.array_equal(part.info.counters, full.info.counters[:, sl])
+    # adaptive mode through the same pipeline (rows of (x, y...) per accepted step)
+    x2 = np.array([[0.0, 0.5]]*40000)
+    ad = lo.integrate(x2, b['y0'][:40000], b['params'][:40000], atol=1e-6, rtol=1e-6, nsteps=400, method='dopri5')
+    ad1 = lo.integrate(x2[:64], b['y0'][39000:39064], b['params'][39000:39064], atol=1e-6, rtol=1e-6, nsteps=400,
+                       method='dopri5')
+    for i in range(64):
+        assert np.array_equal(ad[39000 + i].yout, ad1[i].yout) and ad[39000 + i].xout[-1] == 0.5
