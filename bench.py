@@ -92,7 +92,7 @@ class ClockSampler:
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                          '--format=csv,noheader,nounits', '-lms', '20'],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -166,7 +166,7 @@ def cpu_oracle_rate(rob, batch_fn, seconds, nthreads=None):
 
 def main_reference(args, rank, world):
     if rank != 0:
-        return
+        return None
     from pyodesys_b200 import systems
     rob = systems.robertson(compile=False)
     n, cores, run = cpu_oracle_rate(rob, systems.batch_robertson, max(2.0, args.cpu_seconds/3))
@@ -186,10 +186,33 @@ def main_reference(args, rank, world):
             "gpu_launches": 0,
             "note": "reference native back ends (cvode/odeint/gsl) cannot be built in this image (no SUNDIALS/"
                     "Boost/GSL/pycodeexport); this arm is the CPU port of that path on all host cores"}
-    print(json.dumps(line), flush=True)
+    return line
+
+
+class _StdoutToStderr:
+    """ Everything written to file descriptor 1 while the bench runs goes to stderr (NCCL prints its version banner
+    on stdout); the JSON line is the only thing this program puts on stdout. """
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
 
 
 def main():
+    with _StdoutToStderr():
+        line = _main()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def _main():
     args = parse()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -284,8 +307,19 @@ def main():
     except OSError:
         pass
     hbm_peak = peaks.get('hbm_gbs', 6650.0)
+    # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, per launch of 1e6 systems, from the committed
+    # ``ncu --set full`` capture (profiles/r1d_ros4_ncu_summary.md); only quoted for the configuration it was taken on
+    traffic = None
+    try:
+        with open(os.path.join(_root, 'profiles', 'ncu_traffic.json')) as fh:
+            tr = json.load(fh)
+        if tr.get('systems_per_launch') == n and tr.get('method') == 'rosenbrock4':
+            traffic = tr['dram_bytes_per_launch']
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {"bound": "fp64", "achieved": achieved_tf, "peak": peak_sus, "unit": "TFLOP/s",
-                "frac": (achieved_tf/peak_sus) if peak_sus else None, "traffic": None,
+                "frac": (achieved_tf/peak_sus) if peak_sus else None, "traffic": traffic,
+                "traffic_unit": "bytes per launch (ncu dram read+write; algorithmic bytes per launch: %d)" % bytes_alg,
                 "peak_source": "measured live: csrc/fp64_peak.cu DFMA chains, sustained %.1f s (burst %.2f)" %
                                (1.5, peak_best or 0.0),
                 "flops_per_launch": flops, "kernel_ms": kern_avg_s*1e3,
@@ -329,6 +363,7 @@ def main():
                "sample": "%d systems of the same generator (seed 3), oracle/oracle.cpp Rosenbrock-4, OpenMP "
                          "schedule(dynamic), %.1f s" % (ncpu, dt)}
 
+    line = None
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms/args.steps, "higher_is_better": True,
@@ -336,9 +371,9 @@ def main():
                 "config": workload_config(args, world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": int(launches), "clocks": clocks,
                 "check": {"systems_ok": n_ok, "systems": n, "max_mass_error": mass_err, "last": last}}
-        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    return line
 
 
 if __name__ == '__main__':
