@@ -8,11 +8,11 @@ hand-written integrator kernels behind a C ABI -> ``Result`` / ``info`` in the r
 """
 from .core import ODESys, Result, BatchResult, BatchInfo, integrate_auto_switch, integrate_chained
 from .symbolic import SymbolicSys
-from .transforms import TransformedSys, ScaledSys, symmetricsys
+from .transforms import TransformedSys, ScaledSys, symmetricsys, PartiallySolvedSystem, get_logexp
 
 __version__ = '0.1.0'
 __all__ = ['ODESys', 'Result', 'BatchResult', 'BatchInfo', 'SymbolicSys', 'TransformedSys', 'ScaledSys',
-           'symmetricsys', 'integrate_auto_switch', 'integrate_chained', 'native_sys']
+           'symmetricsys', 'PartiallySolvedSystem', 'get_logexp', 'integrate_auto_switch', 'integrate_chained', 'native_sys']
 
 
 def __getattr__(name):

@@ -237,4 +237,10 @@ class SymbolicSys(ODESys):
         if 'dfdx' not in kwargs and getattr(ori, '_dfdx', True) is not True:
             kwargs['dfdx'] = ori._dfdx
         kwargs.setdefault('backend', ori.be)
+        # processors of the template stay innermost (``symbolic.py:489-497``): its pre-processors run first, its
+        # post-processors last
+        if ori.pre_processors:
+            kwargs['pre_processors'] = list(kwargs.get('pre_processors') or []) + list(ori.pre_processors)
+        if ori.post_processors:
+            kwargs['post_processors'] = list(ori.post_processors) + list(kwargs.get('post_processors') or [])
         return cls(zip(ori.dep, ori.exprs), ori.indep, **kwargs)

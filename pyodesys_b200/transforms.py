@@ -226,3 +226,146 @@ class ScaledSys(TransformedSys):
         return TransformedSys.from_callback.__func__(
             cls, cb, ny, nparams, dep_transf_cbs=repeat(cls._scale_fw_bw(dep_scaling)),
             indep_transf_cbs=cls._scale_fw_bw(indep_scaling), **kwargs)
+
+
+def get_logexp(a=1, b=0, a2=None, b2=None, backend=None):
+    """ (forward, backward) callables for ``u = ln(a*x + b)`` (``pyodesys/symbolic.py:1361-1390``); a small shift
+    ``b`` (forward only, ``b2 = 0``) keeps the transformation defined at x = 0. """
+    a2 = a if a2 is None else a2
+    b2 = b if b2 is None else b2
+    be = get_backend(backend)
+    return (lambda x: be.log(a*x + b), lambda x: (be.exp(x) - b2)/a2)
+
+
+class PartiallySolvedSystem(SymbolicSys):
+    """ An ODE system in which some dependent variables are replaced by analytic expressions
+    (``pyodesys/symbolic.py:1134-1358``).
+
+    ``analytic_factory(x0, y0, p0[, backend])`` returns ``{dep_symbol: expression}`` in terms of the initial values;
+    those variables leave the system, the rest is integrated with the expressions substituted, and the full state
+    is rebuilt afterwards.  The initial values reach the integrated system as ordinary extra parameters
+    ``[..., x0, y0_0 .. y0_{ny-1}]`` (the reference does the same, ``symbolic.py:1240-1249``).  Both processors
+    are single vectorised evaluations over the whole batch.
+    """
+
+    def __init__(self, original_system, analytic_factory, **kwargs):
+        ori = original_system
+        be = ori.be
+        if 'pre_processors' in kwargs or 'post_processors' in kwargs:
+            raise NotImplementedError("Cannot override pre-/postprocessors")
+        self._ori_sys = ori
+        self.original_dep = tuple(ori.dep)
+        # own symbols for the initial values: a native subclass adds its ``i_<dep>`` symbols for the REDUCED system
+        x0 = be.Symbol('ps0_' + (str(ori.indep) if ori.indep is not None else 'indep'))
+        y0 = tuple(be.Symbol('ps0_' + str(d)) for d in ori.dep)
+        pars = dict(zip(ori.param_names, ori.params)) if ori.par_by_name else ori.params
+        dep0 = dict(zip(ori.names, y0)) if ori.dep_by_name else y0
+        self.analytic_exprs = dict(_ensure_4args(analytic_factory)(x0, dep0, pars, be))
+        if len(self.analytic_exprs) == 0:
+            raise ValueError("Failed to produce any analytic expressions.")
+        for d in self.analytic_exprs:
+            if d not in self.original_dep:
+                raise ValueError("%s is not a dependent variable of the original system" % d)
+        self._analytic_idx = [self.original_dep.index(d) for d in self.analytic_exprs]   # in factory order
+        self._keep_idx = [i for i in range(len(self.original_dep)) if i not in self._analytic_idx]
+        new_dep = [self.original_dep[i] for i in self._keep_idx]
+        new_exprs = [ori.exprs[i].subs(self.analytic_exprs) for i in self._keep_idx]
+        self._n_ori_params = len(ori.params)
+        new_pars = tuple(ori.params) + (x0,) + y0
+        kw = dict(kwargs)
+        for attr in ('dep_by_name', 'par_by_name', 'description', 'to_arrays_callbacks'):
+            if attr not in kw and getattr(ori, attr, None) is not None:
+                kw[attr] = getattr(ori, attr)
+        if ori.names:
+            self.free_names = [ori.names[i] for i in self._keep_idx]
+            kw.setdefault('names', self.free_names)
+        else:
+            self.free_names = None
+        if ori.param_names:
+            kw.setdefault('param_names', list(ori.param_names) + [str(x0)] + [str(s) for s in y0])
+        for b in ('lower_bounds', 'upper_bounds'):
+            if b not in kw and getattr(ori, b, None) is not None:
+                kw[b] = np.asarray(getattr(ori, b))[self._keep_idx]
+        if kw.get('linear_invariants') is None and ori.linear_invariants is not None:
+            # only meaningful when they do not involve the eliminated variables
+            rows = [r for r in ori.linear_invariants.tolist() if all(r[i] == 0 for i in self._analytic_idx)]
+            kw['linear_invariants'] = [[r[i] for i in self._keep_idx] for r in rows] or None
+        roots = kw.pop('roots', ori.roots)
+        if roots is not None:
+            roots = [r.subs(self.analytic_exprs) for r in roots]
+        args = ((ori.indep,) if ori.indep is not None else (be.Dummy('x'),)) + tuple(new_dep) + new_pars
+        self._analytic_cb = be.Lambdify(args, list(self.analytic_exprs.values()))
+        self._n_new_params = len(new_pars)
+        super().__init__(zip(new_dep, new_exprs), ori.indep, new_pars, backend=be, roots=roots,
+                         pre_processors=list(ori.pre_processors) + [self._reduce_xyp],
+                         post_processors=[self._rebuild_xyp] + list(ori.post_processors), **kw)
+
+    def _reduce_xyp(self, x, y, p):
+        """ (x[..., nt], y0[..., ny_ori], p[..., np]) -> (x, y0 of the kept variables, [p, x0, y0]) """
+        x, y, p = (np.asarray(a, dtype=np.float64) for a in (x, y, p))
+        lead = y.shape[:-1]
+        x0 = np.broadcast_to(x[..., :1], lead + (1,))
+        p = np.broadcast_to(p, lead + p.shape[-1:])
+        return x, y[..., self._keep_idx], np.concatenate((p, x0, y), axis=-1)
+
+    def _rebuild_xyp(self, x, y, p):
+        """ (x[..., nt], y[..., nt, ny_kept], p[..., >= np + 1 + ny_ori]) -> full state, original parameters """
+        if isinstance(x, (list, tuple)) or (hasattr(x, '__getitem__') and not hasattr(x, 'ndim')):
+            out = [self._rebuild_xyp(x[i], y[i], p[i]) for i in range(len(x))]
+            return [o[0] for o in out], [o[1] for o in out], np.asarray(p)[..., :self._n_ori_params]
+        x, y, p = (np.asarray(a, dtype=np.float64) for a in (x, y, p))
+        lead = y.shape[:-1]
+        pp = p[..., :self._n_new_params]
+        pp = np.broadcast_to(pp.reshape(pp.shape[:-1] + (1,)*(len(lead) - (pp.ndim - 1)) + pp.shape[-1:]),
+                             lead + (self._n_new_params,))
+        rows = np.concatenate((np.broadcast_to(x, lead)[..., None], y, pp), axis=-1)
+        analytic = self._analytic_cb(rows)
+        full = np.empty(lead + (len(self.original_dep),))
+        full[..., self._keep_idx] = y
+        full[..., self._analytic_idx] = analytic
+        return x, full, p[..., :self._n_ori_params]
+
+    @classmethod
+    def from_linear_invariants(cls, ori_sys, preferred=None, **kwargs):
+        """ Eliminate one variable per linear invariant (``pyodesys/symbolic.py:1275-1336``): variable ``tgt`` of
+        invariant row ``r`` becomes ``y0_tgt - sum_{c != tgt} A[r,c] (y_c - y0_c) / A[r,tgt]``. """
+        A = ori_sys.be.Matrix(ori_sys.linear_invariants)
+        if len(A.rref()[1]) < A.rows:
+            raise NotImplementedError("Linear invariants contain linear dependencies.")
+        cols = [(r, [c for c in range(A.cols) if A[r, c] != 0]) for r in range(A.rows)]
+        if preferred is None:
+            preferred = list(ori_sys.names[:A.rows]) if ori_sys.dep_by_name else list(range(A.rows))
+        targets = [ori_sys.names.index(d) if ori_sys.dep_by_name else (d if isinstance(d, int) else ori_sys.dep.index(d))
+                   for d in preferred]
+        chosen = []
+        for r, cs in sorted(cols, key=lambda rc: len(rc[1])):
+            hit = next((t for t in targets if t in cs), None)
+            if hit is not None:
+                chosen.append((r, hit))
+                targets.remove(hit)
+            if not targets:
+                break
+        if targets:
+            raise ValueError("Could not find a solutions for: %s" % targets)
+
+        def analytic_factory(x0, y0, p0, be):
+            iv = (lambda c: y0[ori_sys.names[c]]) if ori_sys.dep_by_name else (lambda c: y0[c])
+            return {ori_sys.dep[t]: iv(t) - sum(A[r, c]*(ori_sys.dep[c] - iv(c)) for c in range(A.cols) if c != t)/A[r, t]
+                    for r, t in chosen}
+        used_rows, used_cols = zip(*chosen)
+        rest = [[cell for c, cell in enumerate(row) if c not in used_cols]
+                for r, row in enumerate(A.tolist()) if r not in used_rows]
+        return cls(ori_sys, analytic_factory, linear_invariants=rest or None, **kwargs)
+
+    def __getitem__(self, key):
+        d = self.original_dep[self._ori_sys.names.index(key)]
+        return self.analytic_exprs.get(d, d)
+
+    def integrate(self, *args, **kwargs):
+        """ per-component ``atol`` is given for the ORIGINAL variables (``symbolic.py:1345-1358``) """
+        atol = kwargs.get('atol', None)
+        if isinstance(atol, dict):
+            kwargs['atol'] = [atol[k] for k in self.free_names]
+        elif atol is not None and np.ndim(atol) == 1 and len(atol) == len(self.original_dep):
+            kwargs['atol'] = [atol[i] for i in self._keep_idx]
+        return super().integrate(*args, **kwargs)

@@ -8,7 +8,8 @@ import sympy as sp
 
 from pyodesys_b200 import systems
 from pyodesys_b200.native.cuda import NativeCudaSys
-from pyodesys_b200.transforms import TransformedSys, symmetricsys
+from pyodesys_b200.symbolic import SymbolicSys
+from pyodesys_b200.transforms import TransformedSys, symmetricsys, PartiallySolvedSystem, get_logexp
 
 _cache = {}
 
@@ -137,9 +138,33 @@ def loglog_robertson(compile=True):
     return _get(('loglog_robertson', compile), lambda: SS.from_callback(systems.robertson_f, 3, 3, compile=compile))
 
 
+def partsolved_loglog_decay3(multiple=False, compile=True):
+    """ ``_get_transformed_partially_solved_system`` (pyodesys/native/tests/_tests.py:136-153): decay3 with y0 (and
+    optionally y2) replaced by analytic expressions, then log-log transformed, then compiled """
+    def mk():
+        odesys = SymbolicSys.from_callback(decay3_rhs, 3, 3)
+        if multiple:
+            def substitutions(x0, y0, p0, be):
+                analytic0 = y0[0]*be.exp(-p0[0]*(odesys.indep - x0))
+                analytic2 = y0[0] + y0[1] + y0[2] - analytic0 - odesys.dep[1]
+                return {odesys.dep[0]: analytic0, odesys.dep[2]: analytic2}
+        else:
+            def substitutions(x0, y0, p0, be):
+                return {odesys.dep[0]: y0[0]*sp.exp(-p0[0]*(odesys.indep - x0))}
+        partsys = PartiallySolvedSystem(odesys, substitutions)
+        LogLogSys = symmetricsys(get_logexp(), get_logexp(), SuperClass=TransformedCudaSys)
+        return LogLogSys.from_other(partsys, compile=compile)
+    return _get(('partsolved_loglog_decay3', multiple, compile), mk)
+
+
+def partsolved_loglog_decay3_multi(compile=True):
+    return partsolved_loglog_decay3(True, compile)
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
-           nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson]
+           nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
+           partsolved_loglog_decay3_multi]
     return {f.__name__: f(compile=compile) for f in fns}
 
 

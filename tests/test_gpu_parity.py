@@ -591,3 +591,22 @@ def test_chunk_pipeline_is_invisible(cuda_device):
                        method='dopri5')
     for i in range(64):
         assert np.array_equal(ad[39000 + i].yout, ad1[i].yout) and ad[39000 + i].xout[-1] == 0.5
+
+
+@pytest.mark.parametrize('multiple', [False, True])
+def test_partially_solved_symmetric_native_multi(cuda_device, multiple):
+    """ G7: ``_test_PartiallySolved_symmetric_native(_multi)`` (pyodesys/native/tests/_tests.py:156-185): decay3 with
+    analytic y0 (and y2), log-log transformed, N = 4 per-system (y0, k); Bateman + mass conservation """
+    trnsfsys = tsys.partsolved_loglog_decay3(multiple)
+    y0s = [[3., 2., 1.], [3.1, 2.1, 1.1], [3.2, 2.3, 1.2], [3.6, 2.4, 1.3]]
+    ks = [[3.5, 2.5, 0], [3.3, 2.4, 0], [3.2, 2.1, 0], [3.3, 2.4, 0]]
+    kw = dict(atol=1e-8, rtol=1e-8, nsteps=2000)
+    results = trnsfsys.integrate([(1e-10, 1)]*len(ks), y0s, ks, **kw)
+    for i, (y0, k) in enumerate(zip(y0s, ks)):
+        xout, yout, info = results[i]
+        ref = bateman_full(y0, k, xout - xout[0])
+        assert info['success'] and info['nfev'] > 10 and info['time_cpu'] < 100
+        assert yout.shape[1] == 3 and np.allclose(yout, ref, atol=2e-7, rtol=2e-7)
+        assert np.allclose(np.sum(yout, axis=1), sum(y0), atol=2e-7, rtol=2e-7)
+    xout, yout, info = trnsfsys.integrate([1e-10, 1], y0s[0], ks[0], **kw)
+    assert info['success'] and np.allclose(yout, bateman_full(y0s[0], ks[0], xout - xout[0]), atol=2e-7, rtol=2e-7)

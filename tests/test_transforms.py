@@ -9,8 +9,8 @@ import numpy as np
 import pytest
 import sympy as sp
 
-from pyodesys_b200 import (Result, ScaledSys, TransformedSys, integrate_auto_switch, integrate_chained,
-                           symmetricsys)
+from pyodesys_b200 import (PartiallySolvedSystem, Result, ScaledSys, SymbolicSys, TransformedSys, get_logexp,
+                           integrate_auto_switch, integrate_chained, symmetricsys)
 
 import systems_for_tests as tsys
 
@@ -110,3 +110,50 @@ def test_integrate_auto_switch_logic():
     assert r.info['nsys'] == 1 and not d.calls and np.array_equal(r.yout[:, 0], [5, 6, 7])
     with pytest.raises(NotImplementedError):
         integrate_auto_switch([c], {}, [0., 1., 2.], [5.], [1.])
+
+
+def test_partially_solved_system_processors():
+    """ PartiallySolvedSystem (pyodesys/symbolic.py:1134-1358): eliminated variables, appended initial values,
+    vectorised reconstruction; then stacked under a log-log transformation like the reference's native test """
+    odesys = SymbolicSys.from_callback(tsys.decay3_rhs, 3, 3)
+    x, (y0s, y1s, y2s), (k0, k1, k2) = odesys.indep, odesys.dep, odesys.params
+
+    def subs(x0, y0, p0, be):
+        a0 = y0[0]*be.exp(-p0[0]*(x - x0))
+        return {y0s: a0, y2s: y0[0] + y0[1] + y0[2] - a0 - y1s}
+    ps = PartiallySolvedSystem(odesys, subs)
+    assert ps.dep == (y1s,) and len(ps.params) == 3 + 1 + 3 and ps.ny == 1
+    px0, py0 = ps.params[3], ps.params[4]
+    assert sp.simplify(ps.exprs[0] - (k0*py0*sp.exp(-k0*(x - px0)) - k1*y1s)) == 0
+    X = np.array([[0., 1, 2], [1., 2, 3]])
+    Y0 = np.array([[3., 2, 1], [4., 5, 6]])
+    P = np.array([[3.5, 2.5, 0], [1., 2, 0]])
+    xi, yi, pi = ps.pre_process(X, Y0, P)
+    assert np.array_equal(yi, Y0[:, 1:2]) and np.array_equal(pi, np.concatenate((P, X[:, :1], Y0), axis=1))
+    yint = np.full((2, 3, 1), 1.5)
+    xo, yo, po = ps.post_process(xi, yint, np.concatenate((pi, yi), axis=1))  # internal rows carry appended iv
+    a0 = Y0[:, :1]*np.exp(-P[:, :1]*(X - X[:, :1]))
+    assert np.allclose(yo[..., 0], a0) and np.allclose(yo[..., 1], 1.5)
+    assert np.allclose(yo.sum(axis=-1), Y0.sum(axis=1, keepdims=True)) and np.array_equal(po, P)
+    xo1, yo1, po1 = ps.post_process(xi[1], yint[1], np.concatenate((pi, yi), axis=1)[1])
+    assert np.array_equal(yo1, yo[1]) and np.array_equal(po1, P[1])
+    # per-component atol refers to the original variables
+    assert ps._keep_idx == [1] and ps._analytic_idx == [0, 2]
+    ts = tsys.partsolved_loglog_decay3(True, compile=False)
+    assert ts.ny == 1 and len(ts.pre_processors) == 2 and len(ts.post_processors) == 2
+    xi, yi, pi = ts.pre_process(np.array([[1e-10, 1.]]*2), Y0, P)
+    assert np.allclose(xi, np.log([[1e-10, 1.]]*2)) and np.allclose(yi, np.log(Y0[:, 1:2]))
+    assert np.allclose(pi, np.concatenate((P, [[1e-10]]*2, Y0), axis=1))
+    with pytest.raises(ValueError):
+        PartiallySolvedSystem(odesys, lambda x0, y0, p0: {})
+
+
+def test_from_linear_invariants():
+    """ mass conservation A + B + C = const removes one variable (pyodesys/symbolic.py:1275-1336) """
+    from pyodesys_b200 import systems
+    rob = SymbolicSys.from_callback(systems.robertson_f, 3, 3, linear_invariants=[[1, 1, 1]])
+    red = PartiallySolvedSystem.from_linear_invariants(rob, preferred=[2])
+    A, B, C = rob.dep
+    assert red.dep == (A, B) and red.linear_invariants is None
+    iv = red.params[4:]
+    assert sp.simplify(red.analytic_exprs[C] - (iv[2] - (A - iv[0]) - (B - iv[1]))) == 0
