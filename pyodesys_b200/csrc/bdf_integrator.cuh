@@ -60,24 +60,32 @@ template <> struct Stepper<M_BDF> {
     }
     __device__ __forceinline__ double &Dx(int j, int i) { return Dsm[(j * NY + i) * dstride]; }
     double Jm[NY * NY];
-    RegArr<NY * NY> W;
+    RegArr<NY * NY> W;  // factors of I - c Jm (ny == 3: its explicit inverse, see lin_factor in integrators.cuh)
     int piv[NY];
-    double d[NY], scale[NY];
-    double h_cur, c_lu, atol_[NY], rtol_, newton_tol;
-    float safety;
+    double d[NY];
+    float iscale[NY];   // 1 / (atol_i + rtol |y_i|): the norms only steer Newton and the step size -> fp32
+    double h_cur, c_lu, atol_[NY], rtol_;
+    float newton_tol, safety;
     int order, n_equal;
     bool have_lu, jac_current, fresh, newton_failed;
 
     __device__ __forceinline__ double alpha(int k) const { return (1.0 - kBdfKappa[k]) * kBdfGamma[k]; }
     __device__ __forceinline__ double errconst(int k) const { return fma(kBdfKappa[k], kBdfGamma[k], 1.0 / (k + 1)); }
-    __device__ __forceinline__ double rms(const double *v) const {
-        double s = 0.0;
+    __device__ __forceinline__ void set_scale(const double *y) {
+#pragma unroll
+        for (int i = 0; i < NY; ++i) iscale[i] = rcp_ftz(fmaxf((float)fma(rtol_, fabs(y[i]), atol_[i]), 1e-37f));
+    }
+    // weighted rms norm in single precision (sqrt.approx: one MUFU instead of the IEEE sqrt subroutine)
+    __device__ __forceinline__ float rms(const double *v) const {
+        float s = 0.0f;
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            const double q = v[i] * fast_rcp<1>(scale[i]);
-            s = fma(q, q, s);
+            const float q = (float)v[i] * iscale[i];
+            s = fmaf(q, q, s);
         }
-        return sqrt(s * (1.0 / NY));
+        float r;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s * (1.0f / NY)));
+        return r;
     }
     __device__ __forceinline__ int eval_jac(Sys &sys, double t, const double *y) {
         BdfSink sink{Jm};
@@ -90,7 +98,7 @@ template <> struct Stepper<M_BDF> {
         rtol_ = bdfc::TOL_FACTOR * tol.rtol;
 #pragma unroll
         for (int i = 0; i < NY; ++i) atol_[i] = bdfc::TOL_FACTOR * tol.atol[i];
-        newton_tol = fmax(10.0 * DBL_EPSILON / rtol_, fmin(0.03, sqrt(rtol_)));
+        newton_tol = (float)fmax(10.0 * DBL_EPSILON / rtol_, fmin(0.03, sqrt(rtol_)));
         order = 1;
         n_equal = 0;
         have_lu = false;
@@ -181,14 +189,15 @@ template <> struct Stepper<M_BDF> {
 #pragma unroll
             for (int j = 1; j <= bdfc::MAXORD; ++j) {
                 if (j <= order) {
-                    s += Dx(j, i);
-                    ps = fma(kBdfGamma[j], Dx(j, i), ps);
+                    const double dj = Dx(j, i);
+                    s += dj;
+                    ps = fma(kBdfGamma[j], dj, ps);
                 }
             }
             ypred[i] = s;
             psi[i] = ps * ialpha;
-            scale[i] = fma(rtol_, fabs(s), atol_[i]);
         }
+        set_scale(ypred);
         const double c = h * ialpha;
         bool converged = false;
         int n_iter = 0;
@@ -202,14 +211,14 @@ template <> struct Stepper<M_BDF> {
                 for (int r = 0; r < NY; ++r)
 #pragma unroll
                     for (int q = 0; q < NY; ++q) W[r * NY + q] = fma(-c, Jm[r * NY + q], r == q ? 1.0 : 0.0);
-                const bool ok = lu_factor<NY, false>(W, piv);
+                const bool ok = lin_factor<false>(W, piv, rtol_, cnt);
                 cnt.nlu += 1;
                 c_lu = c;
                 have_lu = ok;
                 if (!ok) return 1;
             }
             double yk[NY], f[NY], dy[NY];
-            double dy_norm_old = -1.0;
+            float nrm_old = -1.0f;
 #pragma unroll
             for (int i = 0; i < NY; ++i) {
                 d[i] = 0.0;
@@ -218,31 +227,33 @@ template <> struct Stepper<M_BDF> {
             for (int k = 0; k < bdfc::NEWTON_MAXITER; ++k) {
                 n_iter = k + 1;
                 const int st = eval_rhs(sys, a, tnew, yk, f);
-                if (st != 0 || !finite_all(f)) break;
+                if (st != 0) break;
 #pragma unroll
                 for (int i = 0; i < NY; ++i) dy[i] = fma(c, f[i], -psi[i]) - d[i];
-                lu_solve<NY, false>(W, piv, dy);
+                lin_solve<false>(W, piv, dy);
                 cnt.nsolve += 1;
-                const double dy_norm = rms(dy);
-                double rate = -1.0;
-                if (dy_norm_old >= 0.0) rate = dy_norm / dy_norm_old;
-                if (rate >= 0.0) {
-                    // rate^(MAXITER - k) / (1 - rate) * dy_norm > tol  -> will not converge in time
-                    double rp = rate;
+                const float nrm = rms(dy);
+                if (!(nrm <= 3.0e38f)) break;  // NaN / inf from the rhs
+                // contraction rate of the simplified Newton iteration; the tests are the usual ones
+                // (rate >= 1, or rate^(MAXITER-k)/(1-rate) |dy| > tol: will not converge in time) without divisions
+                float rate = -1.0f;
+                if (nrm_old >= 0.0f) rate = nrm * rcp_ftz(nrm_old);
+                if (rate >= 0.0f) {
+                    float rp = rate;
                     if (k <= 2) rp *= rate;
                     if (k <= 1) rp *= rate;
-                    if (rate >= 1.0 || rp / (1.0 - rate) * dy_norm > newton_tol) break;
+                    if (rate >= 1.0f || rp * nrm > newton_tol * (1.0f - rate)) break;
                 }
 #pragma unroll
                 for (int i = 0; i < NY; ++i) {
                     yk[i] += dy[i];
                     d[i] += dy[i];
                 }
-                if (dy_norm == 0.0 || (rate >= 0.0 && rate / (1.0 - rate) * dy_norm < newton_tol)) {
+                if (nrm == 0.0f || (rate >= 0.0f && rate * nrm < newton_tol * (1.0f - rate))) {
                     converged = true;
                     break;
                 }
-                dy_norm_old = dy_norm;
+                nrm_old = nrm;
             }
             if (converged) {
 #pragma unroll
@@ -263,10 +274,10 @@ template <> struct Stepper<M_BDF> {
             return 0;
         }
         safety = 0.9f * (2 * bdfc::NEWTON_MAXITER + 1) / (float)(2 * bdfc::NEWTON_MAXITER + n_iter);
-#pragma unroll
-        for (int i = 0; i < NY; ++i) scale[i] = fma(rtol_, fabs(ynew[i]), atol_[i]);
-        err = errconst(order) * rms(d);
-        if (!(err <= DBL_MAX)) return 1;
+        set_scale(ynew);
+        const float ef = (float)errconst(order) * rms(d);
+        if (!(ef <= 3.0e38f) || !finite_all(ynew)) return 1;
+        err = (double)ef;
         return 0;
     }
     __device__ __forceinline__ bool control(double err, double, double &hnext, double h) {
@@ -323,12 +334,12 @@ template <> struct Stepper<M_BDF> {
         const float inf = __int_as_float(0x7f800000);
         float fm = -1.0f, fp = -1.0f;
         if (order > 1) {
-            const double e = errconst(order - 1) * rms(vm);
-            fm = e == 0.0 ? inf : fast_powf(e, -1.0f / (float)order);
+            const float e = (float)errconst(order - 1) * rms(vm);
+            fm = e == 0.0f ? inf : fast_powf(e, -1.0f / (float)order);
         }
         if (order < bdfc::MAXORD) {
-            const double e = errconst(order + 1) * rms(vp);
-            fp = e == 0.0 ? inf : fast_powf(e, -1.0f / (float)(order + 2));
+            const float e = (float)errconst(order + 1) * rms(vp);
+            fp = e == 0.0f ? inf : fast_powf(e, -1.0f / (float)(order + 2));
         }
         const float fc = err == 0.0 ? inf : fast_powf(err, -1.0f / (float)(order + 1));
         float best = fm;

@@ -117,6 +117,9 @@ __device__ __forceinline__ float rcp_ftz(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+__device__ __forceinline__ float fast_powf(float x, float e) {
+    return ex2_ftz(e * lg2_ftz(fminf(fmaxf(x, 1e-30f), 1e30f)));
+}
 __device__ __forceinline__ float fast_powf(double x, float e) {
     const float xf = fminf(fmaxf((float)x, 1e-30f), 1e30f);
     return ex2_ftz(e * lg2_ftz(xf));
@@ -496,6 +499,76 @@ __constant__ double kRos4[ros4c::NCOEF] = {
     0.2476722511418386e+02, -0.6594389125716872e+01};
 #define RC(name) kRos4[ros4c::name]
 
+// The linear algebra of one implicit step: one factorisation of W, several solves (six for Rosenbrock-4, one per
+// Newton iteration for BDF).
+//
+// ny == 3 (register kernel): W^-1 is formed explicitly and the six solves are 3x3 matrix-vector products
+// (9 independent FMAs, depth 3) instead of six permuted forward/back substitutions (9 FP64 + 12 selects each,
+// depth ~10): the serial substitution chains and the select-based row interchanges were the dominant
+// latency and issue-slot cost of the step (profiles/r1b_ros4_ncu_summary.md).  The inverse comes from the
+// cofactor formula when that is safe: the determinant's cancellation is measured (|det| against the sum of
+// the magnitudes of its three terms) and has to keep the relative error of W^-1 a factor 100 below rtol;
+// otherwise this lane falls back to the pivoted LU (AnyODE::getrf semantics) and builds W^-1 from three
+// unit-vector solves.  Either way an inaccurate W^-1 acts as a perturbed Jacobian (W-method): it costs
+// step size through the embedded error estimate, it does not corrupt accepted steps silently.
+#ifndef PYODESYS_ROS4_INV3
+#define PYODESYS_ROS4_INV3 1
+#endif
+template <bool BRANCH_SWAP, class Mat>
+__device__ __forceinline__ bool lin_factor(Mat &W, int *piv, double rtol, Counters &cnt) {
+    if constexpr (PYODESYS_ROS4_INV3 && NY == 3 && !BRANCH_SWAP) {
+        const double a00 = W[0], a01 = W[1], a02 = W[2], a10 = W[3], a11 = W[4], a12 = W[5], a20 = W[6],
+                     a21 = W[7], a22 = W[8];
+        const double c00 = fma(a11, a22, -a12 * a21), c01 = fma(a12, a20, -a10 * a22), c02 = fma(a10, a21, -a11 * a20);
+        const double t0 = a00 * c00, t1 = a01 * c01, t2 = a02 * c02;
+        const double det = t0 + t1 + t2;
+        const double mag = fabs(t0) + fabs(t1) + fabs(t2);
+        // eps * mag / |det| <= rtol / 100  (also false for det = 0, NaN, inf)
+        const bool safe = fabs(det) * rtol >= (100.0 * DBL_EPSILON) * mag && fabs(det) <= DBL_MAX && mag > 0.0;
+        bool ok = true;
+        if (__builtin_expect(!safe, 0)) {
+            ok = lu_factor<NY, false>(W, piv);
+            double e[NY], inv[NY * NY];
+#pragma unroll
+            for (int j = 0; j < NY; ++j) {
+#pragma unroll
+                for (int i = 0; i < NY; ++i) e[i] = (i == j) ? 1.0 : 0.0;
+                lu_solve<NY, false>(W, piv, e);
+#pragma unroll
+                for (int i = 0; i < NY; ++i) inv[i * NY + j] = e[i];
+            }
+#pragma unroll
+            for (int i = 0; i < NY * NY; ++i) W[i] = inv[i];
+            cnt.nsolve += NY;
+        } else {
+            const double r = fast_rcp<2>(det);
+            W[0] = c00 * r;
+            W[3] = c01 * r;
+            W[6] = c02 * r;
+            W[1] = fma(a02, a21, -a01 * a22) * r;
+            W[4] = fma(a00, a22, -a02 * a20) * r;
+            W[7] = fma(a01, a20, -a00 * a21) * r;
+            W[2] = fma(a01, a12, -a02 * a11) * r;
+            W[5] = fma(a02, a10, -a00 * a12) * r;
+            W[8] = fma(a00, a11, -a01 * a10) * r;
+        }
+        return ok;
+    } else {
+        return lu_factor<NY, BRANCH_SWAP>(W, piv);
+    }
+}
+template <bool BRANCH_SWAP, class Mat>
+__device__ __forceinline__ void lin_solve(const Mat &W, const int *piv, double *b) {
+    if constexpr (PYODESYS_ROS4_INV3 && NY == 3 && !BRANCH_SWAP) {
+        const double b0 = b[0], b1 = b[1], b2 = b[2];
+        b[0] = fma(W[0], b0, fma(W[1], b1, W[2] * b2));
+        b[1] = fma(W[3], b0, fma(W[4], b1, W[5] * b2));
+        b[2] = fma(W[6], b0, fma(W[7], b1, W[8] * b2));
+    } else {
+        lu_solve<NY, BRANCH_SWAP>(W, piv, b);
+    }
+}
+
 // ---- storage: everything in registers (ny <= ~8); larger systems use smem_integrators.cuh / group_integrators.cuh
 struct RegStore {
     typedef OdeSys Sys;
@@ -536,72 +609,11 @@ template <class Store> struct Ros4Stepper : Store {
         lg_err_old = 0.0f;
         return 0;
     }
-    // The linear algebra of one step: one factorisation of W, six solves.
-    //
-    // ny == 3 (register kernel): W^-1 is formed explicitly and the six solves are 3x3 matrix-vector products
-    // (9 independent FMAs, depth 3) instead of six permuted forward/back substitutions (9 FP64 + 12 selects each,
-    // depth ~10): the serial substitution chains and the select-based row interchanges were the dominant
-    // latency and issue-slot cost of the step (profiles/r1b_ros4_ncu_summary.md).  The inverse comes from the
-    // cofactor formula when that is safe: the determinant's cancellation is measured (|det| against the sum of
-    // the magnitudes of its three terms) and has to keep the relative error of W^-1 a factor 100 below rtol;
-    // otherwise this lane falls back to the pivoted LU (AnyODE::getrf semantics) and builds W^-1 from three
-    // unit-vector solves.  Either way an inaccurate W^-1 acts as a perturbed Jacobian (W-method): it costs
-    // step size through the embedded error estimate, it does not corrupt accepted steps silently.
-#ifndef PYODESYS_ROS4_INV3
-#define PYODESYS_ROS4_INV3 1
-#endif
-    static constexpr bool kInv3 = PYODESYS_ROS4_INV3 && NY == 3 && !Store::kBranchSwap;
     template <class Mat> __device__ __forceinline__ bool lin_factor(Mat &W, int *piv, double rtol, Counters &cnt) {
-        if constexpr (kInv3) {
-            const double a00 = W[0], a01 = W[1], a02 = W[2], a10 = W[3], a11 = W[4], a12 = W[5], a20 = W[6],
-                         a21 = W[7], a22 = W[8];
-            const double c00 = fma(a11, a22, -a12 * a21), c01 = fma(a12, a20, -a10 * a22), c02 = fma(a10, a21, -a11 * a20);
-            const double t0 = a00 * c00, t1 = a01 * c01, t2 = a02 * c02;
-            const double det = t0 + t1 + t2;
-            const double mag = fabs(t0) + fabs(t1) + fabs(t2);
-            // eps * mag / |det| <= rtol / 100  (also false for det = 0, NaN, inf)
-            const bool safe = fabs(det) * rtol >= (100.0 * DBL_EPSILON) * mag && fabs(det) <= DBL_MAX && mag > 0.0;
-            bool ok = true;
-            if (__builtin_expect(!safe, 0)) {
-                ok = lu_factor<NY, false>(W, piv);
-                double e[NY], inv[NY * NY];
-#pragma unroll
-                for (int j = 0; j < NY; ++j) {
-#pragma unroll
-                    for (int i = 0; i < NY; ++i) e[i] = (i == j) ? 1.0 : 0.0;
-                    lu_solve<NY, false>(W, piv, e);
-#pragma unroll
-                    for (int i = 0; i < NY; ++i) inv[i * NY + j] = e[i];
-                }
-#pragma unroll
-                for (int i = 0; i < NY * NY; ++i) W[i] = inv[i];
-                cnt.nsolve += NY;
-            } else {
-                const double r = fast_rcp<2>(det);
-                W[0] = c00 * r;
-                W[3] = c01 * r;
-                W[6] = c02 * r;
-                W[1] = fma(a02, a21, -a01 * a22) * r;
-                W[4] = fma(a00, a22, -a02 * a20) * r;
-                W[7] = fma(a01, a20, -a00 * a21) * r;
-                W[2] = fma(a01, a12, -a02 * a11) * r;
-                W[5] = fma(a02, a10, -a00 * a12) * r;
-                W[8] = fma(a00, a11, -a01 * a10) * r;
-            }
-            return ok;
-        } else {
-            return lu_factor<NY, Store::kBranchSwap>(W, piv);
-        }
+        return pyodesys_cuda::lin_factor<Store::kBranchSwap>(W, piv, rtol, cnt);
     }
     template <class Mat> __device__ __forceinline__ void lin_solve(const Mat &W, const int *piv, double *b) {
-        if constexpr (kInv3) {
-            const double b0 = b[0], b1 = b[1], b2 = b[2];
-            b[0] = fma(W[0], b0, fma(W[1], b1, W[2] * b2));
-            b[1] = fma(W[3], b0, fma(W[4], b1, W[5] * b2));
-            b[2] = fma(W[6], b0, fma(W[7], b1, W[8] * b2));
-        } else {
-            lu_solve<NY, Store::kBranchSwap>(W, piv, b);
-        }
+        pyodesys_cuda::lin_solve<Store::kBranchSwap>(W, piv, b);
     }
     __device__ __forceinline__ void auto_step(Sys &sys, const KernelArgs &a, const Tol &tol, double t,
                                               const double *y, double span, double &h) {
@@ -757,7 +769,10 @@ template <> struct Stepper<M_ROS4> : Ros4Stepper<RegStore> {};  // instantiated 
 #define PYODESYS_MIN_BLOCKS (ODESYS_NY <= 4 ? 4 : 1)
 #endif
 // BDF carries 8 difference vectors + J + LU per lane: give it the full register file (2 blocks of 128 per SM)
-#define PYODESYS_MIN_BLOCKS_FOR(METHOD) ((METHOD) == M_BDF ? (ODESYS_NY <= 4 ? 2 : 1) : PYODESYS_MIN_BLOCKS)
+#ifndef PYODESYS_BDF_MIN_BLOCKS
+#define PYODESYS_BDF_MIN_BLOCKS (ODESYS_NY <= 4 ? 3 : 1)
+#endif
+#define PYODESYS_MIN_BLOCKS_FOR(METHOD) ((METHOD) == M_BDF ? PYODESYS_BDF_MIN_BLOCKS : PYODESYS_MIN_BLOCKS)
 template <int METHOD, int MODE, int BLOCK>
 __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integrate_kernel(const KernelArgs a) {
     using St = Stepper<METHOD>;

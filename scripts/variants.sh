@@ -8,6 +8,6 @@ while IFS= read -r flags; do
   if [ "$mode" = build ]; then
     python -c "from pyodesys_b200 import systems; s=systems.robertson(compile=True); from oracle import build_oracle; build_oracle(s._native); print(repr('$flags'), s._native.tag)"
   else
-    C3_METHODS=rosenbrock4 python scripts/bench_configs.py c3 --reps 3
+    C3_METHODS=${C3_METHODS:-rosenbrock4} python scripts/bench_configs.py c3 --reps 3
   fi
 done < "${VARIANTS_FILE:-scripts/variants.txt}"
