@@ -93,7 +93,7 @@ typedef struct pyodesys_cuda_options {
      * kernels take m_p[np + i] from y0[i] themselves: no O(N) host concatenation, ny*8 B less H2D per system. */
     int32_t iv_from_y0;
     int32_t params_ld;               /* leading dimension of ``params`` in doubles; 0 = dense rows */
-    int32_t kernel;                  /* Rosenbrock kernel family: 0 auto (1 for ny <= 16, else 2), 1 one system per
+    int32_t kernel;                  /* Rosenbrock kernel family: 0 auto (1 for ny <= 8, else 2), 1 one system per
                                         thread in registers, 2 one system per lane group (ny >= 6), 3 one system
                                         per thread with W / vectors / parameters in shared memory (ny >= 9) */
     int32_t reserved;

@@ -192,6 +192,101 @@ template <int G> __device__ __forceinline__ void g_lu_solve(const Grp<G> &g, con
     for (int r = 0; r < R; ++r) b[r] = x[r];
 }
 
+// ---- explicit inverse across the group ---------------------------------------------------------------------
+// The six triangular solve pairs of one Rosenbrock step are 2 x NY strictly serial shuffle -> FMA links each; with
+// two or three warps per scheduler that latency chain, not the FP64 pipe, set the speed of the kernel.  Instead W is
+// inverted in place by Gauss-Jordan elimination with the same partial (row) pivoting (pivot = largest |a_ik| among
+// the rows not used yet; rows never move, each row remembers the step it served as pivot in, ord[r]) and every
+// solve becomes R dot products of length NY per lane: NY independent FMAs per row, no shuffles.
+//   after the elimination  a[r][m] = (W^-1)[ord[r]][p_m],  p_m = row that was the pivot of step m
+//   x_k = sum_m a[r][m] * b[p_m]  for the row r with ord[r] = k
+// so the right-hand side is staged through shared memory in pivot order (bs[ord[r]] = b[r]) and the result
+// comes back through shared memory in variable order (xs[ord[r]] = x).  Costs 2x the FMAs of the LU but removes
+// ~170 dependent instructions per solve.
+#ifndef PYODESYS_GROUP_INVERSE
+#define PYODESYS_GROUP_INVERSE 1
+#endif
+template <int G> __device__ __forceinline__ bool g_invert(const Grp<G> &g, double (*a)[NY], int *ord) {
+    constexpr int R = Grp<G>::R;
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < R; ++r) ord[r] = g.owns(r) ? NY : -1;
+#pragma unroll
+    for (int k = 0; k < NY; ++k) {
+        int best = -1, bslot = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int hi = (ord[r] == NY) ? (__double2hiint(a[r][k]) & 0x7fffffff) : -1;
+            if (hi > best) {
+                best = hi;
+                bslot = r;
+            }
+        }
+        const int mx = __reduce_max_sync(g.mask, best);
+        const unsigned vote = __ballot_sync(g.mask, best == mx) & g.mask;
+        const int pl = __ffs(vote) - 1;
+        const int ps = __shfl_sync(g.mask, bslot, pl);
+        ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
+        const bool mine = ((int)(threadIdx.x & 31u) == pl);
+        // the owner scales its pivot row (row / pivot, reciprocal pivot on the diagonal) and publishes it
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (mine && r == ps) {
+                ord[r] = k;
+                const double d = fast_rcp<2>(a[r][k]);
+#pragma unroll
+                for (int j = 0; j < NY; ++j) {
+                    const double v = (j == k) ? d : a[r][j] * d;
+                    a[r][j] = v;
+                    g.prow[j] = v;
+                }
+            }
+        }
+        __syncwarp(g.mask);
+        // every other row (pivoted earlier or not yet) drops its column k
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool upd = (ord[r] != k);
+            const double l = upd ? a[r][k] : 0.0;
+#pragma unroll
+            for (int j = 0; j < NY; ++j) {
+                if (j == k) continue;
+                a[r][j] = fma(-l, g.prow[j], a[r][j]);
+            }
+            if (upd) a[r][k] = -l * g.prow[k];
+        }
+        __syncwarp(g.mask);
+    }
+    return ok;
+}
+
+// x = W^-1 b with the in-place inverse of g_invert; b distributed (slot r of lane gl = equation r*G + gl), the
+// solution comes back in the same layout.  Uses g.prow / g.ys as staging (both are free between rhs evaluations).
+template <int G> __device__ __forceinline__ void g_apply(const Grp<G> &g, const double (*a)[NY], const int *ord,
+                                                         double *b) {
+    constexpr int R = Grp<G>::R;
+    __syncwarp(g.mask);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (g.owns(r)) g.prow[ord[r]] = b[r];
+    __syncwarp(g.mask);
+    double acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+#pragma unroll
+    for (int m = 0; m < NY; ++m) {
+        const double bm = g.prow[m];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = fma(a[r][m], bm, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (g.owns(r)) g.ys[ord[r]] = acc[r];
+    __syncwarp(g.mask);
+#pragma unroll
+    for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? g.ys[r * G + g.gl] : 0.0;
+}
+
 // ---- Rosenbrock 4(3) on a lane group (same coefficients/controller as Stepper<M_ROS4>) -------------------
 #define RC(name) kRos4[ros4c::name]
 template <int G> struct GroupRos4 {
@@ -267,12 +362,19 @@ template <int G> struct GroupRos4 {
         for (int r = 0; r < R; ++r)
 #pragma unroll
             for (int j = 0; j < NY; ++j) W[r][j] = ((r * G + g.gl == j) ? diag : 0.0) - W[r][j];
+#if PYODESYS_GROUP_INVERSE
+        if (!g_invert<G>(g, W, ord)) bad |= 1;
+        AnyODE::ignore(piv);
+#define G_SOLVE(vec) g_apply<G>(g, W, ord, vec)
+#else
         if (!g_lu_factor<G>(g, W, ord, piv)) bad |= 1;
+#define G_SOLVE(vec) g_lu_solve<G>(g, W, ord, piv, vec)
+#endif
         cnt.nlu += 1;
         cnt.nsolve += 6;
 #pragma unroll
         for (int r = 0; r < R; ++r) g1[r] = ODESYS_AUTONOMOUS ? f[r] : fma(h * RC(D1), dfdt[r], f[r]);
-        g_lu_solve<G>(g, W, ord, piv, g1);
+        G_SOLVE(g1);
 #pragma unroll
         for (int r = 0; r < R; ++r) tmp[r] = fma(RC(A21), g1[r], y[r]);
         bad |= g_rhs<G>(g, sys, a, fma(RC(C2X), h, t), tmp, f);
@@ -282,7 +384,7 @@ template <int G> struct GroupRos4 {
             g2[r] = fma(c21, g1[r], f[r]);
             if (!ODESYS_AUTONOMOUS) g2[r] = fma(h * RC(D2), dfdt[r], g2[r]);
         }
-        g_lu_solve<G>(g, W, ord, piv, g2);
+        G_SOLVE(g2);
 #pragma unroll
         for (int r = 0; r < R; ++r) tmp[r] = fma(RC(A32), g2[r], fma(RC(A31), g1[r], y[r]));
         bad |= g_rhs<G>(g, sys, a, fma(RC(C3X), h, t), tmp, f);
@@ -291,7 +393,7 @@ template <int G> struct GroupRos4 {
             g3[r] = fma(ih, fma(RC(C32), g2[r], RC(C31) * g1[r]), f[r]);
             if (!ODESYS_AUTONOMOUS) g3[r] = fma(h * RC(D3), dfdt[r], g3[r]);
         }
-        g_lu_solve<G>(g, W, ord, piv, g3);
+        G_SOLVE(g3);
 #pragma unroll
         for (int r = 0; r < R; ++r) tmp[r] = fma(RC(A43), g3[r], fma(RC(A42), g2[r], fma(RC(A41), g1[r], y[r])));
         bad |= g_rhs<G>(g, sys, a, fma(RC(C4X), h, t), tmp, f);
@@ -300,7 +402,7 @@ template <int G> struct GroupRos4 {
             g4[r] = fma(ih, fma(RC(C43), g3[r], fma(RC(C42), g2[r], RC(C41) * g1[r])), f[r]);
             if (!ODESYS_AUTONOMOUS) g4[r] = fma(h * RC(D4), dfdt[r], g4[r]);
         }
-        g_lu_solve<G>(g, W, ord, piv, g4);
+        G_SOLVE(g4);
 #pragma unroll
         for (int r = 0; r < R; ++r)
             tmp[r] = fma(RC(A54), g4[r], fma(RC(A53), g3[r], fma(RC(A52), g2[r], fma(RC(A51), g1[r], y[r]))));
@@ -308,7 +410,7 @@ template <int G> struct GroupRos4 {
 #pragma unroll
         for (int r = 0; r < R; ++r)
             g5[r] = fma(ih, fma(RC(C54), g4[r], fma(RC(C53), g3[r], fma(RC(C52), g2[r], RC(C51) * g1[r]))), f[r]);
-        g_lu_solve<G>(g, W, ord, piv, g5);
+        G_SOLVE(g5);
 #pragma unroll
         for (int r = 0; r < R; ++r) tmp[r] += g5[r];
         bad |= g_rhs<G>(g, sys, a, t + h, tmp, f);
@@ -316,7 +418,7 @@ template <int G> struct GroupRos4 {
         for (int r = 0; r < R; ++r)
             xerr[r] = fma(ih, fma(RC(C65), g5[r], fma(RC(C64), g4[r], fma(RC(C63), g3[r],
                                   fma(RC(C62), g2[r], RC(C61) * g1[r])))), f[r]);
-        g_lu_solve<G>(g, W, ord, piv, xerr);
+        G_SOLVE(xerr);
         double e = 0.0;
         bool finite = true;
 #pragma unroll
@@ -332,6 +434,7 @@ template <int G> struct GroupRos4 {
         err = (double)ef;
         if (!(ef <= 3e38f) || __any_sync(g.mask, !finite)) bad |= 1;
         return bad;
+#undef G_SOLVE
     }
 
     __device__ __forceinline__ bool control(double err, double &hnext, double h) {

@@ -166,10 +166,11 @@ template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t
 }
 #endif
 
-// Which kernel family integrates this call: 1 = one system per thread in registers, 2 = one system per
-// lane group, 3 = one system per thread with its arrays in shared memory.  Auto rule from measurements on
-// B200 (radiolysis ny = 14: family 1 105 ms, 2 113 ms, 3 198 ms per 1e5 systems; profiles/r1_c4_kernels.md):
-// family 1 while its spills stay moderate (ny <= 16), the lane-group kernel above.
+// Which kernel family integrates this call: 1 = one system per thread in registers, 2 = one system per lane
+// group, 3 = one system per thread with its arrays in shared memory.  Auto rule from measurements on B200
+// (radiolysis ny = 14, ms per 1e5 systems: lane group with in-place inverse 85, registers 104-140 (4.3 KB of spills
+// per thread), shared memory 198; profiles/r1_c4_kernels.md, r1e_c4_group_inverse.md): registers up to ny = 8, the
+// lane-group kernel above.
 int pick_kernel(int method, const pyodesys_cuda_options *opt) {
     const int want = opt ? opt->kernel : 0;
     if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3) ? -1 : 1;
@@ -178,7 +179,7 @@ int pick_kernel(int method, const pyodesys_cuda_options *opt) {
 #endif
 #if ODESYS_GROUP_KERNEL
     if (want == 2) return 2;
-    if (want == 0 && NY > 16) return 2;
+    if (want == 0 && NY > 8) return 2;
 #endif
     return (want == 0 || want == 1) ? 1 : -1;
 }
