@@ -342,6 +342,10 @@ def test_error_conventions(cuda_device):
     odes = systems.decay()
     with pytest.raises(ValueError, match="NaN found in y0"):
         odes.integrate([0, 1], [np.nan, 1], [1.0])
+    big = np.ones((40000, 2))  # large batches are screened by the kernel (status 3 before the first step)
+    big[31234, 1] = np.nan
+    with pytest.raises(ValueError, match="NaN found in y0"):
+        odes.integrate([0, 1], big, [[1.0]]*40000, force_predefined=True)
     with pytest.raises(ValueError, match="atol needs to be of length 1 or 2"):
         odes.integrate([0, 1], [1, 1], [1.0], atol=[1e-8, 1e-8, 1e-8])
     with pytest.raises(ValueError, match="incompatible kwargs integrator"):
