@@ -31,6 +31,7 @@
 #include <mutex>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 using namespace pyodesys_cuda;
@@ -288,14 +289,14 @@ int stage(DevCtx &c, Buf b, const void *src, size_t bytes, const void **dst) {
 // i+1 and the D2H copy of chunk i-1 overlap the kernel of chunk i, and because consecutive kernels sit on different
 // streams the blocks of chunk i+1 move onto the SMs as the persistent blocks of chunk i drain (the tail of one
 // chunk is filled by the head of the next).  Device buffers span the whole batch; a chunk is a window into them.
-// Whether to cut at all is decided by the bytes that cross PCIe per system: with a few hundred bytes (final state
-// only: C3, 128 B/system) the copies are ~10 % of the call and every extra kernel boundary costs more than that
-// in load balance (measured: 8 chunks of 125k Robertson systems 18.8 ms against 15.3 ms in one launch); with
-// dense output (C2: 2.4 KB/system, D2H 47 ms against a 33 ms kernel) the pipeline hides the kernel behind D2H.
+// How many chunks: every chunk boundary costs load balance (measured on C3: ~0.6 ms per boundary, a chunk's
+// persistent blocks drain while the next chunk's move in), every additional chunk hides more of the copies
+// (exposed copy time ~ T_copy / k).  Minimising T_copy / k + (k - 1) * 0.6 ms with T_copy = bytes / 50 GB/s gives
+// k = sqrt(bytes / 30 MB): C3 (1e6 systems, 128 MB) -> 2 chunks (17.15 -> 16.64 ms per call; 3 chunks 16.9, 4 chunks
+// 17.2, 8 chunks 21), C2 (1e6 trajectories x 100 samples, 2.5 GB, D2H 47 ms against a 33 ms kernel) -> 9 chunks.
 constexpr int kMaxChunks = 16;
 constexpr int64_t kMinChunk = 32768;
-constexpr size_t kPipelineBytesPerSystem = 512;
-constexpr size_t kChunkBytes = 32u << 20;
+constexpr double kBytesPerBoundary = 30e6;
 
 struct ChunkPlan {
     int nchunks;
@@ -308,9 +309,19 @@ ChunkPlan plan_chunks(int64_t n, size_t bytes_per_system) {
     ChunkPlan p;
     p.nchunks = 1;
     p.per = n;
-    if (bytes_per_system < kPipelineBytesPerSystem) return p;
-    int64_t per = (int64_t)(kChunkBytes / bytes_per_system);
-    if (per * kMaxChunks < n) per = (n + kMaxChunks - 1) / kMaxChunks;
+    // experiment knob: PYODESYS_CUDA_CHUNKS=k forces k equal chunks (k <= kMaxChunks)
+    if (const char *env = getenv("PYODESYS_CUDA_CHUNKS")) {
+        const int k = atoi(env);
+        if (k >= 1 && k <= kMaxChunks && n >= k) {
+            p.per = ((n + k - 1) / k + 1023) / 1024 * 1024;
+            p.nchunks = (int)((n + p.per - 1) / p.per);
+            return p;
+        }
+    }
+    int k = (int)(sqrt((double)n * (double)bytes_per_system / kBytesPerBoundary) + 0.5);
+    if (k > kMaxChunks) k = kMaxChunks;
+    if (k <= 1) return p;
+    int64_t per = (n + k - 1) / k;
     if (per < kMinChunk) per = kMinChunk;
     per = (per + 1023) / 1024 * 1024;
     if (per >= n) return p;

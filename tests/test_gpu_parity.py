@@ -579,12 +579,12 @@ def test_chunk_pipeline_is_invisible(cuda_device):
     """ output-heavy batches are cut into chunks that alternate between two streams (H2D / kernel / D2H overlap);
     systems are independent, so every row must equal the row of an un-chunked call bit for bit """
     lo = systems.lorenz()
-    n = 100000  # 100 samples x 3 doubles per system -> 4 chunks of 32768 rows
+    n = 100000  # 100 samples x 3 doubles per system = 250 MB -> 3 chunks of 33792 rows
     b = systems.batch_lorenz(n=n, nt=100)
     kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'], method='dopri5')
     full = lo.integrate(b['x'], b['y0'], b['params'], **kw)
     assert (full.info.status == 0).all() and (full.info.nreached == 100).all()
-    for sl in (slice(0, 5000), slice(32768 - 100, 32768 + 100), slice(n - 3000, n)):
+    for sl in (slice(0, 5000), slice(33792 - 100, 33792 + 100), slice(n - 3000, n)):
         part = lo.integrate(b['x'], b['y0'][sl], b['params'][sl], **kw)
         assert np.array_equal(part.yout, full.yout[sl])
         assert np.array_equal(part.info.counters, full.info.counters[:, sl])
