@@ -43,7 +43,7 @@
 extern "C" {
 #endif
 
-#define PYODESYS_CUDA_ABI_VERSION 2
+#define PYODESYS_CUDA_ABI_VERSION 3
 
 /* integration methods (``method=`` keyword of the reference wrappers) */
 #define PYODESYS_CUDA_RK4 0        /* fixed step classical Runge-Kutta (pyodesys/integrators.py:17-61) */
@@ -78,7 +78,9 @@ extern "C" {
  * the generated OdeSys (odesys_anyode_template.cpp:92-98) plus launch controls. */
 typedef struct pyodesys_cuda_options {
     double get_dx_max_factor;        /* <=0: ignore OdeSys::get_dx_max (default 0) */
-    double max_invariant_violation;  /* reserved (0 = off) */
+    double max_invariant_violation;  /* != 0: rhs returns a recoverable error (step retried with h/4) when an
+                                        invariant of the system leaves |I - I(x0)| <= v (v > 0: absolute; v < 0:
+                                        |v I(x0)| - v), odesys_anyode_template.cpp:112-123,191-198 */
     int32_t error_outside_bounds;    /* nonzero: rhs outside bounds -> recoverable error */
     int32_t xout_shared;             /* nonzero: ``xout`` is ONE row [nt] shared by all systems */
     int32_t schedule;                /* 0 auto, 1 static (grid-stride), 2 dynamic (work stealing) */
@@ -96,7 +98,17 @@ typedef struct pyodesys_cuda_options {
     int32_t kernel;                  /* Rosenbrock kernel family: 0 auto (1 for ny <= 8, else 2), 1 one system per
                                         thread in registers, 2 one system per lane group (ny >= 6), 3 one system
                                         per thread with W / vectors / parameters in shared memory (ny >= 9) */
+    /* ABI v3.  Event functions: OdeSys::roots (odesys_anyode_template.cpp:377-396), consumed by the cvode wrapper
+     * (``return_on_root``, ``root_indices``, ``root_out``: _cvode_wrapper.pyx:89,206-213,354-355).  Sign changes of
+     * the nroots functions are located on the dense output of each accepted step to 100 eps (|x| + |h|).  The three
+     * arrays follow ptr_kind like every other array; max_roots == 0 (or a system without roots) switches it off. */
+    int32_t return_on_root;          /* adaptive mode: the first root ends the integration; its row is the last one */
+    int32_t max_roots;               /* capacity per system of root_out / root_indices */
     int32_t reserved;
+    double *root_out;                /* [n, max_roots, 1 + ny]: rows (x_root, y(x_root)) */
+    int32_t *root_indices;           /* [n, max_roots]: adaptive: the row of xyout that holds the root;
+                                        predefined: index of the first output point at or behind the root */
+    int32_t *nroots_found;           /* [n]: roots met (may exceed max_roots; only the first max_roots are stored) */
 } pyodesys_cuda_options;
 
 /* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */

@@ -121,7 +121,23 @@ class OracleModule:
             ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_int64, _d, _i32, _i32, _i32,
             ctypes.c_int]
         lib.oracle_eval.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _d, _d]
+        lib.oracle_set_extras.argtypes = [ctypes.c_double, ctypes.c_int, ctypes.c_int, _d, _i32, _i32]
         lib.oracle_lu_solve.argtypes = [ctypes.c_int64, _d, _d, _d, _i32]
+
+    def _extras(self, n, max_invariant_violation, return_on_root, max_roots, sink):
+        """ invariant guard / event functions for the next call; ``sink`` (a dict) receives the root arrays """
+        if sink is None or max_roots <= 0:
+            self.lib.oracle_set_extras(float(max_invariant_violation), 0, 0, None, None, None)
+            return
+        root_out = np.full((n, max_roots, 1 + self.ny), np.nan)
+        root_indices = np.zeros((n, max_roots), dtype=np.int32)
+        nfound = np.zeros(n, dtype=np.int32)
+        self.lib.oracle_set_extras(float(max_invariant_violation), int(bool(return_on_root)), int(max_roots),
+                                   _p(root_out), _p(root_indices, _i32), _p(nfound, _i32))
+        sink.update(root_out=root_out, root_indices=root_indices, nroots_found=nfound, max_roots=int(max_roots))
+
+    def _reset_extras(self):
+        self.lib.oracle_set_extras(0.0, 0, 0, None, None, None)
 
     def max_threads(self):
         return int(self.lib.oracle_max_threads())
@@ -135,9 +151,11 @@ class OracleModule:
 
     def integrate_predefined(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                              mxsteps=0, method='rosenbrock4', autorestart=0, get_dx_max_factor=0.0,
-                             error_outside_bounds=False, nthreads=0):
+                             error_outside_bounds=False, nthreads=0, max_invariant_violation=0.0,
+                             max_roots=0, roots_sink=None):
         y0 = np.ascontiguousarray(y0, dtype=np.float64)
         n = y0.shape[0]
+        self._extras(n, max_invariant_violation, False, max_roots, roots_sink)
         xout = np.ascontiguousarray(xout, dtype=np.float64)
         shared = xout.ndim == 1
         nt = xout.shape[-1]
@@ -155,15 +173,18 @@ class OracleModule:
             _p(dx_min), _p(dx_max), int(mxsteps), METHODS[method], int(autorestart), float(get_dx_max_factor),
             int(error_outside_bounds), _p(yout), _p(nreached, _i32), _p(status, _i32), _p(counters, _i32),
             int(nthreads))
+        self._reset_extras()
         if rc != 0:
             raise RuntimeError("oracle: unsupported method")
         return yout, nreached, status, counters
 
     def integrate_adaptive(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                            mxsteps=0, method='rosenbrock4', autorestart=0, get_dx_max_factor=0.0,
-                           error_outside_bounds=False, max_rows=None, nthreads=0):
+                           error_outside_bounds=False, max_rows=None, nthreads=0, max_invariant_violation=0.0,
+                           return_on_root=False, max_roots=0, roots_sink=None):
         y0 = np.ascontiguousarray(y0, dtype=np.float64)
         n = y0.shape[0]
+        self._extras(n, max_invariant_violation, return_on_root, max_roots, roots_sink)
         x0 = np.ascontiguousarray(np.broadcast_to(np.asarray(x0, dtype=np.float64), (n,)))
         xend = np.ascontiguousarray(np.broadcast_to(np.asarray(xend, dtype=np.float64), (n,)))
         params = np.ascontiguousarray(params, dtype=np.float64).reshape(n, self.np_tot)
@@ -173,6 +194,8 @@ class OracleModule:
         dx0, dx_min, dx_max = (self._opt(v, n) for v in (dx0, dx_min, dx_max))
         if max_rows is None:
             max_rows = (int(mxsteps) if mxsteps else 500)*(1 + int(autorestart)) + 1
+            if roots_sink is not None:
+                max_rows += max_roots
         xyout = np.empty((n, max_rows, 1 + self.ny))
         nrows = np.empty(n, dtype=np.int32)
         status = np.empty(n, dtype=np.int32)
@@ -182,6 +205,7 @@ class OracleModule:
             _p(dx_max), int(mxsteps), METHODS[method], int(autorestart), float(get_dx_max_factor),
             int(error_outside_bounds), int(max_rows), _p(xyout), _p(nrows, _i32), _p(status, _i32),
             _p(counters, _i32), int(nthreads))
+        self._reset_extras()
         if rc != 0:
             raise RuntimeError("oracle: unsupported method")
         return xyout, nrows, status, counters

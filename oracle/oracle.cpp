@@ -50,7 +50,14 @@ struct Settings {
     double atol[NY];
     double get_dx_max_factor;
     int error_outside_bounds;
+    // set through oracle_set_extras (apply to the calls that follow)
+    double max_invariant_violation;
+    int return_on_root, max_roots;
+    double *root_out;       // [n, max_roots, 1 + NY]
+    int32_t *root_indices;  // [n, max_roots]
+    int32_t *nroots_found;  // [n]
 };
+Settings g_extras = {};
 
 struct Work {
     OdeSys sys;
@@ -62,6 +69,9 @@ struct Work {
         sys.nfev = nfev0 + 1;  // every call counts (template:161 increments before the checks)
 #if ODESYS_HAS_BOUNDS
         if (cfg->error_outside_bounds && sys.outside_bounds(y)) st = 1;
+#endif
+#if ODESYS_NINVAR > 0
+        if (sys.invariant_violated(x, y)) st = 1;  // template:191-198
 #endif
 #if ODESYS_NONNEGATIVE
         for (int i = 0; i < NY; ++i)
@@ -654,6 +664,72 @@ StepperBase *make_stepper(int method) {
     }
 }
 
+// ---- event functions (OdeSys::roots, template:377-396) ---------------------------------------------
+// Sign changes of g over an accepted step are located on the stepper's dense output by a bracketing secant
+// iteration with Illinois weights (the scheme documented for CVODE's rootfinding: tolerance
+// 100 eps (|t| + |h|), earliest secant root drives, upper bracket end is reported).
+#if ODESYS_NROOTS > 0
+constexpr int NROOTS = ODESYS_NROOTS;
+bool crossed(double from, double to) { return from != 0.0 && (to == 0.0 || (from < 0.0) != (to < 0.0)); }
+
+struct RootEvent {
+    double theta;  // position inside the step, 1.0 = its end
+    double x;
+    double y[NY];
+    double g[NROOTS];
+};
+
+// first root in (lo, 1] given g at lo (g_lo) and at the end of the step (g_hi); false if there is none
+bool first_root(Work &w, StepperBase *st, double t, double hh, double tnew, const double *y, const double *ynew,
+                double lo, const double *g_lo, const double *g_hi, RootEvent *ev) {
+    bool any = false;
+    for (int r = 0; r < NROOTS; ++r) any = any || crossed(g_lo[r], g_hi[r]);
+    if (!any) return false;
+    const double ttol = 100.0 * DBL_EPSILON * (std::fabs(t) + std::fabs(hh)) / std::fabs(hh);
+    double ta = lo, tb = 1.0;
+    vec ga(g_lo, g_lo + NROOTS), gb(g_hi, g_hi + NROOTS), yb(ynew, ynew + NY), ym(NY), gm(NROOTS);
+    double alpha = 1.0;
+    int side = 0, sideprev = -1;
+    for (int it = 0; it < 200 && (tb - ta) > ttol; ++it) {
+        int imax = -1;
+        double best = -1.0;
+        for (int r = 0; r < NROOTS; ++r)
+            if (crossed(ga[r], gb[r])) {
+                const double frac = std::fabs(gb[r] / (gb[r] - ga[r]));
+                if (frac > best) {
+                    best = frac;
+                    imax = r;
+                }
+            }
+        alpha = (sideprev == side) ? ((side == 2) ? alpha * 2.0 : alpha * 0.5) : 1.0;
+        double tm = tb - (tb - ta) * gb[imax] / (gb[imax] - alpha * ga[imax]);
+        const double width = tb - ta, fracint = width / ttol, fracsub = fracint > 5.0 ? 0.1 : 0.5 / fracint;
+        if (!(std::fabs(tm - ta) >= 0.5 * ttol)) tm = ta + fracsub * width;
+        if (!(std::fabs(tb - tm) >= 0.5 * ttol)) tm = tb - fracsub * width;
+        st->dense(tm, y, ynew, ym.data());
+        w.sys.roots(std::fma(tm, hh, t), ym.data(), gm.data());
+        bool chg = false;
+        for (int r = 0; r < NROOTS; ++r) chg = chg || crossed(ga[r], gm[r]);
+        sideprev = side;
+        if (chg) {
+            tb = tm;
+            gb = gm;
+            yb = ym;
+            side = 1;
+        } else {
+            ta = tm;
+            ga = gm;
+            side = 2;
+        }
+    }
+    ev->theta = tb;
+    ev->x = (tb == 1.0) ? tnew : std::fma(tb, hh, t);
+    std::copy(yb.begin(), yb.end(), ev->y);
+    std::copy(gb.begin(), gb.end(), ev->g);
+    return true;
+}
+#endif
+
 struct Job {
     int64_t n;
     int nt;
@@ -697,6 +773,16 @@ void run_one(const Job &J, const Settings &cfg, int method, int mode, int64_t s)
     const int64_t budget = J.mxsteps > 0 ? J.mxsteps : std::numeric_limits<int64_t>::max();
     int64_t steps_left = budget;
     int restarts = J.autorestart, nfail = 0, nsteps = 0, nreject = 0;
+#if ODESYS_NINVAR > 0
+    w.sys.init_invariants(cfg.max_invariant_violation, t, y);
+#endif
+#if ODESYS_NROOTS > 0
+    double g_old[NROOTS];
+    int n_roots = 0;
+    const bool find_roots = cfg.max_roots > 0;
+    if (find_roots) w.sys.roots(t, y, g_old);
+#endif
+    bool stop_at_root = false;
     int bad0 = st->begin(w, t, y);
     double h = J.dx0 ? J.dx0[s] : 0.0;
 #if ODESYS_HAS_FIRST_STEP
@@ -765,6 +851,49 @@ void run_one(const Job &J, const Settings &cfg, int method, int mode, int64_t s)
             if (status >= 0) break;
             continue;
         }
+#if ODESYS_NROOTS > 0
+        if (find_roots) {
+            double g_hi[NROOTS], g_lo[NROOTS];
+            w.sys.roots(tnew, ynew, g_hi);
+            std::memcpy(g_lo, g_old, sizeof(g_lo));
+            double lo = 0.0;
+            RootEvent ev;
+            for (int found = 0; found < 16 && !stop_at_root; ++found) {
+                if (!first_root(w, st, t, hh, tnew, y, ynew, lo, g_lo, g_hi, &ev)) break;
+                const bool at_end = ev.theta == 1.0;
+                int idx = k_out;
+                if (mode == 0)
+                    while (idx < J.nt && (xo[idx] - ev.x) * dir < 0.0) idx += 1;
+                const bool stored = n_roots < cfg.max_roots;
+                if (stored) {
+                    double *ro = cfg.root_out + (s * cfg.max_roots + n_roots) * (1 + NY);
+                    ro[0] = ev.x;
+                    for (int i = 0; i < NY; ++i) ro[1 + i] = ev.y[i];
+                    cfg.root_indices[s * cfg.max_roots + n_roots] = idx;
+                }
+                n_roots += 1;
+                if (mode == 1 && cfg.return_on_root) {
+                    tnew = ev.x;
+                    std::memcpy(ynew, ev.y, sizeof(ev.y));
+                    stop_at_root = true;
+                } else if (mode == 1 && !at_end && stored) {
+                    if (k_out >= J.max_rows) {
+                        status = ST_ROWS;
+                        break;
+                    }
+                    double *row = J.xyout + (s * J.max_rows + k_out) * (1 + NY);
+                    row[0] = ev.x;
+                    for (int i = 0; i < NY; ++i) row[1 + i] = ev.y[i];
+                    k_out += 1;
+                }
+                lo = ev.theta;
+                std::memcpy(g_lo, ev.g, sizeof(g_lo));
+                if (at_end) break;
+            }
+            std::memcpy(g_old, g_hi, sizeof(g_hi));
+            if (status >= 0) break;
+        }
+#endif
         if (mode == 0) {
             while (k_out < J.nt) {
                 const double xk = xo[k_out];
@@ -788,10 +917,17 @@ void run_one(const Job &J, const Settings &cfg, int method, int mode, int64_t s)
         }
         st->accepted();
         std::memcpy(y, ynew, sizeof(y));
-        t = hits_end ? tend : tnew;
+        t = (hits_end && !stop_at_root) ? tend : tnew;
         if (st->adaptive()) h = hnext;
+        if (stop_at_root) {
+            status = ST_OK;
+            break;
+        }
     }
     J.status[s] = status;
+#if ODESYS_NROOTS > 0
+    if (find_roots) cfg.nroots_found[s] = n_roots;
+#endif
     if (mode == 0) {
         J.nreached[s] = k_out;
         if (status != ST_OK)
@@ -825,6 +961,12 @@ Settings make_settings(const double *atol, int natol, double rtol, double get_dx
     for (int i = 0; i < NY; ++i) c.atol[i] = atol[natol == 1 ? 0 : i];
     c.get_dx_max_factor = get_dx_max_factor;
     c.error_outside_bounds = eob;
+    c.max_invariant_violation = g_extras.max_invariant_violation;
+    c.return_on_root = g_extras.return_on_root;
+    c.max_roots = (ODESYS_NROOTS > 0 && g_extras.root_out) ? g_extras.max_roots : 0;
+    c.root_out = g_extras.root_out;
+    c.root_indices = g_extras.root_indices;
+    c.nroots_found = g_extras.nroots_found;
     return c;
 }
 
@@ -835,6 +977,19 @@ extern "C" {
 int oracle_info(int *ny, int *np_tot) {
     *ny = NY;
     *np_tot = NP_TOT;
+    return 0;
+}
+
+// Options outside the positional signatures: invariant guard and event functions.  They stay in force for
+// the integrate calls that follow (reset with zeros / NULL).
+int oracle_set_extras(double max_invariant_violation, int return_on_root, int max_roots, double *root_out,
+                      int32_t *root_indices, int32_t *nroots_found) {
+    g_extras.max_invariant_violation = max_invariant_violation;
+    g_extras.return_on_root = return_on_root;
+    g_extras.max_roots = max_roots;
+    g_extras.root_out = root_out;
+    g_extras.root_indices = root_indices;
+    g_extras.nroots_found = nroots_found;
     return 0;
 }
 

@@ -86,6 +86,7 @@ class BatchInfo:
         self.nt = nt
         self.timings = timings or {}
         self.method = method
+        self.roots = None  # event-function outputs (root_out / root_indices / nroots_found arrays), if any
 
     @property
     def params(self):
@@ -126,6 +127,9 @@ class BatchInfo:
         d['internal_params'] = self.params[i, ...]
         if self.method is not None:
             d['method'] = self.method
+        if self.roots:
+            from .native.cuda import root_info
+            d.update(root_info(self.roots, i, self.mode))
         return d
 
     def __iter__(self):

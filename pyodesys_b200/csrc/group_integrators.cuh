@@ -89,6 +89,9 @@ template <int G> __device__ __forceinline__ int g_rhs(const Grp<G> &g, OdeSysRef
 #if ODESYS_HAS_BOUNDS
     if (a.error_outside_bounds && sys.outside_bounds(g.ys)) st = AnyODE::Status::recoverable_error;
 #endif
+#if ODESYS_NINVAR > 0
+    if (sys.invariant_violated(x, g.ys)) st = AnyODE::Status::recoverable_error;  // every lane: same y, same verdict
+#endif
 #if ODESYS_NONNEGATIVE
 #pragma unroll
     for (int i = 0; i < NY; ++i)
@@ -567,6 +570,14 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
                 hmax = a.dx_max ? a.dx_max[s] : INFINITY;
                 if (!(hmax > 0.0)) hmax = INFINITY;
                 steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
+#if ODESYS_NINVAR > 0
+                __syncwarp(g.mask);
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (g.owns(r)) g.ys[r * G + g.gl] = y[r];
+                __syncwarp(g.mask);
+                sys.init_invariants(a.max_invariant_violation, t, g.ys);
+#endif
                 st.begin();
                 h = a.dx0 ? a.dx0[s] : 0.0;
 #if ODESYS_HAS_FIRST_STEP

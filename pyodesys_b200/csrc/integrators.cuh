@@ -55,6 +55,13 @@ struct KernelArgs {
     int autorestart;
     double get_dx_max_factor;
     int error_outside_bounds;
+    double max_invariant_violation;  // != 0: rhs reports a recoverable error when an invariant drifts (template:191-198)
+    // event functions (OdeSys::roots, template:377-396): located on the dense output of every accepted step
+    int max_roots;          // capacity per system of root_out / root_indices (0 = no root finding)
+    int return_on_root;     // adaptive mode: the first root ends the integration (its row is the last one)
+    double *root_out;       // [n, max_roots, 1 + NY]: (x_root, y(x_root))
+    int32_t *root_indices;  // [n, max_roots]: adaptive: row of xyout; predefined: index of the next output point
+    int32_t *nroots_found;  // [n]
     // outputs
     double *yout;           // predefined: [n, nt, NY]  (or [nt, NY, n] when yout_soa)
     int yout_soa;
@@ -153,6 +160,9 @@ __device__ __forceinline__ AnyODE::Status eval_rhs(Sys &sys, const KernelArgs &a
     sys.nfev = nfev0 + 1;
 #if ODESYS_HAS_BOUNDS
     if (a.error_outside_bounds && sys.outside_bounds(y)) st = AnyODE::Status::recoverable_error;
+#endif
+#if ODESYS_NINVAR > 0
+    if (sys.invariant_violated(x, y)) st = AnyODE::Status::recoverable_error;
 #endif
 #if ODESYS_NONNEGATIVE
 #pragma unroll
@@ -763,6 +773,138 @@ template <> struct Stepper<M_ROS4> : Ros4Stepper<RegStore> {};  // instantiated 
 #endif  // ODESYS_HAS_JAC
 
 // ----------------------------------------------------------------------------------------------
+// Event functions (OdeSys::roots, odesys_anyode_template.cpp:377-396; consumers _cvode_wrapper.pyx:89,206-213,
+// 354-355).  After every accepted step the signs of g(t, y) at both ends are compared; a change is located on the
+// step's dense output with a bracketing secant iteration (Illinois weights, the scheme CVODE's rootfinding
+// documents: tolerance 100 eps (|t| + |h|), the component whose secant root is earliest drives the iteration, the
+// reported root is the upper end of the final bracket).  Several roots inside one step are found in order.
+// ----------------------------------------------------------------------------------------------
+#if ODESYS_NROOTS > 0
+constexpr int NROOTS = ODESYS_NROOTS;
+__device__ __forceinline__ bool root_crossed(double g_from, double g_to) {
+    return g_from != 0.0 && (g_to == 0.0 || (g_from < 0.0) != (g_to < 0.0));
+}
+
+// Returns true when the integration has to stop at a root (return_on_root): tnew / ynew are then the root.
+template <int MODE, class St, class Sys>
+__device__ __noinline__ bool locate_roots(St &st, Sys &sys, const KernelArgs &a, int64_t s, double t, double hh,
+                                          double &tnew, const double *y, double *ynew, double *g_old, int &n_roots,
+                                          int &k_out, double dir, int &status) {
+    double g_lo[NROOTS], g_hi[NROOTS];
+    sys.roots(tnew, ynew, g_hi);
+#pragma unroll
+    for (int r = 0; r < NROOTS; ++r) g_lo[r] = g_old[r];
+    double lo = 0.0;
+    bool stop = false;
+    const double ttol = 100.0 * DBL_EPSILON * (fabs(t) + fabs(hh)) / fabs(hh);  // in units of the step
+    for (int found = 0; found < 16 && !stop; ++found) {
+        bool any = false;
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) any = any || root_crossed(g_lo[r], g_hi[r]);
+        if (!any) break;
+        double ta = lo, tb = 1.0, ga[NROOTS], gb[NROOTS], yb[NY];
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) {
+            ga[r] = g_lo[r];
+            gb[r] = g_hi[r];
+        }
+#pragma unroll
+        for (int i = 0; i < NY; ++i) yb[i] = ynew[i];
+        double alpha = 1.0;
+        int side = 0, sideprev = -1;
+        for (int it = 0; it < 200 && (tb - ta) > ttol; ++it) {
+            double best = -1.0, gai = 0.0, gbi = 0.0;
+#pragma unroll
+            for (int r = 0; r < NROOTS; ++r)
+                if (root_crossed(ga[r], gb[r])) {
+                    const double frac = fabs(gb[r] / (gb[r] - ga[r]));
+                    if (frac > best) {
+                        best = frac;
+                        gai = ga[r];
+                        gbi = gb[r];
+                    }
+                }
+            if (sideprev == side) alpha = (side == 2) ? alpha * 2.0 : alpha * 0.5;
+            else alpha = 1.0;
+            double tm = tb - (tb - ta) * gbi / (gbi - alpha * gai);
+            const double width = tb - ta;
+            if (!(fabs(tm - ta) >= 0.5 * ttol)) {
+                const double fracint = width / ttol;
+                tm = ta + (fracint > 5.0 ? 0.1 : 0.5 / fracint) * width;
+            }
+            if (!(fabs(tb - tm) >= 0.5 * ttol)) {
+                const double fracint = width / ttol;
+                tm = tb - (fracint > 5.0 ? 0.1 : 0.5 / fracint) * width;
+            }
+            double ym[NY], gm[NROOTS];
+            st.dense(tm, hh, y, ynew, ym);
+            sys.roots(fma(tm, hh, t), ym, gm);
+            bool chg = false;
+#pragma unroll
+            for (int r = 0; r < NROOTS; ++r) chg = chg || root_crossed(ga[r], gm[r]);
+            sideprev = side;
+            if (chg) {
+                tb = tm;
+#pragma unroll
+                for (int r = 0; r < NROOTS; ++r) gb[r] = gm[r];
+#pragma unroll
+                for (int i = 0; i < NY; ++i) yb[i] = ym[i];
+                side = 1;
+            } else {
+                ta = tm;
+#pragma unroll
+                for (int r = 0; r < NROOTS; ++r) ga[r] = gm[r];
+                side = 2;
+            }
+        }
+        const bool at_end = (tb == 1.0);
+        const double x_root = at_end ? tnew : fma(tb, hh, t);
+        int idx = k_out;
+        if (MODE == 0) {
+            const double *xo = a.xout + s * a.xout_stride;
+            while (idx < a.nt && (xo[idx] - x_root) * dir < 0.0) idx += 1;
+        }
+        const bool stored = n_roots < a.max_roots;  // roots beyond the capacity are counted only
+        if (stored) {
+            double *ro = a.root_out + (s * a.max_roots + n_roots) * (1 + NY);
+            ro[0] = x_root;
+#pragma unroll
+            for (int i = 0; i < NY; ++i) ro[1 + i] = yb[i];
+            a.root_indices[s * a.max_roots + n_roots] = idx;
+        }
+        n_roots += 1;
+        if (MODE == 1 && a.return_on_root) {
+            // the root becomes the end of this (shortened) step; the driver writes its row and retires the system
+            tnew = x_root;
+#pragma unroll
+            for (int i = 0; i < NY; ++i) ynew[i] = yb[i];
+            stop = true;
+        } else if (MODE == 1 && !at_end && stored) {
+            if (k_out >= a.max_rows) {
+                status = ST_ROWS;
+                stop = true;
+            } else {
+                double *row = a.xyout + (s * a.max_rows + k_out) * (1 + NY);
+                row[0] = x_root;
+#pragma unroll
+                for (int i = 0; i < NY; ++i) row[1 + i] = yb[i];
+                k_out += 1;
+            }
+        }
+        // continue behind the root: components that crossed have their new sign (or are exactly zero and stay
+        // disarmed until they leave zero)
+        lo = tb;
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) g_lo[r] = gb[r];
+        if (at_end) break;
+    }
+#pragma unroll
+    for (int r = 0; r < NROOTS; ++r) g_old[r] = g_hi[r];
+    return stop && status < 0;
+}
+#endif  // ODESYS_NROOTS
+
+// ----------------------------------------------------------------------------------------------
 // The persistent kernel.  MODE 0: predefined output points, MODE 1: every accepted step.
 // ----------------------------------------------------------------------------------------------
 #ifndef PYODESYS_MIN_BLOCKS
@@ -773,7 +915,9 @@ template <> struct Stepper<M_ROS4> : Ros4Stepper<RegStore> {};  // instantiated 
 #define PYODESYS_BDF_MIN_BLOCKS (ODESYS_NY <= 4 ? 3 : 1)
 #endif
 #define PYODESYS_MIN_BLOCKS_FOR(METHOD) ((METHOD) == M_BDF ? PYODESYS_BDF_MIN_BLOCKS : PYODESYS_MIN_BLOCKS)
-template <int METHOD, int MODE, int BLOCK>
+// GUARD: compiled with the invariant test of rhs (max_invariant_violation != 0); the unguarded instantiation is the
+// one every other call runs (the test costs 3.6 % on C3 even when it is switched off at run time).
+template <int METHOD, int MODE, int BLOCK, bool GUARD = false>
 __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integrate_kernel(const KernelArgs a) {
     using St = Stepper<METHOD>;
     const unsigned lane = threadIdx.x & 31u;
@@ -798,6 +942,10 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
     int restarts = 0, nfail = 0;
     Counters cnt = {0, 0, 0, 0};
     bool active = false, exhausted = false;
+#if ODESYS_NROOTS > 0
+    double g_old[NROOTS];
+    int n_roots = 0;
+#endif
 
     for (;;) {
         // ---- (A) fetch a new system for every idle lane ---------------------------------------
@@ -857,6 +1005,14 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                 hmax = a.dx_max ? a.dx_max[s] : INFINITY;
                 if (!(hmax > 0.0)) hmax = INFINITY;
                 steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
+#if ODESYS_NINVAR > 0
+                // GUARD = false: the limit is the literal 0 and the tests inside eval_rhs fold away
+                sys.init_invariants(GUARD ? a.max_invariant_violation : 0.0, t, y);
+#endif
+#if ODESYS_NROOTS > 0
+                n_roots = 0;
+                if (a.max_roots > 0) sys.roots(t, y, g_old);
+#endif
                 int bad = st.begin(sys, a, tol, t, y);
                 h = a.dx0 ? a.dx0[s] : 0.0;
 #if ODESYS_HAS_FIRST_STEP
@@ -960,6 +1116,11 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                 // x_next is tested from a register; everything an output needs (the address of the xout row, the
                 // dense-output vectors) stays inside this branch - the compiler used to hoist the loop invariant
                 // dense-output arithmetic (30 FP64 instructions for ny = 3) in front of the test, i.e. into every step.
+                bool stop_at_root = false;
+#if ODESYS_NROOTS > 0
+                if (a.max_roots > 0)
+                    stop_at_root = locate_roots<MODE>(st, sys, a, s, t, hh, tnew, y, ynew, g_old, n_roots, k_out, dir, status);
+#endif
                 if (MODE == 0 && (x_next - tnew) * dir <= 0.0) {
                     const double *xo = a.xout + s * a.xout_stride;
                     while (k_out < a.nt) {
@@ -998,8 +1159,9 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
 #pragma unroll
                 for (int i = 0; i < NY; ++i) y[i] = ynew[i];
                 t = tnew;
-                if (hits_end) t = tend;
+                if (hits_end && !stop_at_root) t = tend;
                 if (St::kAdaptive) h = hnext;  // a fixed-step method keeps its nominal step
+                if (stop_at_root && status < 0) status = ST_OK;
             }
         }
 
@@ -1020,6 +1182,9 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
             } else {
                 a.nrows[s] = k_out;
             }
+#if ODESYS_NROOTS > 0
+            if (a.max_roots > 0) a.nroots_found[s] = n_roots;
+#endif
             if (a.counters) {
                 a.counters[C_NSTEPS * a.counters_ld + s] = cnt.nsteps;
                 a.counters[C_NFEV * a.counters_ld + s] = sys.nfev;

@@ -61,7 +61,7 @@ constexpr int kMaxDev = 64;
 #endif
 constexpr int kBlock = PYODESYS_BLOCK;
 
-enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, NBUF };
+enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, B_ROOTOUT, B_ROOTIDX, B_NROOTS, NBUF };
 
 struct DevCtx {
     std::mutex mtx;
@@ -105,7 +105,10 @@ int ensure(DevCtx &c, Buf b, size_t bytes) {
 }
 
 template <int METHOD, int MODE> int launch(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
-    auto kern = integrate_kernel<METHOD, MODE, kBlock>;
+    auto kern = integrate_kernel<METHOD, MODE, kBlock, false>;
+#if ODESYS_NINVAR > 0
+    if (a.max_invariant_violation != 0.0) kern = integrate_kernel<METHOD, MODE, kBlock, true>;
+#endif
     // steppers whose state is addressed dynamically (BDF difference table) keep it in shared memory
     const size_t smem = (size_t)Stepper<METHOD>::kSharedDoublesPerThread * kBlock * sizeof(double);
     if (smem > 48 * 1024) CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -174,6 +177,9 @@ template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t
 // lane-group kernel above.
 int pick_kernel(int method, const pyodesys_cuda_options *opt) {
     const int want = opt ? opt->kernel : 0;
+#if ODESYS_NROOTS > 0
+    if (want == 0 && opt && opt->max_roots > 0) return 1;  // roots are located by the thread kernels
+#endif
     if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3) ? -1 : 1;
 #if ODESYS_SMEM_KERNEL
     if (want == 3) return 3;
@@ -246,6 +252,16 @@ int check_common(const Common &q) {
     if (!q.status && q.n > 0) return fail("status is NULL");
     if (q.ptr_kind != 0 && q.ptr_kind != 1) return fail("ptr_kind must be 0 (host) or 1 (device)");
     if (!(q.rtol >= 0.0)) return fail("rtol must be non-negative");
+    if (ODESYS_NROOTS > 0 && q.opt && q.opt->max_roots > 0) {
+        if (!q.opt->root_out || !q.opt->root_indices || !q.opt->nroots_found)
+            return fail("max_roots > 0 needs root_out, root_indices and nroots_found");
+        if (pick_kernel(q.method, q.opt) != 1)
+            return fail("event functions are located by the one-system-per-thread kernels (ny <= 16): pass kernel=1");
+    }
+    if (q.opt && q.opt->max_invariant_violation != 0.0) {
+        if (ODESYS_NINVAR == 0) return fail("max_invariant_violation given but the system defines no invariants");
+        if (pick_kernel(q.method, q.opt) == 3) return fail("the shared-memory thread kernel has no invariant guard");
+    }
     return 0;
 }
 
@@ -261,7 +277,17 @@ void fill_args(KernelArgs &a, const Common &q) {
     a.params_ld = (q.opt && q.opt->params_ld > 0) ? q.opt->params_ld : (a.iv_from_y0 ? ODESYS_NPARAMS : NP_TOT);
     a.get_dx_max_factor = q.opt ? q.opt->get_dx_max_factor : 0.0;
     a.error_outside_bounds = q.opt ? q.opt->error_outside_bounds : 0;
+    a.max_invariant_violation = q.opt ? q.opt->max_invariant_violation : 0.0;
+#if ODESYS_NROOTS > 0
+    if (q.opt && q.opt->max_roots > 0) {
+        a.max_roots = q.opt->max_roots;
+        a.return_on_root = q.opt->return_on_root;
+    }
+#endif
 }
+
+// event-function outputs requested and available?
+bool want_roots(const Common &q) { return ODESYS_NROOTS > 0 && q.opt && q.opt->max_roots > 0; }
 
 bool want_dynamic(const Common &q) {
     const int sched = q.opt ? q.opt->schedule : 0;
@@ -382,7 +408,7 @@ int64_t pyodesys_cuda_query(const char *key) {
     const KV kv[] = {
         {"abi_version", PYODESYS_CUDA_ABI_VERSION}, {"ny", NY}, {"nparams", ODESYS_NPARAMS}, {"np_tot", NP_TOT},
         {"np_used", NP_USED}, {"npcse", ODESYS_NPCSE}, {"has_jac", ODESYS_HAS_JAC}, {"autonomous", ODESYS_AUTONOMOUS},
-        {"nroots", ODESYS_NROOTS}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
+        {"nroots", ODESYS_NROOTS}, {"ninvar", ODESYS_NINVAR}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
         {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
         {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL},
         {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF},
@@ -470,6 +496,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         if (opt && opt->stream) stream = (cudaStream_t)opt->stream;
         a.y0 = y0; a.params = params; a.xout = xout; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
         a.yout = yout; a.nreached = nreached; a.status = status; a.counters = counters;
+        if (want_roots(q)) { a.root_out = opt->root_out; a.root_indices = opt->root_indices; a.nroots_found = opt->nroots_found; }
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));
         if (dispatch<0>(c, a, method, stream, bps, opt)) return -1;
@@ -490,6 +517,11 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         ensure(c, B_YOUT, nn * nt * NY * 8) || ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4) ||
         (counters && ensure(c, B_COUNTERS, nn * NCOUNT * 4)) ||
         ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long)))
+        return -1;
+    const bool roots = want_roots(q);
+    const size_t root_row = roots ? (size_t)a.max_roots * (1 + NY) * 8 : 0;
+    if (roots && (ensure(c, B_ROOTOUT, nn * root_row) || ensure(c, B_ROOTIDX, nn * a.max_roots * 4) ||
+                  ensure(c, B_NROOTS, nn * 4)))
         return -1;
     const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + (shared_x ? 0 : nt) + (size_t)nt * NY) * 8 + 32);
     const bool dynamic = a.work_counter != nullptr;
@@ -520,6 +552,11 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         ak.counters = counters ? (int32_t *)c.buf[B_COUNTERS] + lo : nullptr;
         ak.counters_ld = n;
         ak.work_counter = dynamic ? (unsigned long long *)c.buf[B_WORK] + k : nullptr;
+        if (roots) {
+            ak.root_out = (double *)c.buf[B_ROOTOUT] + (size_t)lo * a.max_roots * (1 + NY);
+            ak.root_indices = (int32_t *)c.buf[B_ROOTIDX] + (size_t)lo * a.max_roots;
+            ak.nroots_found = (int32_t *)c.buf[B_NROOTS] + lo;
+        }
         if (k == 0) CU_CHECK(cudaEventRecord(c.ev_k0, st));
         if (dispatch<0>(c, ak, method, st, bps, opt)) return -1;
         if (k == plan.nchunks - 1) CU_CHECK(cudaEventRecord(c.ev_k1, st));
@@ -529,6 +566,10 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         if (counters)
             CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
                                        (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
+        if (roots && (d2h(c, B_ROOTOUT, opt->root_out, root_row, lo, len, st) ||
+                      d2h(c, B_ROOTIDX, opt->root_indices, (size_t)a.max_roots * 4, lo, len, st) ||
+                      d2h(c, B_NROOTS, opt->nroots_found, 4, lo, len, st)))
+            return -1;
     }
     CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
     CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
@@ -572,6 +613,7 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         if (opt && opt->stream) stream = (cudaStream_t)opt->stream;
         a.y0 = y0; a.params = params; a.x0 = x0; a.xend = xend; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
         a.xyout = xyout; a.nrows = nrows; a.status = status; a.counters = counters;
+        if (want_roots(q)) { a.root_out = opt->root_out; a.root_indices = opt->root_indices; a.nroots_found = opt->nroots_found; }
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));
         if (dispatch<1>(c, a, method, stream, bps, opt)) return -1;
@@ -591,6 +633,11 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         ensure(c, B_NREACHED, nn * 4) || ensure(c, B_STATUS, nn * 4) ||
         (counters && ensure(c, B_COUNTERS, nn * NCOUNT * 4)) ||
         ensure(c, B_WORK, kMaxChunks * sizeof(unsigned long long)))
+        return -1;
+    const bool roots = want_roots(q);
+    const size_t root_row = roots ? (size_t)a.max_roots * (1 + NY) * 8 : 0;
+    if (roots && (ensure(c, B_ROOTOUT, nn * root_row) || ensure(c, B_ROOTIDX, nn * a.max_roots * 4) ||
+                  ensure(c, B_NROOTS, nn * 4)))
         return -1;
     const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + 2) * 8 + row_bytes + 32);
     const bool dynamic = a.work_counter != nullptr;
@@ -622,6 +669,11 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         ak.counters = counters ? (int32_t *)c.buf[B_COUNTERS] + lo : nullptr;
         ak.counters_ld = n;
         ak.work_counter = dynamic ? (unsigned long long *)c.buf[B_WORK] + k : nullptr;
+        if (roots) {
+            ak.root_out = (double *)c.buf[B_ROOTOUT] + (size_t)lo * a.max_roots * (1 + NY);
+            ak.root_indices = (int32_t *)c.buf[B_ROOTIDX] + (size_t)lo * a.max_roots;
+            ak.nroots_found = (int32_t *)c.buf[B_NROOTS] + lo;
+        }
         if (k == 0) CU_CHECK(cudaEventRecord(c.ev_k0, st));
         if (dispatch<1>(c, ak, method, st, bps, opt)) return -1;
         if (k == plan.nchunks - 1) CU_CHECK(cudaEventRecord(c.ev_k1, st));
@@ -631,6 +683,10 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
         if (counters)
             CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
                                        (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
+        if (roots && (d2h(c, B_ROOTOUT, opt->root_out, root_row, lo, len, st) ||
+                      d2h(c, B_ROOTIDX, opt->root_indices, (size_t)a.max_roots * 4, lo, len, st) ||
+                      d2h(c, B_NROOTS, opt->nroots_found, 4, lo, len, st)))
+            return -1;
     }
     CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
     CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));

@@ -211,6 +211,9 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     if nroots:
         all_exprs += [be.sympify(r) for r in roots]
 
+    invar = [be.sympify(e) for e in odesys.all_invariants()] if hasattr(odesys, 'all_invariants') else []
+    ninvar = len(invar)
+
     xsym = be.Symbol('x')
     subsd = {k: be.Symbol('y[%d]' % i) for i, k in enumerate(odesys.dep)}
     if odesys.indep is not None:
@@ -352,6 +355,14 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     else:
         roots_body = '        return AnyODE::Status::success;'
 
+    # template:112-123,191-198 - invariants: values at the initial state, and the violation test of ``rhs``
+    if ninvar:
+        inv_cses, inv_exprs = cse_cb(invar, be.numbered_symbols('cse'))
+        invar_body = _body([(sy.name, cc(e)) for sy, e in inv_cses],
+                           [('out[%d]' % i, cc(e)) for i, e in enumerate(inv_exprs)], ret='')
+    else:
+        invar_body = ''
+
     lb = odesys.lower_bounds
     ub = odesys.upper_bounds
 
@@ -373,6 +384,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         ('ODESYS_FLOPS_PCSE', flops['pcse']), ('ODESYS_JAC_NNZ', jac_nnz),
         ('ODESYS_HAS_BOUNDS', int(lb is not None or ub is not None)),
         ('ODESYS_NONNEGATIVE', int(bool(getattr(odesys, '_nonnegative', False)))),
+        ('ODESYS_NINVAR', ninvar),
     ]
     struct_body = '''
     int nfev, njev;
@@ -425,7 +437,33 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(out);
 %(roots)s
     }
-''' % dict(bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
+#if ODESYS_NINVAR > 0
+    // template:112-123 (m_invar0 from the initial state) and :191-198 (violation -> recoverable error)
+    double m_invar0[ODESYS_NINVAR];
+    double m_max_invariant_violation;  // 0 = guard off (kernels instantiated without the guard only ever store 0)
+    ODESYS_FN void invariants(double x, const double * const y, double * const out) const {
+        AnyODE::ignore(x); AnyODE::ignore(y);
+%(invar)s
+    }
+    ODESYS_FN void init_invariants(double max_violation, double x, const double * const y) {
+        m_max_invariant_violation = max_violation;
+        if (max_violation != 0.0) invariants(x, y, m_invar0);
+    }
+    ODESYS_FN bool invariant_violated(double x, const double * const y) const {
+        if (m_max_invariant_violation == 0.0) return false;
+        double cur[ODESYS_NINVAR];
+        invariants(x, y, cur);
+        bool bad = false;
+#pragma unroll
+        for (int i = 0; i < ODESYS_NINVAR; ++i) {
+            const double lim = (m_max_invariant_violation > 0) ? m_max_invariant_violation
+                : fabs(m_max_invariant_violation*m_invar0[i]) - m_max_invariant_violation;
+            if (fabs(cur[i] - m_invar0[i]) > lim) bad = true;
+        }
+        return bad;
+    }
+#endif
+''' % dict(invar=invar_body, bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
            rhs_sink=rhs_sink_body, jac_sink=jac_sink_body, fs=fs_body, dxmax=dxmax_body, roots=roots_body)
 
     text = '''// -*- mode: read-only -*-

@@ -58,7 +58,12 @@ class Options(ctypes.Structure):
                 ('iv_from_y0', ctypes.c_int32),
                 ('params_ld', ctypes.c_int32),
                 ('kernel', ctypes.c_int32),
-                ('reserved', ctypes.c_int32)]
+                ('return_on_root', ctypes.c_int32),
+                ('max_roots', ctypes.c_int32),
+                ('reserved', ctypes.c_int32),
+                ('root_out', ctypes.c_void_p),
+                ('root_indices', ctypes.c_void_p),
+                ('nroots_found', ctypes.c_void_p)]
 
 
 def cache_dir():
@@ -193,6 +198,8 @@ class CudaModule:
         self.pinned = PinnedPool(lib)
         self.nparams = int(self.query('nparams'))
         self.ny = int(self.query('ny'))
+        self.nroots = max(0, int(self.query('nroots')))
+        self.ninvar = max(0, int(self.query('ninvar')))
         self.np_tot = int(self.query('np_tot'))
         self.has_jac = bool(self.query('has_jac'))
 
@@ -259,7 +266,29 @@ class CudaModule:
         return Options(float(get_dx_max_factor or 0.0), float(max_invariant_violation or 0.0),
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
                        int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
-                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0)
+                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, 0,
+                       None, None, None)
+
+    def _root_buffers(self, opts, n, kw_roots):
+        """ Event functions (``roots=`` of the system): attach the three output arrays of ABI v3 to ``opts``.
+        ``kw_roots`` = (roots_sink, return_on_root, max_roots); the arrays are handed back through the sink. """
+        sink, return_on_root, max_roots = kw_roots
+        if sink is None or self.nroots == 0 or max_roots <= 0:
+            return None
+        root_out = self.pinned.empty((n, max_roots, 1 + self.ny), np.float64)
+        root_indices = self.pinned.empty((n, max_roots), np.int32)
+        nfound = self.pinned.empty((n,), np.int32)
+        opts.return_on_root = int(bool(return_on_root))
+        opts.max_roots = int(max_roots)
+        opts.root_out = root_out.ctypes.data
+        opts.root_indices = root_indices.ctypes.data
+        opts.nroots_found = nfound.ctypes.data
+        sink.update(root_out=root_out, root_indices=root_indices, nroots_found=nfound, max_roots=int(max_roots))
+        return sink
+
+    @staticmethod
+    def _pop_roots(kw):
+        return (kw.pop('roots_sink', None), kw.pop('return_on_root', False), int(kw.pop('max_roots', 8)))
 
     def integrate_predefined_arrays(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                     mxsteps=0, method=None, autorestart=0, return_on_error=False,
@@ -271,7 +300,9 @@ class CudaModule:
         if not shared and xout.shape[0] != n:
             raise ValueError("xout needs to be of shape (N, nt)")
         nt = xout.shape[-1]
+        kw_roots = self._pop_roots(kw)
         opts = self._options(xout_shared=shared, **kw)
+        self._root_buffers(opts, n, kw_roots)
         # outputs live in page-locked memory (D2H at PCIe speed); the blocks return to the pool when the
         # arrays are garbage collected
         yout = self.pinned.empty((n, nt, self.ny), np.float64) if out is None else out
@@ -301,7 +332,10 @@ class CudaModule:
             # a system can never produce more rows than steps it is allowed to take (+ the start)
             steps = int(mxsteps) if mxsteps else 500
             max_rows = steps*(1 + int(autorestart)) + 1
+        kw_roots = self._pop_roots(kw)
         opts = self._options(**kw)
+        if self._root_buffers(opts, n, kw_roots) is not None:
+            max_rows += kw_roots[2]  # every stored root is one more row
         xyout = self.pinned.empty((n, max_rows, 1 + self.ny), np.float64)
         nrows = self.pinned.empty((n,), np.int32)
         status = self.pinned.empty((n,), np.int32)
@@ -340,7 +374,7 @@ class CudaModule:
 
     # -- reference-shaped entry points --------------------------------------------------------
     @staticmethod
-    def _nfo(i, n, status, counters, timings, mode, nreached=None):
+    def _nfo(i, n, status, counters, timings, mode, nreached=None, roots=None):
         d = {k: int(counters[j, i]) for j, k in enumerate(BatchInfo.counter_names)}
         d['n_rhs_evals'] = d['nfev']
         d['dense_n_dls_jac_evals'] = d['njev']
@@ -350,27 +384,31 @@ class CudaModule:
         d['success'] = bool(status[i] == 0)
         if nreached is not None:
             d['nreached'] = int(nreached[i])
+        if roots:
+            d.update(root_info(roots, i, mode))
         return d
 
     def integrate_predefined(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                              mxsteps=0, method=None, autorestart=0, return_on_error=False, **kw):
+        roots = {}
         yout, nreached, status, counters, timings = self.integrate_predefined_arrays(
             y0, xout, params, atol, rtol, dx0, dx_min, dx_max, mxsteps, method, autorestart,
-            return_on_error, **kw)
+            return_on_error, roots_sink=roots, **kw)
         _raise_on_failure(status, return_on_error)
         n = yout.shape[0]
-        return yout, [self._nfo(i, n, status, counters, timings, 'predefined', nreached) for i in range(n)]
+        return yout, [self._nfo(i, n, status, counters, timings, 'predefined', nreached, roots) for i in range(n)]
 
     def integrate_adaptive(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                            mxsteps=0, method=None, autorestart=0, return_on_error=False, **kw):
+        roots = {}
         xyout, nrows, status, counters, timings = self.integrate_adaptive_arrays(
             y0, x0, xend, params, atol, rtol, dx0, dx_min, dx_max, mxsteps, method, autorestart,
-            return_on_error, **kw)
+            return_on_error, roots_sink=roots, **kw)
         _raise_on_failure(status, return_on_error)
         n = xyout.shape[0]
         xs = [xyout[i, :nrows[i], 0] for i in range(n)]
         ys = [xyout[i, :nrows[i], 1:] for i in range(n)]
-        return xs, ys, [self._nfo(i, n, status, counters, timings, 'adaptive') for i in range(n)]
+        return xs, ys, [self._nfo(i, n, status, counters, timings, 'adaptive', None, roots) for i in range(n)]
 
     # -- verification hooks -----------------------------------------------------------------
     def eval_rhs_jac(self, x, y, params, device=0, jac=True):
@@ -393,6 +431,17 @@ class CudaModule:
         ok = np.empty(n, dtype=np.int32)
         self._check(self.lib.pyodesys_cuda_lu_solve(device, n, _ptr(A), _ptr(b), _ptr(x), _ptr(ok, _i32)))
         return x, ok
+
+
+def root_info(roots, i, mode):
+    """ ``root_indices`` (and ``root_out`` in predefined mode) of system ``i`` as the cvode wrapper reports them
+    (``_cvode_wrapper.pyx:63-70,206-219,354-355``) """
+    k = min(int(roots['nroots_found'][i]), roots['max_roots'])
+    d = {'root_indices': [int(v) for v in roots['root_indices'][i, :k]]}
+    if mode == 'predefined':
+        d['root_out'] = np.array(roots['root_out'][i, :k])
+    d['n_root_evals'] = int(roots['nroots_found'][i])
+    return d
 
 
 def _check_nan_y0(y0, status):
@@ -520,6 +569,9 @@ class NativeCudaSys(SymbolicSys):
         y0 = np.ascontiguousarray(intern_y0, dtype=np.float64)
         params = np.ascontiguousarray(intern_p, dtype=np.float64)
         t0 = time.time()
+        roots = {}
+        if mod.nroots and not (devices is not None and len(devices) > 1):
+            kwargs['roots_sink'] = roots
         if devices is not None and len(devices) > 1:
             from ..multi import integrate_sharded
             binfo = integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol, rtol,
@@ -542,6 +594,7 @@ class NativeCudaSys(SymbolicSys):
             binfo = BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, intern_p,
                               return_on_error, nt=intern_x.shape[-1], timings=_tdict(timings), method=method, iv=iv)
         n = len(binfo)
+        binfo.roots = roots or None
         binfo.time_wall = binfo.timings.get('kernel', 0.0)/max(n, 1)
         binfo.time_cpu = (time.time() - t0)/max(n, 1)
         _raise_on_failure(binfo.status, return_on_error)

@@ -161,10 +161,82 @@ def partsolved_loglog_decay3_multi(compile=True):
     return partsolved_loglog_decay3(True, compile)
 
 
+def growth_root(compile=True):
+    """ ``_test_NativeSys__roots`` (``pyodesys/native/tests/_tests.py:262-273``): y' = y, root of y - e at x = 1 """
+    return _get(('growth_root', compile), lambda: NativeCudaSys.from_callback(
+        lambda t, y: [y[0]], 1, 0, roots_cb=lambda t, y, p, backend: [y[0] - backend.exp(1)], compile=compile))
+
+
+def chain3_rhs(x, y, p):
+    """ A -> B -> C of ``test_NativeSys__PartiallySolvedSystem__roots`` (``native/tests/test_cvode.py:153-176``) """
+    return [-p[0]*y[0], p[0]*y[0] - p[1]*y[1], p[1]*y[1]]
+
+
+def chain3_roots(idx, compile=True):
+    """ crossings y0 = y1, y0 = y2, y1 = y2 of the chain (reference x: 0.11299628, 0.20674119, 0.35418287) """
+    return _get(('chain3_roots', idx, compile), lambda: NativeCudaSys.from_callback(
+        chain3_rhs, 3, 2, compile=compile,
+        roots_cb=lambda x, y: ([y[0] - y[1]], [y[0] - y[2]], [y[1] - y[2]])[idx]))
+
+
+def chain3_roots_all(compile=True):
+    """ the three crossings as one system with nroots = 3 (several events per integration) """
+    return _get(('chain3_roots_all', compile), lambda: NativeCudaSys.from_callback(
+        chain3_rhs, 3, 2, compile=compile, roots_cb=lambda x, y: [y[0] - y[1], y[0] - y[2], y[1] - y[2]]))
+
+
+def chain3_roots_partsolved(idx, compile=True):
+    """ same crossings with y0 solved analytically (``PartiallySolvedSystem``), natively compiled """
+    def mk():
+        ori = SymbolicSys.from_callback(chain3_rhs, 3, 2,
+                                        roots_cb=lambda x, y: ([y[0] - y[1]], [y[0] - y[2]], [y[1] - y[2]])[idx])
+        psys = PartiallySolvedSystem(ori, lambda t0, xyz, par0, be: {
+            ori.dep[0]: xyz[0]*be.exp(-par0[0]*(ori.indep - t0))})
+        return NativeCudaSys.from_other(psys, compile=compile)
+    return _get(('chain3_roots_partsolved', idx, compile), mk)
+
+
+def chain3_roots_0(compile=True):
+    return chain3_roots(0, compile)
+
+
+def chain3_roots_1(compile=True):
+    return chain3_roots(1, compile)
+
+
+def chain3_roots_2(compile=True):
+    return chain3_roots(2, compile)
+
+
+def chain3_roots_partsolved_1(compile=True):
+    return chain3_roots_partsolved(1, compile)
+
+
+def leaky_invariant(compile=True):
+    """ A <-> B with a declared invariant A + B that the rhs does NOT conserve (a leak of rate p[2]):
+    ``max_invariant_violation`` turns the drift into recoverable errors -> the integration fails where
+    |A + B - (A0 + B0)| passes the limit (template:112-123,191-198). """
+    return _get(('leaky_invariant', compile), lambda: NativeCudaSys.from_callback(
+        lambda x, y, p: [-p[0]*y[0] + p[1]*y[1], p[0]*y[0] - p[1]*y[1] - p[2]*y[1]], 2, 3,
+        linear_invariants=[[1, 1]], compile=compile))
+
+
+def leaky_chain6(compile=True):
+    """ six species decay chain whose last species leaks away (rate p[5]) although sum(y) is declared invariant;
+    ny = 6 so that the lane-group kernel can run it too """
+    def rhs(x, y, p):
+        out = systems.decay_chain_rhs(x, y, p[:5])
+        out[5] = out[5] - p[5]*y[5]
+        return out
+    return _get(('leaky_chain6', compile), lambda: NativeCudaSys.from_callback(
+        rhs, 6, 6, linear_invariants=[[1]*6], compile=compile))
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
            nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
-           partsolved_loglog_decay3_multi]
+           partsolved_loglog_decay3_multi, growth_root, chain3_roots_0, chain3_roots_1, chain3_roots_2,
+           chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6]
     return {f.__name__: f(compile=compile) for f in fns}
 
 

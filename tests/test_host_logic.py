@@ -41,7 +41,7 @@ def test_c_abi_library_exports_every_declared_symbol():
             assert hasattr(lib, nm), nm
         lib.pyodesys_cuda_query.restype = ctypes.c_int64
         lib.pyodesys_cuda_query.argtypes = [ctypes.c_char_p]
-        assert lib.pyodesys_cuda_query(b'abi_version') == 2
+        assert lib.pyodesys_cuda_query(b'abi_version') == 3
         assert lib.pyodesys_cuda_query(b'ny') == sysobj.ny
         assert lib.pyodesys_cuda_query(b'np_tot') == len(sysobj.params) + sysobj.ny  # append_iv, core.py:410-411
         assert lib.pyodesys_cuda_query(b'no such key') == -1
