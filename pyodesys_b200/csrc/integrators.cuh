@@ -73,7 +73,37 @@ struct KernelArgs {
     int32_t *counters;      // [NCOUNT, counters_ld] or nullptr
     int64_t counters_ld;    // row length of ``counters`` (= n of the whole call; a chunk sees a column window)
     unsigned long long *work_counter;  // dynamic scheduling (nullptr = static grid-stride)
+    // Streaming host-pointer calls (one persistent launch, copies run underneath on a second stream):
+    const unsigned long long *ready;   // device word: inputs of systems [0, *ready) have arrived (nullptr: all of them)
+    unsigned int *slice_done;          // device [ceil(n / slice_len)]: retired systems per output slice (nullptr: off)
+    unsigned int *slice_flags;         // host-mapped [nslices]: set to 1 once a slice is complete and visible
+    int64_t slice_len;
 };
+
+// leader lane: block until the inputs of systems [0, hi) are in device memory
+__device__ __forceinline__ void wait_inputs(const unsigned long long *ready, unsigned long long hi) {
+    const volatile unsigned long long *r = ready;
+    if (*r < hi) {
+        const long long t0 = clock64();
+        while (*r < hi) {
+            __nanosleep(200);
+            if (clock64() - t0 > (1ll << 33)) __trap();  // ~4 s: the copy stream died; fail loudly instead of hanging
+        }
+    }
+    __threadfence();  // loads of the inputs stay behind the flag read
+}
+
+// a system of an output slice retired: the last one of the slice tells the host, which then copies the slice back
+__device__ __forceinline__ void slice_retire(const KernelArgs &a, int64_t s) {
+    __threadfence();  // this system's results before the count
+    const int64_t j = s / a.slice_len;
+    const int64_t lo = j * a.slice_len;
+    const unsigned int len = (unsigned int)((lo + a.slice_len > a.n ? a.n : lo + a.slice_len) - lo);
+    if (atomicAdd(a.slice_done + j, 1u) + 1u == len) {
+        __threadfence_system();
+        *(volatile unsigned int *)(a.slice_flags + j) = 1u;
+    }
+}
 
 struct Counters {
     int nsteps, nlu, nsolve, nreject;
@@ -954,7 +984,13 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
             if (need) {
                 const int leader = __ffs(need) - 1;
                 unsigned long long base = 0;
-                if ((int)lane == leader) base = atomicAdd(a.work_counter, (unsigned long long)__popc(need));
+                if ((int)lane == leader) {
+                    base = atomicAdd(a.work_counter, (unsigned long long)__popc(need));
+                    if (a.ready != nullptr && base < (unsigned long long)a.n) {
+                        const unsigned long long hi = base + (unsigned long long)__popc(need);
+                        wait_inputs(a.ready, hi < (unsigned long long)a.n ? hi : (unsigned long long)a.n);
+                    }
+                }
                 base = __shfl_sync(FULL_MASK, base, leader);
                 if (!active && !exhausted) s = (int64_t)base + __popc(need & ((1u << lane) - 1u));
             }
@@ -1193,6 +1229,7 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                 a.counters[C_NSOLVE * a.counters_ld + s] = cnt.nsolve;
                 a.counters[C_NREJECT * a.counters_ld + s] = cnt.nreject;
             }
+            if (a.slice_done != nullptr) slice_retire(a, s);
             active = false;
         }
     }

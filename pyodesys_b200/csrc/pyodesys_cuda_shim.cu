@@ -26,7 +26,9 @@
 #endif
 #include "pyodesys_cuda.h"
 
+#include <algorithm>
 #include <atomic>
+#include <thread>
 #include <chrono>
 #include <mutex>
 #include <stdarg.h>
@@ -61,7 +63,7 @@ constexpr int kMaxDev = 64;
 #endif
 constexpr int kBlock = PYODESYS_BLOCK;
 
-enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, B_ROOTOUT, B_ROOTIDX, B_NROOTS, NBUF };
+enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, B_ROOTOUT, B_ROOTIDX, B_NROOTS, B_READY, B_SLICEDONE, NBUF };
 
 struct DevCtx {
     std::mutex mtx;
@@ -73,7 +75,12 @@ struct DevCtx {
     void *buf[NBUF] = {};
     size_t cap[NBUF] = {};
     int sm_count = 0;
+    // streaming calls: pinned table of "systems ready" values (source of the 8-byte flag copies) and the
+    // host-mapped completion flags the kernel sets per output slice
+    unsigned long long *h_ready = nullptr;
+    unsigned int *h_flags = nullptr, *d_flags = nullptr;
 };
+constexpr int kMaxSlices = 64;
 DevCtx g_ctx[kMaxDev];
 
 int ctx_init(DevCtx &c, int device) {
@@ -89,6 +96,10 @@ int ctx_init(DevCtx &c, int device) {
     CU_CHECK(cudaEventCreate(&c.ev_k1));
     CU_CHECK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
+    CU_CHECK(cudaHostAlloc((void **)&c.h_ready, kMaxSlices * sizeof(unsigned long long), cudaHostAllocPortable));
+    CU_CHECK(cudaHostAlloc((void **)&c.h_flags, kMaxSlices * sizeof(unsigned int),
+                           cudaHostAllocPortable | cudaHostAllocMapped));
+    CU_CHECK(cudaHostGetDevicePointer((void **)&c.d_flags, c.h_flags, 0));
     c.ready = true;
     return 0;
 }
@@ -389,6 +400,38 @@ int pipeline_timings(DevCtx &c, double *timings, double t_begin) {
     return 0;
 }
 
+// ---- streaming host-pointer call (predefined mode, one-system-per-thread kernels, work stealing) ----------------
+// ONE persistent launch for the whole batch.  The inputs of the first slice are copied in front of the kernel; the
+// remaining slices follow on the second stream while the kernel runs, each one published through an 8-byte copy
+// into ``ready`` that the work-stealing leader lane waits for before it hands out indices beyond it.  Every retired
+// system counts into its output slice; the last one raises a host-mapped flag and the host thread (which is inside
+// this synchronous call anyway) then queues the D2H of that slice.  Compared with cutting the batch into separate
+// launches there is no drain/fill at chunk boundaries, and only the first H2D slice and the last D2H slice are
+// exposed (C3: 17.6 -> see DESIGN.md section 3).
+struct SlicePlan {
+    int64_t len;
+    int n;
+    int64_t lo(int j) const { return (int64_t)j * len; }
+    int64_t size(int j, int64_t total) const { return (j + 1) * len > total ? total - j * len : len; }
+};
+
+SlicePlan plan_slices(int64_t n, size_t out_bytes_per_system) {
+    int64_t len = (int64_t)((size_t)(16u << 20) / (out_bytes_per_system ? out_bytes_per_system : 1));
+    const int64_t lo = std::max<int64_t>(16384, (n + kMaxSlices - 1) / kMaxSlices), hi = (n + 7) / 8;
+    if (len > hi) len = hi;
+    if (len < lo) len = lo;
+    len = (len + 1023) / 1024 * 1024;
+    SlicePlan p;
+    p.len = len;
+    p.n = (int)((n + len - 1) / len);
+    return p;
+}
+
+bool streaming_enabled() {
+    const char *env = getenv("PYODESYS_CUDA_STREAMING");
+    return !(env && env[0] == '0');
+}
+
 }  // namespace
 
 extern "C" {
@@ -523,8 +566,79 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
     if (roots && (ensure(c, B_ROOTOUT, nn * root_row) || ensure(c, B_ROOTIDX, nn * a.max_roots * 4) ||
                   ensure(c, B_NROOTS, nn * 4)))
         return -1;
-    const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + (shared_x ? 0 : nt) + (size_t)nt * NY) * 8 + 32);
     const bool dynamic = a.work_counter != nullptr;
+    if (dynamic && !roots && n >= 131072 && pick_kernel(method, opt) == 1 && streaming_enabled()) {
+        // ---- streaming: one persistent launch, sliced copies underneath ------------------------------------
+        const SlicePlan sp = plan_slices(n, (size_t)nt * NY * 8 + 8 + (counters ? NCOUNT * 4 : 0));
+        if (ensure(c, B_READY, 8) || ensure(c, B_SLICEDONE, kMaxSlices * 4)) return -1;
+        for (int j = 0; j < sp.n; ++j) {
+            c.h_ready[j] = (unsigned long long)std::min<int64_t>(n, sp.lo(j) + sp.len);
+            c.h_flags[j] = 0;
+        }
+        auto copy_in = [&](int j, cudaStream_t st) -> int {
+            const int64_t lo = sp.lo(j), len = sp.size(j, n);
+            if (h2d(c, B_Y0, y0, NY * 8, lo, len, st) || h2d(c, B_PARAMS, prow ? params : nullptr, prow * 8, lo, len, st) ||
+                (!shared_x && h2d(c, B_XOUT, xout, (size_t)nt * 8, lo, len, st)) || h2d(c, B_DX0, dx0, 8, lo, len, st) ||
+                h2d(c, B_DXMIN, dx_min, 8, lo, len, st) || h2d(c, B_DXMAX, dx_max, 8, lo, len, st))
+                return -1;
+            CU_CHECK(cudaMemcpyAsync(c.buf[B_READY], c.h_ready + j, 8, cudaMemcpyHostToDevice, st));
+            return 0;
+        };
+        CU_CHECK(cudaEventRecord(c.ev[0], c.stream));
+        CU_CHECK(cudaMemsetAsync(c.buf[B_WORK], 0, sizeof(unsigned long long), c.stream));
+        CU_CHECK(cudaMemsetAsync(c.buf[B_SLICEDONE], 0, kMaxSlices * 4, c.stream));
+        if (shared_x) CU_CHECK(cudaMemcpyAsync(c.buf[B_XOUT], xout, (size_t)nt * 8, cudaMemcpyHostToDevice, c.stream));
+        if (copy_in(0, c.stream)) return -1;
+        CU_CHECK(cudaEventRecord(c.ev_fork, c.stream));
+        CU_CHECK(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+        KernelArgs ak = a;
+        ak.y0 = (const double *)c.buf[B_Y0];
+        ak.params = prow ? (const double *)c.buf[B_PARAMS] : nullptr;
+        ak.xout = (const double *)c.buf[B_XOUT];
+        ak.dx0 = dev_or_null<double>(c, B_DX0, dx0, 0);
+        ak.dx_min = dev_or_null<double>(c, B_DXMIN, dx_min, 0);
+        ak.dx_max = dev_or_null<double>(c, B_DXMAX, dx_max, 0);
+        ak.yout = (double *)c.buf[B_YOUT];
+        ak.nreached = (int32_t *)c.buf[B_NREACHED];
+        ak.status = (int32_t *)c.buf[B_STATUS];
+        ak.counters = counters ? (int32_t *)c.buf[B_COUNTERS] : nullptr;
+        ak.work_counter = (unsigned long long *)c.buf[B_WORK];
+        ak.ready = (const unsigned long long *)c.buf[B_READY];
+        ak.slice_done = (unsigned int *)c.buf[B_SLICEDONE];
+        ak.slice_flags = c.d_flags;
+        ak.slice_len = sp.len;
+        CU_CHECK(cudaEventRecord(c.ev_k0, c.stream));
+        if (dispatch<0>(c, ak, method, c.stream, bps, opt)) return -1;
+        CU_CHECK(cudaEventRecord(c.ev_k1, c.stream));
+        for (int j = 1; j < sp.n; ++j)
+            if (copy_in(j, c.stream2)) return -1;
+        for (int j = 0; j < sp.n; ++j) {
+            // wait for the kernel to complete slice j (or to end: then every slice is complete, or it failed)
+            volatile unsigned int *flag = c.h_flags + j;
+            for (unsigned spin = 0; !*flag; ++spin) {
+                if ((spin & 63u) == 63u) {
+                    const cudaError_t q = cudaStreamQuery(c.stream);
+                    if (q == cudaSuccess) break;
+                    if (q != cudaErrorNotReady) return fail("streaming kernel failed: %s", cudaGetErrorString(q));
+                    std::this_thread::yield();
+                }
+            }
+            std::atomic_thread_fence(std::memory_order_acquire);
+            const int64_t lo = sp.lo(j), len = sp.size(j, n);
+            if (d2h(c, B_YOUT, yout, (size_t)nt * NY * 8, lo, len, c.stream2) ||
+                d2h(c, B_NREACHED, nreached, 4, lo, len, c.stream2) || d2h(c, B_STATUS, status, 4, lo, len, c.stream2))
+                return -1;
+            if (counters)
+                CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+                                           (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, c.stream2));
+        }
+        CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
+        CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+        CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
+        CU_CHECK(cudaStreamSynchronize(c.stream));
+        return pipeline_timings(c, timings, t_begin);
+    }
+    const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + (shared_x ? 0 : nt) + (size_t)nt * NY) * 8 + 32);
     cudaStream_t lanes[2] = {c.stream, c.stream2};
     CU_CHECK(cudaEventRecord(c.ev[0], c.stream));
     CU_CHECK(cudaMemsetAsync(c.buf[B_WORK], 0, kMaxChunks * sizeof(unsigned long long), c.stream));

@@ -597,6 +597,33 @@ def test_chunk_pipeline_is_invisible(cuda_device):
         assert np.array_equal(ad[39000 + i].yout, ad1[i].yout) and ad[39000 + i].xout[-1] == 0.5
 
 
+def test_streaming_call_is_invisible(cuda_device, monkeypatch):
+    """ large host-pointer batches run as ONE persistent launch with sliced copies underneath (inputs published
+    through a ready word, finished output slices copied back while the kernel is still running): every array must
+    equal the chunked-launch path (PYODESYS_CUDA_STREAMING=0) bit for bit, for final-state and dense-output calls,
+    with per-system step-size arrays, failures included """
+    rob = systems.robertson()
+    n = 300000
+    b = systems.batch_robertson(n=n)
+    b['params'][1234, 0] = np.nan              # a system that fails at once (non-finite rhs)
+    b['params'][777, 2] = 3e12                 # and one that runs out of steps
+    kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=3000, method='rosenbrock4', force_predefined=True,
+              return_on_error=True, first_step=np.linspace(1e-6, 1e-5, n))
+    out = {}
+    for flag in ('1', '0'):
+        monkeypatch.setenv('PYODESYS_CUDA_STREAMING', flag)
+        r1 = rob.integrate(b['x'], b['y0'], b['params'], **kw)
+        r2 = rob.integrate(np.array([0.0, 1.0, 1e2, 1e4, 1e5]), b['y0'], b['params'], **kw)
+        out[flag] = (np.array(r1.yout), np.array(r1.info.status), np.array(r1.info.counters), np.array(r1.info.nreached),
+                     np.array(r2.yout), np.array(r2.info.nreached))
+    for u, v in zip(out['1'], out['0']):
+        assert np.array_equal(u, v, equal_nan=True)
+    st = out['1'][1]
+    assert st[1234] != 0, st[1234]
+    assert (st != 0).sum() < n//100, ((st != 0).sum(), st[777])
+    assert np.abs(out['1'][0][st == 0, -1].sum(axis=1) - 1).max() < 1e-9
+
+
 @pytest.mark.parametrize('multiple', [False, True])
 def test_partially_solved_symmetric_native_multi(cuda_device, multiple):
     """ G7: ``_test_PartiallySolved_symmetric_native(_multi)`` (pyodesys/native/tests/_tests.py:156-185): decay3 with
