@@ -420,6 +420,22 @@ template <> struct Stepper<M_RK4> {
 };
 
 // ---- Dormand-Prince 5(4) -----------------------------------------------------------------------
+// Coefficients in constant memory (an FP64 instruction takes a constant-bank operand for free; as 64-bit
+// literals they cost two UMOV each - 14 % of the executed instructions in profiles/r1g_c2_dopri5_ncu_summary.md).
+namespace dp5c {
+enum { A21, A31, A32, A41, A42, A43, A51, A52, A53, A54, A61, A62, A63, A64, A65, B1, B3, B4, B5, B6,
+       E1, E3, E4, E5, E6, E7, D1, D3, D4, D5, D6, D7, C2, C3, C4, C5, NCOEF };
+}
+__constant__ double kDp5[dp5c::NCOEF] = {
+    0.2, 3.0 / 40.0, 9.0 / 40.0, 44.0 / 45.0, -56.0 / 15.0, 32.0 / 9.0,
+    19372.0 / 6561.0, -25360.0 / 2187.0, 64448.0 / 6561.0, -212.0 / 729.0,
+    9017.0 / 3168.0, -355.0 / 33.0, 46732.0 / 5247.0, 49.0 / 176.0, -5103.0 / 18656.0,
+    35.0 / 384.0, 500.0 / 1113.0, 125.0 / 192.0, -2187.0 / 6784.0, 11.0 / 84.0,
+    71.0 / 57600.0, -71.0 / 16695.0, 71.0 / 1920.0, -17253.0 / 339200.0, 22.0 / 525.0, -1.0 / 40.0,
+    -12715105075.0 / 11282082432.0, 87487479700.0 / 32700410799.0, -10690763975.0 / 1880347072.0,
+    701980252875.0 / 199316789632.0, -1453857185.0 / 822651844.0, 69997945.0 / 29380423.0,
+    0.2, 0.3, 0.8, 8.0 / 9.0};
+#define DC(name) kDp5[dp5c::name]
 template <> struct Stepper<M_DOPRI5> {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
@@ -427,8 +443,8 @@ template <> struct Stepper<M_DOPRI5> {
     static constexpr int kSharedDoublesPerThread = 0;
     __device__ __forceinline__ void bind_shared(double *, int, int) {}
     double k1[NY];                                   // f(t, y), FSAL
+    double k3[NY], k4[NY], k5[NY], k6[NY];           // stages of the last attempt (dense output forms from them)
     double k7[NY];                                   // f(t+h, ynew) of the last attempt
-    double r3[NY], r4[NY], r5[NY];                   // dense output polynomial of the last attempt
 
     __device__ __forceinline__ int begin(OdeSys &sys, const KernelArgs &a, const Tol &, double t, const double *y) {
         return eval_rhs(sys, a, t, y, k1);
@@ -439,50 +455,42 @@ template <> struct Stepper<M_DOPRI5> {
     }
     __device__ __forceinline__ int attempt(OdeSys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y,
                                            double h, double *ynew, double &err, Counters &) {
-        double k2[NY], k3[NY], k4[NY], k5[NY], k6[NY], tmp[NY];
+        double k2[NY], tmp[NY];
         int bad = 0;
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h * (0.2 * k1[i]);
-        bad |= eval_rhs(sys, a, t + 0.2 * h, tmp, k2);
+        for (int i = 0; i < NY; ++i) tmp[i] = fma(h, DC(A21) * k1[i], y[i]);
+        bad |= eval_rhs(sys, a, fma(DC(C2), h, t), tmp, k2);
 #pragma unroll
-        for (int i = 0; i < NY; ++i) tmp[i] = y[i] + h * (3.0 / 40.0 * k1[i] + 9.0 / 40.0 * k2[i]);
-        bad |= eval_rhs(sys, a, t + 0.3 * h, tmp, k3);
-#pragma unroll
-        for (int i = 0; i < NY; ++i)
-            tmp[i] = y[i] + h * (44.0 / 45.0 * k1[i] - 56.0 / 15.0 * k2[i] + 32.0 / 9.0 * k3[i]);
-        bad |= eval_rhs(sys, a, t + 0.8 * h, tmp, k4);
+        for (int i = 0; i < NY; ++i) tmp[i] = fma(h, fma(DC(A32), k2[i], DC(A31) * k1[i]), y[i]);
+        bad |= eval_rhs(sys, a, fma(DC(C3), h, t), tmp, k3);
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            tmp[i] = y[i] + h * (19372.0 / 6561.0 * k1[i] - 25360.0 / 2187.0 * k2[i] + 64448.0 / 6561.0 * k3[i] -
-                                 212.0 / 729.0 * k4[i]);
-        bad |= eval_rhs(sys, a, t + 8.0 / 9.0 * h, tmp, k5);
+            tmp[i] = fma(h, fma(DC(A43), k3[i], fma(DC(A42), k2[i], DC(A41) * k1[i])), y[i]);
+        bad |= eval_rhs(sys, a, fma(DC(C4), h, t), tmp, k4);
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            tmp[i] = y[i] + h * (9017.0 / 3168.0 * k1[i] - 355.0 / 33.0 * k2[i] + 46732.0 / 5247.0 * k3[i] +
-                                 49.0 / 176.0 * k4[i] - 5103.0 / 18656.0 * k5[i]);
+            tmp[i] = fma(h, fma(DC(A54), k4[i], fma(DC(A53), k3[i], fma(DC(A52), k2[i], DC(A51) * k1[i]))), y[i]);
+        bad |= eval_rhs(sys, a, fma(DC(C5), h, t), tmp, k5);
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            tmp[i] = fma(h, fma(DC(A65), k5[i], fma(DC(A64), k4[i], fma(DC(A63), k3[i],
+                            fma(DC(A62), k2[i], DC(A61) * k1[i])))), y[i]);
         bad |= eval_rhs(sys, a, t + h, tmp, k6);
 #pragma unroll
         for (int i = 0; i < NY; ++i)
-            ynew[i] = y[i] + h * (35.0 / 384.0 * k1[i] + 500.0 / 1113.0 * k3[i] + 125.0 / 192.0 * k4[i] -
-                                  2187.0 / 6784.0 * k5[i] + 11.0 / 84.0 * k6[i]);
+            ynew[i] = fma(h, fma(DC(B6), k6[i], fma(DC(B5), k5[i], fma(DC(B4), k4[i],
+                             fma(DC(B3), k3[i], DC(B1) * k1[i])))), y[i]);
         bad |= eval_rhs(sys, a, t + h, ynew, k7);
         // error estimate and odeint's measure: |err_i| / (atol + rtol (|y_i| + |h| |y'_i|))
         // the error measure only steers the step size: formed in single precision (see Ros4Stepper::attempt)
         float ef = 0.0f;
+        const double ah = fabs(h);
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
-            const double e = h * (71.0 / 57600.0 * k1[i] - 71.0 / 16695.0 * k3[i] + 71.0 / 1920.0 * k4[i] -
-                                  17253.0 / 339200.0 * k5[i] + 22.0 / 525.0 * k6[i] - 1.0 / 40.0 * k7[i]);
-            const double sc = fma(tol.rtol, fabs(y[i]) + fabs(h * k1[i]), tol.atol[i]);
+            const double e = h * fma(DC(E7), k7[i], fma(DC(E6), k6[i], fma(DC(E5), k5[i], fma(DC(E4), k4[i],
+                                     fma(DC(E3), k3[i], DC(E1) * k1[i])))));
+            const double sc = fma(tol.rtol, fma(ah, fabs(k1[i]), fabs(y[i])), tol.atol[i]);
             ef = fmaxf(ef, fabsf((float)e) * rcp_ftz(fmaxf((float)sc, 1e-37f)));
-            // continuous extension (Hairer, Norsett, Wanner: Solving ODEs I, II.6; dopri5.f CONTD5)
-            const double ydiff = ynew[i] - y[i];
-            const double bspl = h * k1[i] - ydiff;
-            r3[i] = bspl;
-            r4[i] = ydiff - h * k7[i] - bspl;
-            r5[i] = h * (-12715105075.0 / 11282082432.0 * k1[i] + 87487479700.0 / 32700410799.0 * k3[i] -
-                         10690763975.0 / 1880347072.0 * k4[i] + 701980252875.0 / 199316789632.0 * k5[i] -
-                         1453857185.0 / 822651844.0 * k6[i] + 69997945.0 / 29380423.0 * k7[i]);
         }
         if (!(ef <= 3.0e38f)) bad |= 1;
         err = (double)ef;
@@ -507,13 +515,22 @@ template <> struct Stepper<M_DOPRI5> {
 #pragma unroll
         for (int i = 0; i < NY; ++i) k1[i] = k7[i];
     }
-    __device__ __forceinline__ void dense(double theta, double, const double *yold, const double *ynew, double *out) {
+    // continuous extension (Hairer, Norsett, Wanner: Solving ODEs I, II.6; dopri5.f CONTD5), formed from the stages
+    // only when an output point (or an event) falls inside the step - not in every attempt
+    __device__ __forceinline__ void dense(double theta, double h, const double *yold, const double *ynew, double *out) {
         const double th1 = 1.0 - theta;
 #pragma unroll
-        for (int i = 0; i < NY; ++i)
-            out[i] = yold[i] + theta * ((ynew[i] - yold[i]) + th1 * (r3[i] + theta * (r4[i] + th1 * r5[i])));
+        for (int i = 0; i < NY; ++i) {
+            const double ydiff = ynew[i] - yold[i];
+            const double r3 = fma(h, k1[i], -ydiff);
+            const double r4 = ydiff - fma(h, k7[i], r3);
+            const double r5 = h * fma(DC(D7), k7[i], fma(DC(D6), k6[i], fma(DC(D5), k5[i], fma(DC(D4), k4[i],
+                                      fma(DC(D3), k3[i], DC(D1) * k1[i])))));
+            out[i] = yold[i] + theta * (ydiff + th1 * (r3 + theta * (r4 + th1 * r5)));
+        }
     }
 };
+#undef DC
 
 #if ODESYS_HAS_JAC
 // ---- Rosenbrock 4(3), six stages (RODAS-type; coefficients proven by oracle/check_ros4_coeffs.py) ---

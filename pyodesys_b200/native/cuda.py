@@ -446,7 +446,7 @@ def root_info(roots, i, mode):
 
 def _check_nan_y0(y0, status):
     """ deferred NaN screen of large batches: only rows the kernel rejected are looked at """
-    if y0.size <= (1 << 16):
+    if y0.size <= (1 << 16) or not np.count_nonzero(status):  # count_nonzero: one SIMD pass, 0.05 ms per 1e6
         return
     bad = np.flatnonzero(status == 3)
     if bad.size and np.isnan(y0[bad]).any():
@@ -454,7 +454,7 @@ def _check_nan_y0(y0, status):
 
 
 def _raise_on_failure(status, return_on_error):
-    if return_on_error:
+    if return_on_error or not np.count_nonzero(status):
         return
     bad = np.flatnonzero(status != 0)
     if bad.size:
