@@ -607,11 +607,13 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
         ak.slice_done = (unsigned int *)c.buf[B_SLICEDONE];
         ak.slice_flags = c.d_flags;
         ak.slice_len = sp.len;
+        // the remaining input slices are queued BEFORE the launch: a tool that makes launches synchronous (ncu,
+        // compute-sanitizer) would otherwise leave the kernel waiting for copies nobody has queued yet
+        for (int j = 1; j < sp.n; ++j)
+            if (copy_in(j, c.stream2)) return -1;
         CU_CHECK(cudaEventRecord(c.ev_k0, c.stream));
         if (dispatch<0>(c, ak, method, c.stream, bps, opt)) return -1;
         CU_CHECK(cudaEventRecord(c.ev_k1, c.stream));
-        for (int j = 1; j < sp.n; ++j)
-            if (copy_in(j, c.stream2)) return -1;
         for (int j = 0; j < sp.n; ++j) {
             // wait for the kernel to complete slice j (or to end: then every slice is complete, or it failed)
             volatile unsigned int *flag = c.h_flags + j;
