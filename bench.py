@@ -48,7 +48,8 @@ def parse():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--n', type=int, default=1000000, help='systems per GPU and step')
+    ap.add_argument('--n', '--systems-per-gpu', dest='n', type=int, default=1000000,
+                    help='systems per GPU and step (use the long form under torchrun: its parser trips over --n)')
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='target CPU time of the cpu_baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--schedule', default='dynamic', choices=['static', 'dynamic'])
