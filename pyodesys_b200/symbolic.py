@@ -106,6 +106,9 @@ class SymbolicSys(ODESys):
         self.lower_bounds = None if lower_bounds is None else np.array(lower_bounds)*np.ones(ny)
         self.upper_bounds = None if upper_bounds is None else np.array(upper_bounds)*np.ones(ny)
         self._nonnegative = kwargs.pop('nonnegative', False)
+        # banded / sparse Jacobian storage is a choice of cvode's linear solver (pyodesys/symbolic.py:160-170); the
+        # CUDA kernels factorise dense ny x ny matrices, so the hint is recorded and otherwise ignored
+        self.band = kwargs.pop('band', None)
         self.autonomous_exprs = _is_autonomous(self.indep, self.exprs)
         super().__init__(**kwargs)
         self.linear_invariants = linear_invariants

@@ -100,8 +100,18 @@ class TransformedSys(SymbolicSys):
         self._f_indep = mk(None if self.indep_fw is None else [self.indep_fw])
         self._b_indep = mk(None if self.indep_bw is None else [self.indep_bw])
         self._n_tr_params = len(tuple(params or ()))
+        # invariants that are still linear after the transformation (ScaledSys) stay linear rows, the rest become
+        # general expressions (``_group_invariants``, pyodesys/symbolic.py:777-795)
+        lin_rows, nonlin_kept = [], []
+        for iv in nonlin:
+            derivs = [be.sympify(iv).diff(y) for y in dep]
+            if all(d.is_Number for d in derivs):
+                lin_rows.append(derivs)
+            else:
+                nonlin_kept.append(iv)
+        nonlin = nonlin_kept
         super().__init__(zip(dep, exprs), indep, params, roots=roots,
-                         nonlinear_invariants=nonlin or None,
+                         linear_invariants=lin_rows or None, nonlinear_invariants=nonlin or None,
                          pre_processors=pre + [self._forward_transform_xy],
                          post_processors=[self._back_transform_out] + post, **kwargs)
         nan_p = [float('nan')]*self._n_tr_params

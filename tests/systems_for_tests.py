@@ -232,12 +232,72 @@ def leaky_chain6(compile=True):
         rhs, 6, 6, linear_invariants=[[1]*6], compile=compile))
 
 
+def scaled_chain4(compile=True):
+    """ ``_test_ScaledSys_NativeSys`` (``pyodesys/native/tests/_tests.py:53-72``): dep_scaling = 1e8 """
+    def mk():
+        from pyodesys_b200.transforms import ScaledSys
+
+        class ScaledCudaSys(ScaledSys, NativeCudaSys):
+            pass
+        y0, y1, y2, y3 = sp.symbols('y0 y1 y2 y3', real=True, positive=True)
+        eqs = [(y0, -7*y0), (y1, 7*y0 - 3*y1), (y2, 3*y1 - 2*y2), (y3, 2*y2)]
+        return ScaledCudaSys(eqs, dep_scaling=1e8, compile=compile)
+    return _get(('scaled_chain4', compile), mk)
+
+
+def _decay3_symbolic(**kw):
+    return SymbolicSys.from_callback(decay3_rhs, 3, 3, **kw)
+
+
+def decay3_nonneg(compile=True):
+    """ ``_test_Decay_nonnegative`` (``_tests.py:98-104``) """
+    return _get(('decay3_nonneg', compile), lambda: NativeCudaSys.from_other(
+        _decay3_symbolic(lower_bounds=[0]*3), compile=compile))
+
+
+def partsolved_family(compile=True):
+    """ the native members of ``_test_PartiallySolvedSystem_Native`` (``_tests.py:107-134``): plain, scaled (42),
+    reduced by the linear invariant, and the log-log transforms of the last two """
+    def mk():
+        from pyodesys_b200.transforms import ScaledSys
+        logexp = get_logexp(1, 1e-24)
+        NativeLogLog = symmetricsys(logexp, logexp, SuperClass=TransformedCudaSys)
+        odesys = _decay3_symbolic(lower_bounds=[0, 0, 0], linear_invariants=[[1, 1, 1]])
+        scaledsys = ScaledSys.from_other(odesys, dep_scaling=42)
+        partsys = PartiallySolvedSystem.from_linear_invariants(scaledsys)
+        return dict(odesys=odesys, scaledsys=scaledsys, partsys=partsys,
+                    n_sys=NativeCudaSys.from_other(odesys, compile=compile),
+                    ns_sys=NativeCudaSys.from_other(scaledsys, compile=compile),
+                    np_sys=NativeCudaSys.from_other(partsys, compile=compile),
+                    nll_scaledsys=NativeLogLog.from_other(scaledsys, compile=compile),
+                    nll_partsys=NativeLogLog.from_other(partsys, compile=compile))
+    return _get(('partsolved_family', compile), mk)
+
+
+def band_chain3(compile=True):
+    """ ``_test_NativeSys__band`` (``_tests.py:294-302``; xfail in the reference, ``native/_base.py:128-129``
+    raises NotImplementedError): the same error here """
+    def mk():
+        y = sp.symarray('y', 3)
+        f = systems.decay_dydt_factory([4, 3])(0, y)
+        return NativeCudaSys(zip(y, f), band=(1, 0), compile=compile)
+    return _get(('band_chain3', compile), mk)
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
            nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
            partsolved_loglog_decay3_multi, growth_root, chain3_roots_0, chain3_roots_1, chain3_roots_2,
-           chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6]
-    return {f.__name__: f(compile=compile) for f in fns}
+           chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6, scaled_chain4, decay3_nonneg,
+           partsolved_family]
+    out = {}
+    for f in fns:
+        obj = f(compile=compile)
+        if isinstance(obj, dict):  # a family: only its natively compiled members
+            out.update({'%s.%s' % (f.__name__, k): v for k, v in obj.items() if hasattr(v, '_native')})
+        else:
+            out[f.__name__] = obj
+    return out
 
 
 def full_params(y0, p=None):

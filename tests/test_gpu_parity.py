@@ -641,3 +641,46 @@ def test_partially_solved_symmetric_native_multi(cuda_device, multiple):
         assert np.allclose(np.sum(yout, axis=1), sum(y0), atol=2e-7, rtol=2e-7)
     xout, yout, info = trnsfsys.integrate([1e-10, 1], y0s[0], ks[0], **kw)
     assert info['success'] and np.allclose(yout, bateman_full(y0s[0], ks[0], xout - xout[0]), atol=2e-7, rtol=2e-7)
+
+
+def test_scaledsys_native(cuda_device):
+    """ ``_test_ScaledSys_NativeSys`` (pyodesys/native/tests/_tests.py:53-72): dep_scaling = 1e8, tol 1e-12,
+    nsteps = 4000 as for odeint's rosenbrock4 (native/tests/test_odeint.py:29-30) """
+    ss = tsys.scaled_chain4()
+    k = [7., 3, 2]
+    y0 = [1, 0, 0, 0]
+    xout, yout, info = ss.integrate([1e-12, 1], y0, atol=1e-12, rtol=1e-12, nsteps=4000)
+    ref = bateman_full(y0, k + [0], xout - xout[0])
+    assert info['success'] and np.allclose(yout, ref, rtol=2e-11, atol=2e-11)
+
+
+def test_decay_nonnegative(cuda_device):
+    """ ``_test_Decay_nonnegative`` (_tests.py:98-104) """
+    odesys = tsys.decay3_nonneg()
+    y0, k = [3., 2., 1.], [3.5, 2.5, 0]
+    xout, yout, info = odesys.integrate([1e-10, 1], y0, k, integrator='native')
+    ref = bateman_full(y0, k, xout - xout[0])
+    assert info['success'] and info['nfev'] > 10 and info['time_cpu'] < 100
+    assert np.allclose(yout, ref) and np.allclose(np.sum(yout, axis=1), sum(y0))
+
+
+def test_partially_solved_system_native_family(cuda_device):
+    """ ``_test_PartiallySolvedSystem_Native`` (_tests.py:107-134): the same decay through every native
+    formulation - plain, scaled by 42, reduced by the linear invariant, and the log-log transforms of both """
+    fam = tsys.partsolved_family()
+    assert fam['odesys'].linear_invariants == fam['n_sys'].linear_invariants
+    assert len(fam['nll_scaledsys'].nonlinear_invariants) > 0
+    y0, k = [3.3, 2.4, 1.5], [3.5, 2.5, 0]
+    for name in ('n_sys', 'ns_sys', 'np_sys', 'nll_scaledsys', 'nll_partsys'):
+        result = fam[name].integrate([0, .3, .5, .7, .9, 1.3], y0, k, integrator='native', atol=1e-9, rtol=1e-9)
+        ref = bateman_full(y0, k, result.xout - result.xout[0])
+        assert result.info['success'], name
+        assert result.yout.shape == ref.shape and np.allclose(result.yout, ref), name
+    # the same batched: per-system (y0, k), N = 5
+    rng = np.random.default_rng(8)
+    Y0 = np.array(y0)*(1 + 0.2*rng.uniform(size=(5, 3)))
+    K = np.array(k)*(1 + 0.2*rng.uniform(size=(5, 3)))
+    for name in ('np_sys', 'nll_partsys'):
+        results = fam[name].integrate([0, .3, .5, .7, .9, 1.3], Y0, K, atol=1e-9, rtol=1e-9)
+        for i in range(5):
+            assert np.allclose(results[i].yout, bateman_full(Y0[i], K[i], results[i].xout - results[i].xout[0])), name

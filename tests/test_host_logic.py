@@ -217,3 +217,10 @@ def test_two_rank_gloo_sharding_and_gather():
         os.remove(path)
     assert proc.returncode == 0, proc.stderr[-3000:]
     assert 'GATHER_OK 2' in proc.stdout
+
+
+def test_band_is_not_implemented_like_the_reference():
+    """ ``_test_NativeSys__band`` is xfail in the reference: ``native/_base.py:128-129`` raises for banded Jacobians """
+    import systems_for_tests as tsys
+    with pytest.raises(NotImplementedError, match="Banded"):
+        tsys.band_chain3(compile=False)
