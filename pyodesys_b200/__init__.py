@@ -6,13 +6,15 @@ pyodesys: ``NativeSys.from_callback(...).integrate(x, y0[N,ny], params[N,np], at
 Only that path is provided: symbolic definition -> CUDA code generation ->
 hand-written integrator kernels behind a C ABI -> ``Result`` / ``info`` in the reference's layout.
 """
-from .core import ODESys, Result, BatchResult, BatchInfo, integrate_auto_switch, integrate_chained
+from .core import (ODESys, Result, BatchResult, BatchInfo, integrate_auto_switch, integrate_chained,
+                   chained_parameter_variation)
 from .symbolic import SymbolicSys
 from .transforms import TransformedSys, ScaledSys, symmetricsys, PartiallySolvedSystem, get_logexp
 
 __version__ = '0.1.0'
 __all__ = ['ODESys', 'Result', 'BatchResult', 'BatchInfo', 'SymbolicSys', 'TransformedSys', 'ScaledSys',
-           'symmetricsys', 'PartiallySolvedSystem', 'get_logexp', 'integrate_auto_switch', 'integrate_chained', 'native_sys']
+           'symmetricsys', 'PartiallySolvedSystem', 'get_logexp', 'integrate_auto_switch', 'integrate_chained',
+           'chained_parameter_variation', 'native_sys']
 
 
 def __getattr__(name):

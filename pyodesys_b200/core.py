@@ -59,6 +59,50 @@ class Result:
         sel = (xdata > lower) & (xdata < upper)
         return xdata[..., sel], ydata[..., sel, :]
 
+    def calc_invariant_violations(self):
+        """ invariants along the trajectory minus their value at the first point (``pyodesys/results.py:265-268``),
+        evaluated on the internal variables the system was integrated in """
+        cb = self.odesys.get_invariants_callback()
+        x, y, p = (np.asarray(self.info['internal_' + k]) for k in ('xout', 'yout', 'params'))
+        val = cb(x, y, p)
+        return val - val[0, :]
+
+    def extend_by_integration(self, xend, params=None, odesys=None, autonomous=None, npoints=1, **kwargs):
+        """ continue from the last point to ``xend`` (``pyodesys/results.py:277-314``): rows are appended, counters
+        summed, ``success`` and-ed, ``*_indices`` shifted, ``internal_*`` concatenated when the system is the same """
+        odesys = odesys or self.odesys
+        if autonomous is None:
+            autonomous = bool(getattr(odesys, 'autonomous_interface', False) == True)  # noqa: E712
+        x0 = self.xout[-1]
+        nx0 = self.xout.size
+        span = np.linspace(0.0, xend - x0, npoints + 1) if autonomous else np.linspace(x0, xend, npoints + 1)
+        res = odesys.integrate(span, self.yout[..., -1, :], self.params if params is None else params, **kwargs)
+        self._append_leg(res, x0 if autonomous else 0.0, nx0, odesys is self.odesys)
+        return self
+
+    def _append_leg(self, res, x_shift, nx0, same_system):
+        self.xout = np.concatenate((self.xout, np.asarray(res.xout)[1:] + x_shift))
+        self.yout = np.concatenate((self.yout, np.asarray(res.yout)[..., 1:, :]))
+        info = {k: v for k, v in self.info.items() if not (k.startswith('internal') and not same_system)}
+        for k, v in res.info.items():
+            if k.startswith('internal'):
+                if same_system and k in info and k != 'internal_params':
+                    tail = np.asarray(v)[1:]
+                    info[k] = np.concatenate((np.asarray(info[k]), tail + x_shift if k == 'internal_xout' else tail))
+            elif k == 'success':
+                info[k] = bool(info.get(k, True)) and bool(v)
+            elif k.endswith('_indices'):
+                info[k] = list(info.get(k, [])) + [itm + nx0 - 1 for itm in v]
+            elif k in ('mode', 'method', 'status', 'nreached', 'root_out'):
+                info[k] = v
+            elif isinstance(v, str):
+                info[k] = (info[k] if isinstance(info.get(k), list) else [info.get(k)]) + [v]
+            elif k in info:
+                info[k] = info[k] + v
+            else:
+                info[k] = v
+        self.info = info
+
 
 class BatchInfo:
     """ Array-backed per-system info: ``batch_info[i]`` builds the reference's dict.
@@ -392,3 +436,55 @@ def integrate_auto_switch(odes, kw, x, y0, params=(), **kwargs):
 
 
 integrate_chained = integrate_auto_switch  # the reference keeps the old name (core.py:918)
+
+
+def chained_parameter_variation(subject, durations, y0, varied_params, default_params=None,
+                                integrate_kwargs=None, x0=None, npoints=1, numpy=None):
+    """ Integrate over consecutive durations with some parameters changed in between
+    (``pyodesys/core.py:921-1000``).
+
+    ``varied_params`` maps a parameter name (``par_by_name``) or index to one value per duration - a scalar, or
+    for a batch (``y0`` two-dimensional) optionally one value per system.  The reference extends every
+    ``Result`` of a batch separately (one native call per system and duration); here every duration is ONE
+    batched call over all systems, started from the final states of the previous one.  ``result.params`` keeps
+    the parameters of the first duration, as in the reference.
+    """
+    if len(durations) == 0:
+        raise ValueError("need at least 1 duration (preferably many)")
+    if npoints <= 0:
+        raise ValueError("need at least 1 point per duration")
+    for k, v in varied_params.items():
+        if len(v) != len(durations):
+            raise ValueError("Mismathced lengths of durations and varied_params")
+    integrate = subject.integrate if isinstance(subject, ODESys) else subject
+    default_params = {} if default_params is None else default_params
+    integrate_kwargs = integrate_kwargs or {}
+    ends = np.cumsum(durations)
+    if x0 is None:
+        x0 = ends[0]*0
+    out = None
+    for idx, xend in enumerate(ends):
+        params = dict(default_params) if isinstance(default_params, dict) else list(default_params)
+        for k, v in varied_params.items():
+            params[k] = v[idx]
+        if out is None:
+            out = integrate(np.linspace(x0, xend, npoints + 1), y0, params, **integrate_kwargs)
+            if not isinstance(out, Result):
+                out = [out[i] for i in range(len(out))]  # materialise: the legs are appended in place
+            continue
+        if isinstance(out, Result):
+            out.extend_by_integration(xend, params, npoints=npoints, **integrate_kwargs)
+            continue
+        # batch: one call for all systems
+        odesys = out[0].odesys
+        autonomous = bool(getattr(odesys, 'autonomous_interface', False) == True)  # noqa: E712
+        xlast = np.array([r.xout[-1] for r in out])
+        ylast = np.array([r.yout[-1] for r in out])
+        if autonomous:
+            span = np.array([np.linspace(0.0, xend - xl, npoints + 1) for xl in xlast])
+        else:
+            span = np.array([np.linspace(xl, xend, npoints + 1) for xl in xlast])
+        legs = odesys.integrate(span, ylast, params, **integrate_kwargs)
+        for i, r in enumerate(out):
+            r._append_leg(legs[i], xlast[i] if autonomous else 0.0, r.xout.size, True)
+    return out

@@ -127,6 +127,8 @@ class SymbolicSys(ODESys):
         if lin_invar is None or len(lin_invar) == 0:
             self._linear_invariants = None
         else:
+            if isinstance(lin_invar[0], dict) and self.names:  # rows keyed by name (symbolic.py:73-74)
+                lin_invar = [[d.get(n, 0) for n in self.names] for d in lin_invar]
             m = self.be.Matrix(len(lin_invar), self.ny, lambda i, j: lin_invar[i][j])
             self._linear_invariants = m
 
@@ -140,6 +142,22 @@ class SymbolicSys(ODESys):
             for i in range(linear_invariants.shape[0]):
                 out.append(sum(linear_invariants[i, j]*dep[j] for j in range(len(dep))))
         return out + list(nonlinear_invariants or [])
+
+    def get_invariants_callback(self):
+        """ ``pyodesys/symbolic.py:755-759``: ``cb(x[nt], y[nt, ny], p[np_tot]) -> [nt, ninvar]`` """
+        invar = self.all_invariants()
+        if len(invar) == 0:
+            return None
+        fn = self._callback(invar)
+
+        def cb(x, y, p):
+            y = np.asarray(y, dtype=np.float64)
+            xs = np.broadcast_to(np.asarray(x, dtype=np.float64), y.shape[:-1])[..., None]
+            p = np.asarray(p, dtype=np.float64)
+            npar = len(self.params) + (len(self.init_dep) if self.append_iv and self.init_dep else 0)
+            p = np.broadcast_to(p[..., :npar], y.shape[:-1] + (npar,))
+            return fn(np.concatenate((xs, y, p), axis=-1))
+        return cb
 
     # -- derivation ---------------------------------------------------------------------
     def get_jac(self):

@@ -284,12 +284,23 @@ def band_chain3(compile=True):
     return _get(('band_chain3', compile), mk)
 
 
+def power_decay(compile=True):
+    """ ``_test_chained_parameter_variation`` (``pyodesys/tests/test_symbolic.py:1602-1617``): a -> b with rate
+    t**e; named variables and parameters, one linear invariant given by name """
+    def f(t, y, p):
+        k = t**p['e']
+        return {'a': -k*y['a'], 'b': +k*y['a']}
+    return _get(('power_decay', compile), lambda: NativeCudaSys.from_callback(
+        f, names='ab', param_names='e', dep_by_name=True, par_by_name=True,
+        linear_invariants=[{'a': 1, 'b': 1}], compile=compile))
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
            nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
            partsolved_loglog_decay3_multi, growth_root, chain3_roots_0, chain3_roots_1, chain3_roots_2,
            chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6, scaled_chain4, decay3_nonneg,
-           partsolved_family]
+           partsolved_family, power_decay]
     out = {}
     for f in fns:
         obj = f(compile=compile)

@@ -684,3 +684,46 @@ def test_partially_solved_system_native_family(cuda_device):
         results = fam[name].integrate([0, .3, .5, .7, .9, 1.3], Y0, K, atol=1e-9, rtol=1e-9)
         for i in range(5):
             assert np.allclose(results[i].yout, bateman_full(Y0[i], K[i], results[i].xout - results[i].xout[0])), name
+
+
+def test_chained_parameter_variation(cuda_device):
+    """ ``_test_chained_parameter_variation`` (pyodesys/tests/test_symbolic.py:1602-1660, run natively by
+    native/tests/test_cvode.py:192-194): exponent e of the rate t**e switched after the first duration; then the
+    same for a batch, where every duration is one batched call.  BDF as in the reference (cvode): the symbolic
+    d/dt of t**e is e*t**e/t, not finite at t = 0, and only Rosenbrock methods evaluate it """
+    from pyodesys_b200 import chained_parameter_variation
+    odesys = tsys.power_decay()
+    durs = dur1, dur2 = 1.0, 3.0
+    e2 = 0
+
+    def analytic(tout, a0, b0, e):
+        a = a0*np.exp(-tout**(e + 1)/(e + 1))
+        return np.array([a, a0 - a + b0]).T
+
+    def check(result, e1):
+        assert result.info['success']
+        m1, m2 = result.xout <= dur1, result.xout >= dur1
+        y1, y2 = result.yout[m1], result.yout[m2]
+        assert np.allclose(y1, analytic(result.xout[m1], y1[0, 0], y1[0, 1], e1), atol=1e-6)
+        assert np.allclose(y2, analytic(result.xout[m2] - dur1, y2[0, 0], y2[0, 1], e2), atol=1e-6)
+        assert np.allclose(result.calc_invariant_violations(), 0)
+
+    for e1 in (2, 3):
+        res = chained_parameter_variation(odesys, durs, {'a': 2, 'b': 1}, {'e': [e1, e2]},
+                                          integrate_kwargs=dict(integrator='native', method='bdf'))
+        assert res.params[0] == e1  # only the initial parameter is stored (test_symbolic.py:1624)
+        check(res, e1)
+        res = chained_parameter_variation(odesys, durs, {'a': 2, 'b': 1}, {'e': [e1, e2]}, npoints=5,
+                                          integrate_kwargs=dict(integrator='native', method='bdf', nsteps=2000))
+        assert res.xout.size == 11 and res.xout[5] == dur1 and res.xout[-1] == dur1 + dur2
+        check(res, e1)
+    # batch of initial states: one call per duration
+    A0 = np.array([[2.0, 1.0], [1.5, 0.5], [3.0, 0.0], [0.7, 0.2]])
+    launches0 = odesys._native.mod.launch_count()
+    results = chained_parameter_variation(odesys, durs, A0, {'e': [2, e2]}, npoints=3,
+                                          integrate_kwargs=dict(method='bdf'))
+    assert odesys._native.mod.launch_count() - launches0 == len(durs)
+    assert len(results) == 4
+    for i, r in enumerate(results):
+        assert r.yout[0].tolist() == A0[i].tolist() and r.xout.size == 7
+        check(r, 2)
