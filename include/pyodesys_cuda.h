@@ -164,6 +164,11 @@ int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double 
 void *pyodesys_cuda_host_alloc(size_t bytes);
 void pyodesys_cuda_host_free(void *ptr);
 
+/* Free the device buffers, streams and pinned tables the library keeps for ``device`` (created lazily, sized for the
+ * largest batch seen; the role of ``del systems[idx]`` / ``free`` at the end of the Cython wrappers,
+ * _cvode_wrapper.pyx:227-233, for state that here outlives a call).  The next call re-creates what it needs. */
+int pyodesys_cuda_release(int device);
+
 /* Number of kernel launches issued by this library since it was loaded (bench bookkeeping). */
 int64_t pyodesys_cuda_launch_count(void);
 

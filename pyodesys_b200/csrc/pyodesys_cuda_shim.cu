@@ -503,7 +503,7 @@ void pyodesys_cuda_host_free(void *ptr) {
 
 const char *pyodesys_cuda_last_error(void) { return g_err; }
 
-int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const double *y0, const double *xout,
+static int integrate_predefined_impl(int device, int64_t n, int nt, const double *y0, const double *xout,
                                        const double *params, const double *atol, int natol, double rtol,
                                        const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
                                        int method, int autorestart, int return_on_error, double *yout,
@@ -694,7 +694,7 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
     return pipeline_timings(c, timings, t_begin);
 }
 
-int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, const double *x0, const double *xend,
+static int integrate_adaptive_impl(int device, int64_t n, const double *y0, const double *x0, const double *xend,
                                      const double *params, const double *atol, int natol, double rtol,
                                      const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
                                      int method, int autorestart, int return_on_error, int64_t max_rows,
@@ -809,6 +809,80 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
     CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
     CU_CHECK(cudaStreamSynchronize(c.stream));
     return pipeline_timings(c, timings, t_begin);
+}
+
+// A call that fails half way (bad argument found late, CUDA error) must not leave copies or kernels of its own
+// in flight on the library streams: the caller is free to release its buffers as soon as the call returns.
+static void drain_after_failure(int device) {
+    if (device < 0 || device >= kMaxDev) return;
+    DevCtx &c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mtx);
+    if (!c.ready) return;
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));  // keep the first error text
+    cudaSetDevice(device);
+    cudaStreamSynchronize(c.stream);
+    cudaStreamSynchronize(c.stream2);
+    cudaGetLastError();
+    memcpy(g_err, keep, sizeof(keep));
+}
+
+int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const double *y0, const double *xout,
+                                       const double *params, const double *atol, int natol, double rtol,
+                                       const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
+                                       int method, int autorestart, int return_on_error, double *yout,
+                                       int32_t *nreached, int32_t *status, int32_t *counters, double *timings,
+                                       int ptr_kind, const pyodesys_cuda_options *opt) {
+    const int rc = integrate_predefined_impl(device, n, nt, y0, xout, params, atol, natol, rtol, dx0, dx_min, dx_max,
+                                             mxsteps, method, autorestart, return_on_error, yout, nreached, status,
+                                             counters, timings, ptr_kind, opt);
+    if (rc != 0) drain_after_failure(device);
+    return rc;
+}
+
+int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, const double *x0, const double *xend,
+                                     const double *params, const double *atol, int natol, double rtol,
+                                     const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
+                                     int method, int autorestart, int return_on_error, int64_t max_rows,
+                                     double *xyout, int32_t *nrows, int32_t *status, int32_t *counters,
+                                     double *timings, int ptr_kind, const pyodesys_cuda_options *opt) {
+    const int rc = integrate_adaptive_impl(device, n, y0, x0, xend, params, atol, natol, rtol, dx0, dx_min, dx_max,
+                                           mxsteps, method, autorestart, return_on_error, max_rows, xyout, nrows,
+                                           status, counters, timings, ptr_kind, opt);
+    if (rc != 0) drain_after_failure(device);
+    return rc;
+}
+
+// Free every device buffer, stream and pinned table this library holds for ``device`` (they are created lazily and
+// grow to the largest batch seen).  The next call re-creates what it needs.
+int pyodesys_cuda_release(int device) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+    DevCtx &c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mtx);
+    if (!c.ready) return 0;
+    CU_CHECK(cudaSetDevice(device));
+    cudaStreamSynchronize(c.stream);
+    cudaStreamSynchronize(c.stream2);
+    for (int b = 0; b < NBUF; ++b) {
+        if (c.buf[b]) cudaFree(c.buf[b]);
+        c.buf[b] = nullptr;
+        c.cap[b] = 0;
+    }
+    cudaFreeHost(c.h_ready);
+    cudaFreeHost(c.h_flags);
+    c.h_ready = nullptr;
+    c.h_flags = c.d_flags = nullptr;
+    for (auto &e : c.ev) cudaEventDestroy(e);
+    cudaEventDestroy(c.ev_k0);
+    cudaEventDestroy(c.ev_k1);
+    cudaEventDestroy(c.ev_fork);
+    cudaEventDestroy(c.ev_join);
+    cudaStreamDestroy(c.stream);
+    cudaStreamDestroy(c.stream2);
+    c.stream = c.stream2 = nullptr;
+    c.ready = false;
+    cudaGetLastError();
+    return 0;
 }
 
 int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params, double *f,

@@ -209,6 +209,10 @@ class CudaModule:
     def launch_count(self):
         return int(self.lib.pyodesys_cuda_launch_count())
 
+    def release(self, device=0):
+        """ free the device buffers / streams the library keeps for ``device`` (re-created on the next call) """
+        self._check(self.lib.pyodesys_cuda_release(int(device)))
+
     def _check(self, rc):
         if rc != 0:
             raise RuntimeError("pyodesys_cuda: " + self.lib.pyodesys_cuda_last_error().decode())

@@ -727,3 +727,20 @@ def test_chained_parameter_variation(cuda_device):
     for i, r in enumerate(results):
         assert r.yout[0].tolist() == A0[i].tolist() and r.xout.size == 7
         check(r, 2)
+
+
+def test_release_and_failed_call_leave_the_library_usable(cuda_device):
+    """ ``pyodesys_cuda_release`` frees the per-device state (buffers are re-created lazily); a call that fails on
+    its arguments must not poison the next one """
+    dec = systems.decay()
+    mod = dec._native.mod
+    y0 = np.tile([1.0, 0.0], (1000, 1))
+    ref = dec.integrate([0, 1.0], y0, np.full((1000, 1), 2.0))
+    mod.release(cuda_device)
+    mod.release(cuda_device)  # idempotent
+    again = dec.integrate([0, 1.0], y0, np.full((1000, 1), 2.0))
+    assert np.array_equal(np.array(ref.yout), np.array(again.yout))
+    with pytest.raises(RuntimeError, match="pyodesys_cuda"):
+        mod.integrate_predefined_arrays(y0, np.array([0.0, 1.0]), np.full((1000, 3), 2.0), 1e-8, 1e-8, kernel=3)
+    third = dec.integrate([0, 1.0], y0, np.full((1000, 1), 2.0))
+    assert np.array_equal(np.array(ref.yout), np.array(third.yout))

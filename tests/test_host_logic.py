@@ -34,7 +34,8 @@ def test_c_abi_library_exports_every_declared_symbol():
     names = _declared_symbols()
     assert {'pyodesys_cuda_integrate_predefined', 'pyodesys_cuda_integrate_adaptive', 'pyodesys_cuda_info',
             'pyodesys_cuda_query', 'pyodesys_cuda_last_error', 'pyodesys_cuda_eval', 'pyodesys_cuda_lu_solve',
-            'pyodesys_cuda_launch_count', 'pyodesys_cuda_host_alloc', 'pyodesys_cuda_host_free'} <= set(names)
+            'pyodesys_cuda_launch_count', 'pyodesys_cuda_host_alloc', 'pyodesys_cuda_host_free',
+            'pyodesys_cuda_release'} <= set(names)
     for sysobj in (systems.robertson(), systems.vdp(), systems.radiolysis()):
         lib = ctypes.CDLL(sysobj._native.so_file)
         for nm in names:
