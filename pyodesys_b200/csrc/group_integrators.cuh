@@ -74,6 +74,43 @@ template <int G> __device__ __forceinline__ double gmax_d(const Grp<G> &g, doubl
     return v;
 }
 
+// The generated right-hand side of a network like C4 is several hundred straight-line instructions and a Rosenbrock
+// step evaluates it at eight places; inlined eight times the step outgrows the instruction cache (ncu: no_instruction
+// 1.5 stalls per issue, profiles/r1e_c4_group_inverse.md).  PYODESYS_GROUP_RHS_NOINLINE=1 keeps ONE copy: the state is
+// already staged in shared memory, the rows a lane owns come back by value in registers.
+#ifndef PYODESYS_GROUP_RHS_NOINLINE
+#define PYODESYS_GROUP_RHS_NOINLINE (ODESYS_NY >= 9 && ODESYS_NINVAR == 0)
+#endif
+template <int G> struct RhsRows {
+    double f[Grp<G>::R];
+    int st;
+};
+template <int G>
+__device__ __noinline__ RhsRows<G> g_rhs_shared_copy(double *ys, double *m_p, double *m_p_cse, int gl, double x,
+                                                     int error_outside_bounds) {
+    RhsRows<G> out;
+#pragma unroll
+    for (int r = 0; r < Grp<G>::R; ++r) out.f[r] = 0.0;
+    OdeSysRef s;
+    s.m_p = m_p;
+    s.m_p_cse = m_p_cse;
+    s.nfev = 0;
+    s.njev = 0;
+    SinkF<G> sink{gl, out.f};
+    int st = s.rhs_sink(x, ys, sink);
+#if ODESYS_HAS_BOUNDS
+    if (error_outside_bounds && s.outside_bounds(ys)) st = AnyODE::Status::recoverable_error;
+#endif
+#if ODESYS_NONNEGATIVE
+#pragma unroll
+    for (int i = 0; i < NY; ++i)
+        if (ys[i] < 0) st = AnyODE::Status::recoverable_error;
+#endif
+    AnyODE::ignore(error_outside_bounds);
+    out.st = st;
+    return out;
+}
+
 template <int G> __device__ __forceinline__ int g_rhs(const Grp<G> &g, OdeSysRef &sys, const KernelArgs &a, double x,
                                                       const double *yv, double *f) {
     constexpr int R = Grp<G>::R;
@@ -82,6 +119,13 @@ template <int G> __device__ __forceinline__ int g_rhs(const Grp<G> &g, OdeSysRef
     for (int r = 0; r < R; ++r)
         if (g.owns(r)) g.ys[r * G + g.gl] = yv[r];
     __syncwarp(g.mask);
+#if PYODESYS_GROUP_RHS_NOINLINE
+    const RhsRows<G> out = g_rhs_shared_copy<G>(g.ys, sys.m_p, sys.m_p_cse, g.gl, x, a.error_outside_bounds);
+#pragma unroll
+    for (int r = 0; r < R; ++r) f[r] = out.f[r];
+    sys.nfev += 1;
+    return out.st;
+#else
     SinkF<G> sink{g.gl, f};
     const int nfev0 = sys.nfev;
     int st = sys.rhs_sink(x, g.ys, sink);
@@ -98,6 +142,7 @@ template <int G> __device__ __forceinline__ int g_rhs(const Grp<G> &g, OdeSysRef
         if (g.ys[i] < 0) st = AnyODE::Status::recoverable_error;
 #endif
     return st;
+#endif
 }
 
 // ---- dense LU across the group -------------------------------------------------------------------
