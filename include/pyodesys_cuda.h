@@ -109,6 +109,8 @@ typedef struct pyodesys_cuda_options {
     int32_t *root_indices;           /* [n, max_roots]: adaptive: the row of xyout that holds the root;
                                         predefined: index of the first output point at or behind the root */
     int32_t *nroots_found;           /* [n]: roots met (may exceed max_roots; only the first max_roots are stored) */
+    int64_t counters_ld;             /* row length of ``counters`` ([NCOUNTERS, counters_ld]); 0 = n.  Lets several
+                                        calls (one per device) fill column ranges of ONE array without a gather */
 } pyodesys_cuda_options;
 
 /* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */

@@ -263,6 +263,7 @@ int check_common(const Common &q) {
     if (!q.status && q.n > 0) return fail("status is NULL");
     if (q.ptr_kind != 0 && q.ptr_kind != 1) return fail("ptr_kind must be 0 (host) or 1 (device)");
     if (!(q.rtol >= 0.0)) return fail("rtol must be non-negative");
+    if (q.opt && q.opt->counters_ld != 0 && q.opt->counters_ld < q.n) return fail("counters_ld %lld < n", (long long)q.opt->counters_ld);
     if (ODESYS_NROOTS > 0 && q.opt && q.opt->max_roots > 0) {
         if (!q.opt->root_out || !q.opt->root_indices || !q.opt->nroots_found)
             return fail("max_roots > 0 needs root_out, root_indices and nroots_found");
@@ -279,7 +280,7 @@ int check_common(const Common &q) {
 void fill_args(KernelArgs &a, const Common &q) {
     memset(&a, 0, sizeof(a));
     a.n = q.n;
-    a.counters_ld = q.n;
+    a.counters_ld = (q.ptr_kind == 1 && q.opt && q.opt->counters_ld > 0) ? q.opt->counters_ld : q.n;
     for (int i = 0; i < NY; ++i) a.atol[i] = q.atol[q.natol == 1 ? 0 : i];
     a.rtol = q.rtol;
     a.mxsteps = q.mxsteps;
@@ -295,6 +296,12 @@ void fill_args(KernelArgs &a, const Common &q) {
         a.return_on_root = q.opt->return_on_root;
     }
 #endif
+}
+
+// row pitch in bytes of the caller's counters array: [NCOUNT, counters_ld] (options) or dense [NCOUNT, n]
+size_t host_counters_pitch(const Common &q) {
+    const int64_t ld = (q.opt && q.opt->counters_ld > 0) ? q.opt->counters_ld : q.n;
+    return (size_t)ld * 4;
 }
 
 // event-function outputs requested and available?
@@ -553,6 +560,7 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
 
     // ---- host pointers: chunked H2D / kernel / D2H pipeline on two streams ---------------------------------
     const size_t nn = (size_t)n;
+    const size_t cnt_pitch = host_counters_pitch(q);
     const size_t prow = (size_t)a.params_ld;
     if (reserve(c, B_Y0, y0, nn * NY * 8) || reserve(c, B_PARAMS, prow ? params : nullptr, nn * prow * 8) ||
         reserve(c, B_XOUT, xout, (shared_x ? 1 : nn) * nt * 8) || reserve(c, B_DX0, dx0, nn * 8) ||
@@ -607,13 +615,31 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         ak.slice_done = (unsigned int *)c.buf[B_SLICEDONE];
         ak.slice_flags = c.d_flags;
         ak.slice_len = sp.len;
-        // the remaining input slices are queued BEFORE the launch: a tool that makes launches synchronous (ncu,
-        // compute-sanitizer) would otherwise leave the kernel waiting for copies nobody has queued yet
-        for (int j = 1; j < sp.n; ++j)
-            if (copy_in(j, c.stream2)) return -1;
+        // The remaining input slices are queued by a helper thread that starts BEFORE the launch.  Copies from
+        // pageable memory block the calling thread while the driver stages them, so queued from this thread they
+        // would either delay the launch (all input copied first) or, queued after it, never be issued under a tool
+        // that makes launches synchronous (ncu) - the kernel would wait for its inputs forever.
+        struct Feeder {
+            std::thread th;
+            int rc = 0;
+            char err[sizeof(g_err)] = "";
+            ~Feeder() { if (th.joinable()) th.join(); }
+        } feeder;
+        if (sp.n > 1)
+            feeder.th = std::thread([&]() {
+                if (cudaSetDevice(device) != cudaSuccess) { feeder.rc = -1; snprintf(feeder.err, sizeof(feeder.err), "cudaSetDevice failed in the copy thread"); return; }
+                for (int j = 1; j < sp.n; ++j)
+                    if (copy_in(j, c.stream2)) {
+                        feeder.rc = -1;
+                        memcpy(feeder.err, g_err, sizeof(feeder.err));  // thread-local text of THIS thread
+                        return;
+                    }
+            });
         CU_CHECK(cudaEventRecord(c.ev_k0, c.stream));
         if (dispatch<0>(c, ak, method, c.stream, bps, opt)) return -1;
         CU_CHECK(cudaEventRecord(c.ev_k1, c.stream));
+        if (feeder.th.joinable()) feeder.th.join();  // D2H copies below go to the same stream, behind the inputs
+        if (feeder.rc != 0) return fail("%s", feeder.err);
         for (int j = 0; j < sp.n; ++j) {
             // wait for the kernel to complete slice j (or to end: then every slice is complete, or it failed)
             volatile unsigned int *flag = c.h_flags + j;
@@ -631,7 +657,7 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
                 d2h(c, B_NREACHED, nreached, 4, lo, len, c.stream2) || d2h(c, B_STATUS, status, 4, lo, len, c.stream2))
                 return -1;
             if (counters)
-                CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+                CU_CHECK(cudaMemcpy2DAsync(counters + lo, cnt_pitch, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
                                            (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, c.stream2));
         }
         CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
@@ -680,7 +706,7 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
             d2h(c, B_STATUS, status, 4, lo, len, st))
             return -1;
         if (counters)
-            CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+            CU_CHECK(cudaMemcpy2DAsync(counters + lo, cnt_pitch, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
                                        (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
         if (roots && (d2h(c, B_ROOTOUT, opt->root_out, root_row, lo, len, st) ||
                       d2h(c, B_ROOTIDX, opt->root_indices, (size_t)a.max_roots * 4, lo, len, st) ||
@@ -742,6 +768,7 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
     }
 
     const size_t prow = (size_t)a.params_ld;
+    const size_t cnt_pitch = host_counters_pitch(q);
     const size_t row_bytes = (size_t)max_rows * (1 + NY) * 8;
     if (reserve(c, B_Y0, y0, nn * NY * 8) || reserve(c, B_PARAMS, prow ? params : nullptr, nn * prow * 8) ||
         ensure(c, B_XOUT, nn * 8) || ensure(c, B_XEND, nn * 8) || reserve(c, B_DX0, dx0, nn * 8) ||
@@ -797,7 +824,7 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
             d2h(c, B_STATUS, status, 4, lo, len, st))
             return -1;
         if (counters)
-            CU_CHECK(cudaMemcpy2DAsync(counters + lo, nn * 4, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
+            CU_CHECK(cudaMemcpy2DAsync(counters + lo, cnt_pitch, (const int32_t *)c.buf[B_COUNTERS] + lo, nn * 4,
                                        (size_t)len * 4, NCOUNT, cudaMemcpyDeviceToHost, st));
         if (roots && (d2h(c, B_ROOTOUT, opt->root_out, root_row, lo, len, st) ||
                       d2h(c, B_ROOTIDX, opt->root_indices, (size_t)a.max_roots * 4, lo, len, st) ||

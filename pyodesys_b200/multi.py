@@ -42,8 +42,10 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
     g = len(devices)
     adaptive = intern_x.shape[-1] == 2 and not force_predefined
     ny = mod.ny
-    status = np.empty(n, dtype=np.int32)
-    counters = np.zeros((6, n), dtype=np.int32)
+    # one page-locked array per output for the whole batch: every device thread hands row (column) ranges of them
+    # to the C ABI, the copies back from the devices ARE the gather
+    status = mod.pinned.empty((n,), np.int32)
+    counters = mod.pinned.empty((6, n), np.int32)
     timings = np.zeros((g, 4))
     errors = [None]*g
     kw = dict(kwargs)
@@ -52,12 +54,13 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
         steps = int(nsteps) if nsteps else 500
         max_rows = kw.pop('max_rows', None) or steps*(1 + int(kw.get('autorestart', 0))) + 1
         xyout = mod.pinned.empty((n, max_rows, 1 + ny), np.float64)
-        nrows = np.empty(n, dtype=np.int32)
+        nrows = mod.pinned.empty((n,), np.int32)
     else:
-        xout = np.ascontiguousarray(intern_x, dtype=np.float64)
+        shared_x = intern_x.shape[0] > 1 and intern_x.strides[0] == 0  # one broadcast row (core.to_arrays)
+        xout = np.ascontiguousarray(intern_x[0] if shared_x else intern_x, dtype=np.float64)
         nt = xout.shape[-1]
         yout = mod.pinned.empty((n, nt, ny), np.float64)
-        nreached = np.empty(n, dtype=np.int32)
+        nreached = mod.pinned.empty((n,), np.int32)
 
     def work(k):
         lo, hi = shard_range(n, g, k)
@@ -67,15 +70,14 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
             if adaptive:
                 r = mod.integrate_adaptive_arrays(
                     y0[lo:hi], intern_x[lo:hi, 0], intern_x[lo:hi, 1], params[lo:hi], atol, rtol,
-                    dx0=first_step, mxsteps=nsteps, device=devices[k], max_rows=max_rows, **kw)
-                xyout[lo:hi], nrows[lo:hi] = r[0], r[1]
+                    dx0=first_step, mxsteps=nsteps, device=devices[k], max_rows=max_rows, out=xyout[lo:hi],
+                    out_aux=(nrows[lo:hi], status[lo:hi], counters[:, lo:hi], n), **kw)
             else:
                 r = mod.integrate_predefined_arrays(
-                    y0[lo:hi], xout[lo:hi], params[lo:hi], atol, rtol, dx0=first_step, mxsteps=nsteps,
-                    device=devices[k], out=yout[lo:hi], **kw)
-                nreached[lo:hi] = r[1]
-            status[lo:hi] = r[2]
-            counters[:, lo:hi] = r[3]
+                    y0[lo:hi], xout if shared_x else xout[lo:hi], params[lo:hi], atol, rtol, dx0=first_step,
+                    mxsteps=nsteps,
+                    device=devices[k], out=yout[lo:hi],
+                    out_aux=(nreached[lo:hi], status[lo:hi], counters[:, lo:hi], n), **kw)
             timings[k] = r[4]
         except Exception as e:  # re-raised on the calling thread (anyode_parallel.hpp:6-27 semantics)
             errors[k] = e

@@ -63,7 +63,8 @@ class Options(ctypes.Structure):
                 ('reserved', ctypes.c_int32),
                 ('root_out', ctypes.c_void_p),
                 ('root_indices', ctypes.c_void_p),
-                ('nroots_found', ctypes.c_void_p)]
+                ('nroots_found', ctypes.c_void_p),
+                ('counters_ld', ctypes.c_int64)]
 
 
 def cache_dir():
@@ -271,7 +272,7 @@ class CudaModule:
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
                        int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
                        int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, 0,
-                       None, None, None)
+                       None, None, None, 0)
 
     def _root_buffers(self, opts, n, kw_roots):
         """ Event functions (``roots=`` of the system): attach the three output arrays of ABI v3 to ``opts``.
@@ -296,7 +297,10 @@ class CudaModule:
 
     def integrate_predefined_arrays(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                     mxsteps=0, method=None, autorestart=0, return_on_error=False,
-                                    device=0, out=None, special_settings=None, **kw):
+                                    device=0, out=None, out_aux=None, special_settings=None, **kw):
+        """ ``out`` / ``out_aux = (nreached, status, counters, counters_ld)``: caller-provided (ideally page-locked)
+        destinations - row ranges of arrays that span a larger batch (:func:`pyodesys_b200.multi.integrate_sharded`);
+        ``counters`` is then the column window ``[:, lo:hi]`` of a ``[NCOUNTERS, counters_ld]`` array. """
         y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
                                                                    kw.get('iv_from_y0', False))
         xout = np.ascontiguousarray(xout, dtype=np.float64)
@@ -310,9 +314,12 @@ class CudaModule:
         # outputs live in page-locked memory (D2H at PCIe speed); the blocks return to the pool when the
         # arrays are garbage collected
         yout = self.pinned.empty((n, nt, self.ny), np.float64) if out is None else out
-        nreached = self.pinned.empty((n,), np.int32)
-        status = self.pinned.empty((n,), np.int32)
-        counters = self.pinned.empty((NCOUNTERS, n), np.int32)
+        if out_aux is None:
+            nreached = self.pinned.empty((n,), np.int32)
+            status = self.pinned.empty((n,), np.int32)
+            counters = self.pinned.empty((NCOUNTERS, n), np.int32)
+        else:
+            nreached, status, counters, opts.counters_ld = out_aux
         timings = np.zeros(NTIMINGS)
         rc = self.lib.pyodesys_cuda_integrate_predefined(
             device, n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size, float(rtol),
@@ -325,7 +332,7 @@ class CudaModule:
 
     def integrate_adaptive_arrays(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                   mxsteps=0, method=None, autorestart=0, return_on_error=False,
-                                  device=0, max_rows=None, special_settings=None, **kw):
+                                  device=0, max_rows=None, out=None, out_aux=None, special_settings=None, **kw):
         y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
                                                                    kw.get('iv_from_y0', False))
         x0 = np.ascontiguousarray(x0, dtype=np.float64).reshape(-1)
@@ -340,10 +347,13 @@ class CudaModule:
         opts = self._options(**kw)
         if self._root_buffers(opts, n, kw_roots) is not None:
             max_rows += kw_roots[2]  # every stored root is one more row
-        xyout = self.pinned.empty((n, max_rows, 1 + self.ny), np.float64)
-        nrows = self.pinned.empty((n,), np.int32)
-        status = self.pinned.empty((n,), np.int32)
-        counters = self.pinned.empty((NCOUNTERS, n), np.int32)
+        xyout = self.pinned.empty((n, max_rows, 1 + self.ny), np.float64) if out is None else out
+        if out_aux is None:
+            nrows = self.pinned.empty((n,), np.int32)
+            status = self.pinned.empty((n,), np.int32)
+            counters = self.pinned.empty((NCOUNTERS, n), np.int32)
+        else:
+            nrows, status, counters, opts.counters_ld = out_aux
         timings = np.zeros(NTIMINGS)
         rc = self.lib.pyodesys_cuda_integrate_adaptive(
             device, n, _ptr(y0), _ptr(x0), _ptr(xend), _ptr(params), _ptr(atol), atol.size, float(rtol),
