@@ -225,3 +225,21 @@ def test_band_is_not_implemented_like_the_reference():
     import systems_for_tests as tsys
     with pytest.raises(NotImplementedError, match="Banded"):
         tsys.band_chain3(compile=False)
+
+
+def test_bench_reference_arm_contract():
+    """ ``bench.py --impl reference`` (the CPU arm the driver times beside the CUDA arm): runs without a GPU,
+    prints ONE JSON line on stdout with the metric / config of the CUDA arm and the keys of the contract """
+    import json
+    out = subprocess.run([sys.executable, os.path.join(_root, 'bench.py'), '--impl', 'reference', '--steps', '1',
+                          '--warmup', '1', '--cpu-seconds', '1'], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['impl'] == 'reference' and d['unit'] == 'systems/s' and d['higher_is_better'] is True
+    assert d['config']['workload'] == 'robertson_1e6_rtol1e-8' and d['dtype'] == 'f64'
+    assert d['value'] > 0 and d['steps'] == 1 and d['n_gpus'] == 1
+    cb = d['cpu_baseline']
+    assert cb['kind'] in ('port', 'reference') and cb['cores'] >= 1 and cb['value'] == d['value'] and cb['sample']
+    assert d['e2e'] == {"value": d['value'], "unit": d['unit'], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
