@@ -434,6 +434,16 @@ SlicePlan plan_slices(int64_t n, size_t out_bytes_per_system) {
     return p;
 }
 
+// page-locked (cudaHostAlloc / cudaHostRegister) host memory?
+bool is_pinned(const void *ptr) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
 bool streaming_enabled() {
     const char *env = getenv("PYODESYS_CUDA_STREAMING");
     return !(env && env[0] == '0');
@@ -625,7 +635,17 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
             char err[sizeof(g_err)] = "";
             ~Feeder() { if (th.joinable()) th.join(); }
         } feeder;
-        if (sp.n > 1)
+        // Page-locked inputs: the copies are asynchronous for real, so they are simply queued here, in front of the
+        // launch (also what a profiler needs: ncu serialises CUDA calls behind a running kernel, and a kernel that
+        // waits for copies issued during its own execution would never finish).  Pageable inputs: helper thread;
+        // profile such calls with PYODESYS_CUDA_STREAMING=0.
+        const bool pinned_inputs = is_pinned(y0) && (!prow || is_pinned(params)) && (shared_x || is_pinned(xout)) &&
+                                   (!dx0 || is_pinned(dx0)) && (!dx_min || is_pinned(dx_min)) &&
+                                   (!dx_max || is_pinned(dx_max));
+        if (sp.n > 1 && pinned_inputs) {
+            for (int j = 1; j < sp.n; ++j)
+                if (copy_in(j, c.stream2)) return -1;
+        } else if (sp.n > 1)
             feeder.th = std::thread([&]() {
                 if (cudaSetDevice(device) != cudaSuccess) { feeder.rc = -1; snprintf(feeder.err, sizeof(feeder.err), "cudaSetDevice failed in the copy thread"); return; }
                 for (int j = 1; j < sp.n; ++j)
