@@ -276,32 +276,31 @@ template <int G> __device__ __forceinline__ bool g_invert(const Grp<G> &g, doubl
         const int ps = __shfl_sync(g.mask, bslot, pl);
         ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
         const bool mine = ((int)(threadIdx.x & 31u) == pl);
-        // the owner scales its pivot row (row / pivot, reciprocal pivot on the diagonal) and publishes it
+        // The owner only publishes its raw pivot row and clears it (a section that runs with one lane per group);
+        // the scaling by 1/pivot is folded into the elimination factors that every lane forms anyway:
+        //   pivot row:  0 + (1/p) row[j],  diagonal 1/p;   other rows:  a[r][j] - (l/p) row[j],  column k: -l/p
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if (mine && r == ps) {
                 ord[r] = k;
-                const double d = fast_rcp<2>(a[r][k]);
 #pragma unroll
                 for (int j = 0; j < NY; ++j) {
-                    const double v = (j == k) ? d : a[r][j] * d;
-                    a[r][j] = v;
-                    g.prow[j] = v;
+                    g.prow[j] = a[r][j];
+                    a[r][j] = 0.0;
                 }
             }
         }
         __syncwarp(g.mask);
-        // every other row (pivoted earlier or not yet) drops its column k
+        const double d = fast_rcp<2>(g.prow[k]);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const bool upd = (ord[r] != k);
-            const double l = upd ? a[r][k] : 0.0;
+            const double m = (ord[r] != k) ? -a[r][k] * d : d;
 #pragma unroll
             for (int j = 0; j < NY; ++j) {
                 if (j == k) continue;
-                a[r][j] = fma(-l, g.prow[j], a[r][j]);
+                a[r][j] = fma(m, g.prow[j], a[r][j]);
             }
-            if (upd) a[r][k] = -l * g.prow[k];
+            a[r][k] = m;
         }
         __syncwarp(g.mask);
     }
