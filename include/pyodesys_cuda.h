@@ -100,7 +100,8 @@ typedef struct pyodesys_cuda_options {
                                         per thread with W / vectors / parameters in shared memory (ny >= 9) */
     /* ABI v3.  Event functions: OdeSys::roots (odesys_anyode_template.cpp:377-396), consumed by the cvode wrapper
      * (``return_on_root``, ``root_indices``, ``root_out``: _cvode_wrapper.pyx:89,206-213,354-355).  Sign changes of
-     * the nroots functions are located on the dense output of each accepted step to 100 eps (|x| + |h|).  The three
+     * the nroots functions are located on the dense output of each accepted step to 100 eps (|x| + |h|) (thread and
+     * lane-group kernels).  The three
      * arrays follow ptr_kind like every other array; max_roots == 0 (or a system without roots) switches it off. */
     int32_t return_on_root;          /* adaptive mode: the first root ends the integration; its row is the last one */
     int32_t max_roots;               /* capacity per system of root_out / root_indices */

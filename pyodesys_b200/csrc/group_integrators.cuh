@@ -522,6 +522,142 @@ template <int G> struct GroupRos4 {
 };
 #undef RC
 
+// ---- event functions on a lane group (see locate_roots in integrators.cuh for the scheme) --------------------
+// The state is distributed over the lanes; g(x, y) is evaluated by every lane of the group from the state staged
+// in shared memory, so all lanes see the same values and take the same decisions.
+#if ODESYS_NROOTS > 0
+template <int G> __device__ __forceinline__ void g_eval_roots(const Grp<G> &g, OdeSysRef &sys, double x,
+                                                              const double *yv, double *gout) {
+    constexpr int R = Grp<G>::R;
+    __syncwarp(g.mask);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (g.owns(r)) g.ys[r * G + g.gl] = yv[r];
+    __syncwarp(g.mask);
+    sys.roots(x, g.ys, gout);
+    __syncwarp(g.mask);
+}
+
+template <int G, int MODE, class St>
+__device__ __noinline__ bool g_locate_roots(const Grp<G> &g, St &st, OdeSysRef &sys, const KernelArgs &a, int64_t s,
+                                            double t, double hh, double &tnew, const double *y, double *ynew,
+                                            double *g_old, int &n_roots, int &k_out, double dir, int &status) {
+    constexpr int R = Grp<G>::R;
+    double g_lo[NROOTS], g_hi[NROOTS];
+    g_eval_roots(g, sys, tnew, ynew, g_hi);
+#pragma unroll
+    for (int r = 0; r < NROOTS; ++r) g_lo[r] = g_old[r];
+    double lo = 0.0;
+    bool stop = false;
+    const double ttol = 100.0 * DBL_EPSILON * (fabs(t) + fabs(hh)) / fabs(hh);
+    for (int found = 0; found < 16 && !stop; ++found) {
+        bool any = false;
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) any = any || root_crossed(g_lo[r], g_hi[r]);
+        if (!any) break;
+        double ta = lo, tb = 1.0, ga[NROOTS], gb[NROOTS], yb[R];
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) {
+            ga[r] = g_lo[r];
+            gb[r] = g_hi[r];
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) yb[r] = ynew[r];
+        double alpha = 1.0;
+        int side = 0, sideprev = -1;
+        for (int it = 0; it < 200 && (tb - ta) > ttol; ++it) {
+            double best = -1.0, gai = 0.0, gbi = 0.0;
+#pragma unroll
+            for (int r = 0; r < NROOTS; ++r)
+                if (root_crossed(ga[r], gb[r])) {
+                    const double frac = fabs(gb[r] / (gb[r] - ga[r]));
+                    if (frac > best) {
+                        best = frac;
+                        gai = ga[r];
+                        gbi = gb[r];
+                    }
+                }
+            if (sideprev == side) alpha = (side == 2) ? alpha * 2.0 : alpha * 0.5;
+            else alpha = 1.0;
+            double tm = tb - (tb - ta) * gbi / (gbi - alpha * gai);
+            const double width = tb - ta;
+            if (!(fabs(tm - ta) >= 0.5 * ttol)) {
+                const double fracint = width / ttol;
+                tm = ta + (fracint > 5.0 ? 0.1 : 0.5 / fracint) * width;
+            }
+            if (!(fabs(tb - tm) >= 0.5 * ttol)) {
+                const double fracint = width / ttol;
+                tm = tb - (fracint > 5.0 ? 0.1 : 0.5 / fracint) * width;
+            }
+            double ym[R], gm[NROOTS];
+            st.dense(tm, y, ynew, ym);
+            g_eval_roots(g, sys, fma(tm, hh, t), ym, gm);
+            bool chg = false;
+#pragma unroll
+            for (int r = 0; r < NROOTS; ++r) chg = chg || root_crossed(ga[r], gm[r]);
+            sideprev = side;
+            if (chg) {
+                tb = tm;
+#pragma unroll
+                for (int r = 0; r < NROOTS; ++r) gb[r] = gm[r];
+#pragma unroll
+                for (int r = 0; r < R; ++r) yb[r] = ym[r];
+                side = 1;
+            } else {
+                ta = tm;
+#pragma unroll
+                for (int r = 0; r < NROOTS; ++r) ga[r] = gm[r];
+                side = 2;
+            }
+        }
+        const bool at_end = (tb == 1.0);
+        const double x_root = at_end ? tnew : fma(tb, hh, t);
+        int idx = k_out;
+        if (MODE == 0) {
+            const double *xo = a.xout + s * a.xout_stride;
+            while (idx < a.nt && (xo[idx] - x_root) * dir < 0.0) idx += 1;
+        }
+        const bool stored = n_roots < a.max_roots;
+        if (stored) {
+            double *ro = a.root_out + (s * a.max_roots + n_roots) * (1 + NY);
+            if (g.gl == 0) {
+                ro[0] = x_root;
+                a.root_indices[s * a.max_roots + n_roots] = idx;
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (g.owns(r)) ro[1 + r * G + g.gl] = yb[r];
+        }
+        n_roots += 1;
+        if (MODE == 1 && a.return_on_root) {
+            tnew = x_root;
+#pragma unroll
+            for (int r = 0; r < R; ++r) ynew[r] = yb[r];
+            stop = true;
+        } else if (MODE == 1 && !at_end && stored) {
+            if (k_out >= a.max_rows) {
+                status = ST_ROWS;
+                stop = true;
+            } else {
+                double *row = a.xyout + (s * a.max_rows + k_out) * (1 + NY);
+                if (g.gl == 0) row[0] = x_root;
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (g.owns(r)) row[1 + r * G + g.gl] = yb[r];
+                k_out += 1;
+            }
+        }
+        lo = tb;
+#pragma unroll
+        for (int r = 0; r < NROOTS; ++r) g_lo[r] = gb[r];
+        if (at_end) break;
+    }
+#pragma unroll
+    for (int r = 0; r < NROOTS; ++r) g_old[r] = g_hi[r];
+    return stop && status < 0;
+}
+#endif  // ODESYS_NROOTS
+
 // ----------------------------------------------------------------------------------------------
 // Persistent kernel, one system per lane group.  MODE 0: predefined output points, MODE 1: every
 // accepted step.  Control flow mirrors integrate_kernel (integrators.cuh); all per-system control
@@ -558,6 +694,10 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
     int k_out = 0, restarts = 0, nfail = 0;
     Counters cnt = {0, 0, 0, 0};
     bool active = false, exhausted = false;
+#if ODESYS_NROOTS > 0
+    double g_old[NROOTS];
+    int n_roots = 0;
+#endif
 #pragma unroll
     for (int r = 0; r < R; ++r) y[r] = 0.0;
 
@@ -621,6 +761,10 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
                     if (g.owns(r)) g.ys[r * G + g.gl] = y[r];
                 __syncwarp(g.mask);
                 sys.init_invariants(a.max_invariant_violation, t, g.ys);
+#endif
+#if ODESYS_NROOTS > 0
+                n_roots = 0;
+                if (a.max_roots > 0) g_eval_roots(g, sys, t, y, g_old);
 #endif
                 st.begin();
                 h = a.dx0 ? a.dx0[s] : 0.0;
@@ -718,6 +862,12 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
                 h = hnext;
             } else {
                 // ---- (D) accepted: emit outputs -----------------------------------------------------------
+                bool stop_at_root = false;
+#if ODESYS_NROOTS > 0
+                if (a.max_roots > 0)
+                    stop_at_root = g_locate_roots<G, MODE>(g, st, sys, a, s, t, hh, tnew, y, ynew, g_old, n_roots,
+                                                           k_out, dir, status);
+#endif
                 if (MODE == 0) {
                     const double *xo = a.xout + s * a.xout_stride;
                     while (k_out < a.nt) {
@@ -756,6 +906,7 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
                 for (int r = 0; r < R; ++r) y[r] = ynew[r];
                 t = tnew;
                 h = hnext;
+                if (stop_at_root && status < 0) status = ST_OK;
             }
         }
 
@@ -776,6 +927,9 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_GROUP_MIN_BLOCKS) group_ros4_k
                 a.status[s] = status;
                 if (MODE == 0) a.nreached[s] = k_out;
                 else a.nrows[s] = k_out;
+#if ODESYS_NROOTS > 0
+                if (a.max_roots > 0) a.nroots_found[s] = n_roots;
+#endif
                 if (a.counters) {
                     a.counters[C_NSTEPS * a.counters_ld + s] = cnt.nsteps;
                     a.counters[C_NFEV * a.counters_ld + s] = sys.nfev;

@@ -188,9 +188,6 @@ template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t
 // lane-group kernel above.
 int pick_kernel(int method, const pyodesys_cuda_options *opt) {
     const int want = opt ? opt->kernel : 0;
-#if ODESYS_NROOTS > 0
-    if (want == 0 && opt && opt->max_roots > 0) return 1;  // roots are located by the thread kernels
-#endif
     if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3) ? -1 : 1;
 #if ODESYS_SMEM_KERNEL
     if (want == 3) return 3;
@@ -267,8 +264,8 @@ int check_common(const Common &q) {
     if (ODESYS_NROOTS > 0 && q.opt && q.opt->max_roots > 0) {
         if (!q.opt->root_out || !q.opt->root_indices || !q.opt->nroots_found)
             return fail("max_roots > 0 needs root_out, root_indices and nroots_found");
-        if (pick_kernel(q.method, q.opt) != 1)
-            return fail("event functions are located by the one-system-per-thread kernels (ny <= 16): pass kernel=1");
+        if (pick_kernel(q.method, q.opt) == 3)
+            return fail("the shared-memory thread kernel does not locate event functions: pass kernel=1 or kernel=2");
     }
     if (q.opt && q.opt->max_invariant_violation != 0.0) {
         if (ODESYS_NINVAR == 0) return fail("max_invariant_violation given but the system defines no invariants");

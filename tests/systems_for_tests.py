@@ -295,12 +295,18 @@ def power_decay(compile=True):
         linear_invariants=[{'a': 1, 'b': 1}], compile=compile))
 
 
+def chain6_roots(compile=True):
+    """ six species decay chain (ny = 6: thread AND lane-group kernels) with two event functions: y0 = y1, y1 = y2 """
+    return _get(('chain6_roots', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_chain_rhs, 6, 5, compile=compile, roots_cb=lambda x, y, p, be: [y[0] - y[1], y[1] - y[2]]))
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
            nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
            partsolved_loglog_decay3_multi, growth_root, chain3_roots_0, chain3_roots_1, chain3_roots_2,
            chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6, scaled_chain4, decay3_nonneg,
-           partsolved_family, power_decay]
+           partsolved_family, power_decay, chain6_roots]
     out = {}
     for f in fns:
         obj = f(compile=compile)

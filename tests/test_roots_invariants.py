@@ -260,3 +260,56 @@ def test_cuda_invariant_guard_lane_group_kernel(cuda_device):
         loose = native._native.mod.integrate_predefined_arrays(y0, xo, pf, 1e-10, 1e-10, mxsteps=5000, kernel=kernel,
                                                                max_invariant_violation=10.0)
         assert (base[2] == 0).all() and np.array_equal(base[0], loose[0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('kernel', ['thread', 'group'])
+def test_cuda_roots_lane_group_kernel(cuda_device, kernel):
+    """ ny = 6 chain, two event functions: the lane-group kernel (state distributed over the lanes, g evaluated
+    from the state staged in shared memory) locates the same roots as the thread kernel and the oracle, in
+    adaptive (rows inserted, return_on_root) and predefined mode """
+    native = tsys.chain6_roots()
+    orc = _orc(native)
+    rng = np.random.default_rng(21)
+    n = 130
+    y0 = np.zeros((n, 6))
+    y0[:, 0] = 1 + rng.uniform(0, 1, n)
+    p = rng.uniform(1.0, 4.0, (n, 5))
+    pf = full_params(y0, p)
+    mod = native._native.mod
+    for ror in (False, True):
+        so, sc = {}, {}
+        xy_o, nr_o, st_o, _c = orc.integrate_adaptive(y0, 0.0, 3.0, pf, 1e-10, 1e-10, mxsteps=5000,
+                                                      method='rosenbrock4', max_roots=4, roots_sink=so,
+                                                      return_on_root=ror)
+        xy_c, nr_c, st_c, _c, _t = mod.integrate_adaptive_arrays(
+            y0, np.zeros(n), np.full(n, 3.0), pf, 1e-10, 1e-10, mxsteps=5000, method='rosenbrock4', max_roots=4,
+            roots_sink=sc, return_on_root=ror, kernel=kernel)
+        assert (st_c == 0).all() and np.array_equal(so['nroots_found'], sc['nroots_found'])
+        assert (sc['nroots_found'] >= 1).sum() > n//2
+        for i in range(n):
+            k = min(int(sc['nroots_found'][i]), 4)
+            if k == 0:  # no crossing inside the span for these rates
+                assert xy_c[i, nr_c[i] - 1, 0] == 3.0
+                continue
+            assert np.abs(sc['root_out'][i, :k] - so['root_out'][i, :k]).max() < 1e-9
+            for j in range(k):
+                assert np.array_equal(xy_c[i, sc['root_indices'][i, j]], sc['root_out'][i, j])
+            if ror:
+                assert sc['root_indices'][i, 0] == nr_c[i] - 1
+            else:
+                assert xy_c[i, nr_c[i] - 1, 0] == 3.0
+            # the event functions vanish at the reported states
+            yr = sc['root_out'][i, :k, 1:]
+            assert np.min(np.abs(np.stack((yr[:, 0] - yr[:, 1], yr[:, 1] - yr[:, 2]))), axis=0).max() < 1e-9
+    xo = np.linspace(0, 3, 7)
+    so, sc = {}, {}
+    y_o = orc.integrate_predefined(y0, xo, pf, 1e-10, 1e-10, mxsteps=5000, method='rosenbrock4', max_roots=4,
+                                   roots_sink=so)[0]
+    y_c = mod.integrate_predefined_arrays(y0, xo, pf, 1e-10, 1e-10, mxsteps=5000, method='rosenbrock4', max_roots=4,
+                                          roots_sink=sc, kernel=kernel)[0]
+    assert np.abs(y_c - y_o).max() < 1e-8 and np.array_equal(so['nroots_found'], sc['nroots_found'])
+    for i in range(n):
+        k = min(int(sc['nroots_found'][i]), 4)
+        assert np.array_equal(so['root_indices'][i, :k], sc['root_indices'][i, :k])
+        assert k == 0 or np.abs(sc['root_out'][i, :k] - so['root_out'][i, :k]).max() < 1e-9
