@@ -160,6 +160,22 @@ int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, 
                        double *f, double *jac, double *dfdt);
 int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok);
 
+/* The two alternative Jacobian forms of the generated OdeSys, evaluated for a batch (host pointers):
+ *  - OdeSys::jtimes (odesys_anyode_template.cpp:214-243; expressions from SymbolicSys.get_jtimes,
+ *    pyodesys/symbolic.py:652-665): v[n,ny] -> Jv[n,ny] = J(x, y) v without forming J.  Systems generated
+ *    without ``jtimes=True`` return an error (the template returns unrecoverable_error, :239-243);
+ *    ``pyodesys_cuda_query("has_jtimes")`` tells.
+ *  - OdeSys::sparse_jac_csc / get_nnz (template:311-344,131-133; layout of be.sparse_jacobian_csc,
+ *    pyodesys/symbolic.py:641): data[n,nnz] in compressed-sparse-column order, colptrs[ny+1] and rowvals[nnz]
+ *    (shared by all systems, written once).  Systems generated without ``sparse=True`` have nnz = -1
+ *    (``pyodesys_cuda_query("nnz")``) and return an error.
+ * The integrator kernels of a ``sparse=True`` system assemble their dense ny x ny iteration matrix from exactly
+ * these nnz expressions (structural zeros are compile-time constants). */
+int pyodesys_cuda_eval_jtimes(int device, int64_t n, const double *x, const double *y, const double *params,
+                              const double *v, double *Jv);
+int pyodesys_cuda_eval_sparse_jac(int device, int64_t n, const double *x, const double *y, const double *params,
+                                  double *data, int32_t *colptrs, int32_t *rowvals);
+
 /* Page-locked host memory for inputs/outputs of the ptr_kind 0 calls (portable across devices).  D2H/H2D
  * of pageable numpy memory runs at ~6 GB/s through the driver's staging buffer; pinned memory reaches
  * PCIe speed.  The reference wrappers allocate ``yout`` themselves (numpy.empty, _odeint_wrapper.pyx:162);

@@ -123,6 +123,8 @@ class OracleModule:
         lib.oracle_eval.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _d, _d]
         lib.oracle_set_extras.argtypes = [ctypes.c_double, ctypes.c_int, ctypes.c_int, _d, _i32, _i32]
         lib.oracle_lu_solve.argtypes = [ctypes.c_int64, _d, _d, _d, _i32]
+        lib.oracle_eval_jtimes.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _d]
+        lib.oracle_eval_sparse_jac.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _i32, _i32]
 
     def _extras(self, n, max_invariant_violation, return_on_root, max_roots, sink):
         """ invariant guard / event functions for the next call; ``sink`` (a dict) receives the root arrays """
@@ -220,6 +222,30 @@ class OracleModule:
         dfdt = np.empty((n, self.ny)) if jac else None
         self.lib.oracle_eval(n, _p(x), _p(y), _p(params), _p(f), _p(J), _p(dfdt))
         return f, J, dfdt
+
+    def eval_jtimes(self, x, y, params, v):
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        n = y.shape[0]
+        x = np.ascontiguousarray(np.broadcast_to(np.asarray(x, dtype=np.float64), (n,)))
+        params = np.ascontiguousarray(params, dtype=np.float64).reshape(n, self.np_tot)
+        v = np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.float64), (n, self.ny)))
+        out = np.empty((n, self.ny))
+        if self.lib.oracle_eval_jtimes(n, _p(x), _p(y), _p(params), _p(v), _p(out)) != 0:
+            raise RuntimeError("oracle: system generated without jtimes")
+        return out
+
+    def eval_sparse_jac(self, x, y, params, nnz):
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        n = y.shape[0]
+        x = np.ascontiguousarray(np.broadcast_to(np.asarray(x, dtype=np.float64), (n,)))
+        params = np.ascontiguousarray(params, dtype=np.float64).reshape(n, self.np_tot)
+        data = np.empty((n, nnz))
+        colptrs = np.zeros(self.ny + 1, dtype=np.int32)
+        rowvals = np.zeros(nnz, dtype=np.int32)
+        if self.lib.oracle_eval_sparse_jac(n, _p(x), _p(y), _p(params), _p(data), _p(colptrs, _i32),
+                                           _p(rowvals, _i32)) != 0:
+            raise RuntimeError("oracle: system generated without sparse=True")
+        return data, colptrs, rowvals
 
     def lu_solve(self, A, b):
         A = np.ascontiguousarray(A, dtype=np.float64)

@@ -1047,6 +1047,38 @@ int oracle_eval(int64_t n, const double *x, const double *y, const double *param
     return 0;
 }
 
+// template:214-243 / :311-344 - the matrix-free product and the CSC Jacobian of the generated system
+int oracle_eval_jtimes(int64_t n, const double *x, const double *y, const double *params, const double *v, double *Jv) {
+#if ODESYS_HAS_JTIMES
+    for (int64_t s = 0; s < n; ++s) {
+        OdeSys sys;
+        for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+        sys.setup();
+        sys.jtimes(v + s * NY, Jv + s * NY, x[s], y + s * NY, nullptr);
+    }
+    return 0;
+#else
+    (void)n; (void)x; (void)y; (void)params; (void)v; (void)Jv;
+    return -1;
+#endif
+}
+
+int oracle_eval_sparse_jac(int64_t n, const double *x, const double *y, const double *params, double *data,
+                           int32_t *colptrs, int32_t *rowvals) {
+#if ODESYS_NNZ >= 0
+    for (int64_t s = 0; s < n; ++s) {
+        OdeSys sys;
+        for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+        sys.setup();
+        sys.sparse_jac_csc(x[s], y + s * NY, nullptr, data + s * ODESYS_NNZ, colptrs, rowvals);
+    }
+    return 0;
+#else
+    (void)n; (void)x; (void)y; (void)params; (void)data; (void)colptrs; (void)rowvals;
+    return -1;
+#endif
+}
+
 int oracle_lu_solve(int64_t n, const double *A, const double *b, double *x, int32_t *ok) {
     for (int64_t s = 0; s < n; ++s) {
         DenseLU lu;

@@ -1283,6 +1283,55 @@ __global__ void eval_kernel(int64_t n, const double *x, const double *y, const d
 #endif
 }
 
+// Jv = J(x, y) v by the generated matrix-free product (template:214-243), one system per thread
+__global__ void eval_jtimes_kernel(int64_t n, const double *x, const double *y, const double *params, const double *v,
+                                   double *Jv) {
+#if ODESYS_HAS_JTIMES
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    OdeSys sys;
+    double yy[NY], vv[NY], out[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) {
+        yy[i] = y[s * NY + i];
+        vv[i] = v[s * NY + i];
+    }
+#pragma unroll
+    for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+    sys.setup();
+    sys.jtimes(vv, out, x[s], yy, nullptr);
+#pragma unroll
+    for (int i = 0; i < NY; ++i) Jv[s * NY + i] = out[i];
+#endif
+}
+
+// data[n, nnz] of the CSC Jacobian (template:311-344); the index arrays are the same for every system and are
+// written once by thread 0
+__global__ void eval_sparse_jac_kernel(int64_t n, const double *x, const double *y, const double *params, double *data,
+                                       int32_t *colptrs, int32_t *rowvals) {
+#if ODESYS_NNZ >= 0
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    OdeSys sys;
+    double yy[NY], dat[ODESYS_NNZ > 0 ? ODESYS_NNZ : 1];
+    int32_t cp[NY + 1], rv[ODESYS_NNZ > 0 ? ODESYS_NNZ : 1];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) yy[i] = y[s * NY + i];
+#pragma unroll
+    for (int i = 0; i < NP_TOT; ++i) sys.m_p[i] = params[s * NP_TOT + i];
+    sys.setup();
+    sys.sparse_jac_csc(x[s], yy, nullptr, dat, cp, rv);
+#pragma unroll
+    for (int k = 0; k < ODESYS_NNZ; ++k) data[s * ODESYS_NNZ + k] = dat[k];
+    if (s == 0) {
+#pragma unroll
+        for (int k = 0; k <= NY; ++k) colptrs[k] = cp[k];
+#pragma unroll
+        for (int k = 0; k < ODESYS_NNZ; ++k) rowvals[k] = rv[k];
+    }
+#endif
+}
+
 #if ODESYS_NY <= 16
 __global__ void lu_kernel(int64_t n, const double *A, const double *b, double *xsol, int32_t *ok) {
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

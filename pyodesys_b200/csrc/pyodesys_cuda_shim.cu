@@ -465,7 +465,7 @@ int64_t pyodesys_cuda_query(const char *key) {
     const KV kv[] = {
         {"abi_version", PYODESYS_CUDA_ABI_VERSION}, {"ny", NY}, {"nparams", ODESYS_NPARAMS}, {"np_tot", NP_TOT},
         {"np_used", NP_USED}, {"npcse", ODESYS_NPCSE}, {"has_jac", ODESYS_HAS_JAC}, {"autonomous", ODESYS_AUTONOMOUS},
-        {"nroots", ODESYS_NROOTS}, {"ninvar", ODESYS_NINVAR}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
+        {"nroots", ODESYS_NROOTS}, {"nnz", ODESYS_NNZ}, {"has_jtimes", ODESYS_HAS_JTIMES}, {"ninvar", ODESYS_NINVAR}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
         {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
         {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL},
         {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF},
@@ -953,6 +953,69 @@ int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, 
     if (dd) CU_CHECK(cudaMemcpy(dfdt, dd, nn * NY * 8, cudaMemcpyDeviceToHost));
     cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(df); cudaFree(dj); cudaFree(dd);
     return 0;
+}
+
+int pyodesys_cuda_eval_jtimes(int device, int64_t n, const double *x, const double *y, const double *params,
+                              const double *v, double *Jv) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+#if !ODESYS_HAS_JTIMES
+    (void)n; (void)x; (void)y; (void)params; (void)v; (void)Jv;
+    return fail("this system was generated without a Jacobian-vector product (jtimes=True)");
+#else
+    if (n <= 0) return 0;
+    CU_CHECK(cudaSetDevice(device));
+    const size_t nn = (size_t)n;
+    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *dv = nullptr, *dout = nullptr;
+    CU_CHECK(cudaMalloc(&dx, nn * 8));
+    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
+    CU_CHECK(cudaMalloc(&dv, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dout, nn * NY * 8));
+    CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
+    CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
+    CU_CHECK(cudaMemcpy(dv, v, nn * NY * 8, cudaMemcpyHostToDevice));
+    if (NP_TOT) CU_CHECK(cudaMemcpy(dp, params, nn * NP_TOT * 8, cudaMemcpyHostToDevice));
+    eval_jtimes_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dx, dy, dp, dv, dout);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    CU_CHECK(cudaMemcpy(Jv, dout, nn * NY * 8, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(dv); cudaFree(dout);
+    return 0;
+#endif
+}
+
+int pyodesys_cuda_eval_sparse_jac(int device, int64_t n, const double *x, const double *y, const double *params,
+                                  double *data, int32_t *colptrs, int32_t *rowvals) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+#if ODESYS_NNZ < 0
+    (void)n; (void)x; (void)y; (void)params; (void)data; (void)colptrs; (void)rowvals;
+    return fail("this system stores its Jacobian densely (nnz = -1); generate it with sparse=True");
+#else
+    if (n <= 0) return 0;
+    CU_CHECK(cudaSetDevice(device));
+    const size_t nn = (size_t)n, nz = ODESYS_NNZ > 0 ? ODESYS_NNZ : 1;
+    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *dd = nullptr;
+    int32_t *dc = nullptr, *dr = nullptr;
+    CU_CHECK(cudaMalloc(&dx, nn * 8));
+    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
+    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
+    CU_CHECK(cudaMalloc(&dd, nn * nz * 8));
+    CU_CHECK(cudaMalloc(&dc, (NY + 1) * 4));
+    CU_CHECK(cudaMalloc(&dr, nz * 4));
+    CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
+    CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
+    if (NP_TOT) CU_CHECK(cudaMemcpy(dp, params, nn * NP_TOT * 8, cudaMemcpyHostToDevice));
+    eval_sparse_jac_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dx, dy, dp, dd, dc, dr);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    if (ODESYS_NNZ > 0) {
+        CU_CHECK(cudaMemcpy(data, dd, nn * ODESYS_NNZ * 8, cudaMemcpyDeviceToHost));
+        CU_CHECK(cudaMemcpy(rowvals, dr, ODESYS_NNZ * 4, cudaMemcpyDeviceToHost));
+    }
+    CU_CHECK(cudaMemcpy(colptrs, dc, (NY + 1) * 4, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(dd); cudaFree(dc); cudaFree(dr);
+    return 0;
+#endif
 }
 
 int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok) {

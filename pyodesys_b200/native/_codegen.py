@@ -77,7 +77,7 @@ class GeneratedCode:
     """ Result of :func:`generate`: header text + the compile-time facts about the system. """
 
     def __init__(self, text, ny, nparams, np_tot, np_used, npcse, flops, has_jac, autonomous,
-                 has_first_step, has_dx_max, nroots, jac_nnz):
+                 has_first_step, has_dx_max, nroots, jac_nnz, nnz=-1, has_jtimes=False):
         self.text = text
         self.ny = ny
         self.nparams = nparams
@@ -91,6 +91,8 @@ class GeneratedCode:
         self.has_dx_max = has_dx_max
         self.nroots = nroots
         self.jac_nnz = jac_nnz
+        self.nnz = nnz                # stored CSC entries (sparse=True) or -1
+        self.has_jtimes = has_jtimes
 
     @property
     def digest(self):
@@ -191,7 +193,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     nparams = len(odesys.params)
     np_tot = nparams + (ny if odesys.append_iv else 0)
 
-    jac = odesys.get_jac()
+    jac = odesys.get_dense_jac() if hasattr(odesys, 'get_dense_jac') else odesys.get_jac()
     all_exprs = list(odesys.exprs)
     if jac is not False:
         dfdx = odesys.get_dfdx()
@@ -210,6 +212,18 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     nroots = 0 if roots is None else len(roots)
     if nroots:
         all_exprs += [be.sympify(r) for r in roots]
+    # _base.py:134-155 - CSC Jacobian entries (``sparse=True``) and the Jacobian-vector product (``jtimes=True``);
+    # appended last so that systems without them generate exactly the text they did before
+    nnz = odesys.nnz if (jac is not False and getattr(odesys, 'sparse', False)) else -1
+    if nnz >= 0:
+        csc_data = odesys.get_jac()
+        all_exprs += [csc_data[k] for k in range(nnz)]
+    jtimes = odesys.get_jtimes() if hasattr(odesys, 'get_jtimes') else False
+    njtimes = 0
+    if jtimes is not False:
+        jt_v, jt_exprs = jtimes
+        all_exprs += [be.sympify(e) for e in jt_exprs]
+        njtimes = len(jt_exprs)
 
     invar = [be.sympify(e) for e in odesys.all_invariants()] if hasattr(odesys, 'all_invariants') else []
     ninvar = len(invar)
@@ -221,6 +235,8 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     subsd.update({k: be.Symbol('m_p[%d]' % i) for i, k in enumerate(odesys.params)})
     if odesys.append_iv and odesys.init_dep is not None:
         subsd.update({k: be.Symbol('m_p[%d]' % (nparams + i)) for i, k in enumerate(odesys.init_dep)})
+    if njtimes:
+        subsd.update({k: be.Symbol('v[%d]' % i) for i, k in enumerate(jt_v)})  # _base.py:160-162
 
     use_cse = os.getenv('PYODESYS_NATIVE_CSE', '1') == '1'  # _base.py:175-179
 
@@ -230,7 +246,8 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         return be.cse(exprs, symbols=symbols, ignore=ignore)
 
     # ---- level 1: parameter-only sub-expressions -> m_p_cse[] -------------------------------
-    ignore = tuple(odesys.dep) + ((odesys.indep,) if odesys.indep is not None else ())
+    ignore = tuple(odesys.dep) + ((odesys.indep,) if odesys.indep is not None else ()) + \
+        (tuple(jt_v) if njtimes else ())
     common_cses, common_exprs = cse_cb(all_exprs, be.numbered_symbols('cse_temporary'), ignore)
     common_subs, k = {}, 0
     for symb, _sub in common_cses:
@@ -254,6 +271,12 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         off += 1
     if nroots:
         roots_cses, roots_exprs = cse_cb(common_exprs[off:off + nroots], be.numbered_symbols('cse'))
+        off += nroots
+    if nnz >= 0:
+        csc_cses, csc_exprs = cse_cb(common_exprs[off:off + nnz], be.numbered_symbols('cse'))
+        off += nnz
+    if njtimes:
+        jt_cses, jt_exprs_c = cse_cb(common_exprs[off:off + njtimes], be.numbered_symbols('cse'))
 
     flops = {
         'pcse': _count([e for _s, e in common_cses]),
@@ -355,6 +378,26 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     else:
         roots_body = '        return AnyODE::Status::success;'
 
+    # template:311-344 - data[nnz] in CSC order plus the (constant) index arrays
+    if nnz >= 0:
+        csc_body = _body([(sy.name, cc(e)) for sy, e in csc_cses],
+                         [('data[%d]' % k, cc(e)) for k, e in enumerate(csc_exprs)] +
+                         [('rowvals[%d]' % k, '%d' % r) for k, r in enumerate(odesys._rowvals)] +
+                         [('colptrs[%d]' % k, '%d' % c) for k, c in enumerate(odesys._colptrs)],
+                         ret='this->njev++;\n        return AnyODE::Status::success;')
+    else:
+        csc_body = '        return AnyODE::Status::unrecoverable_error;'
+    # template:214-243
+    if 'p_jtimes' in ns_over:
+        jtimes_body = '        ' + ns_over['p_jtimes'] + '\n        this->njvev++;\n        return AnyODE::Status::success;'
+    elif njtimes:
+        jtimes_body = _body([(sy.name, cc(e)) for sy, e in jt_cses],
+                            [('Jv[%d]' % i, cc(e)) for i, e in enumerate(jt_exprs_c)],
+                            ret='this->njvev++;\n        return AnyODE::Status::success;')
+    else:
+        jtimes_body = '        return AnyODE::Status::unrecoverable_error;'
+    has_jtimes = bool(njtimes) or 'p_jtimes' in ns_over
+
     # template:112-123,191-198 - invariants: values at the initial state, and the violation test of ``rhs``
     if ninvar:
         inv_cses, inv_exprs = cse_cb(invar, be.numbered_symbols('cse'))
@@ -384,10 +427,13 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         ('ODESYS_FLOPS_PCSE', flops['pcse']), ('ODESYS_JAC_NNZ', jac_nnz),
         ('ODESYS_HAS_BOUNDS', int(lb is not None or ub is not None)),
         ('ODESYS_NONNEGATIVE', int(bool(getattr(odesys, '_nonnegative', False)))),
-        ('ODESYS_NINVAR', ninvar),
+        ('ODESYS_NINVAR', ninvar), ('ODESYS_NNZ', nnz), ('ODESYS_HAS_JTIMES', int(has_jtimes)),
     ]
     struct_body = '''
     int nfev, njev;
+#if ODESYS_HAS_JTIMES
+    int njvev;
+#endif
 
     // template:163-190 - true when a lower/upper bound is violated
     ODESYS_FN bool outside_bounds(const double * const y) const {
@@ -397,6 +443,9 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     // template:92-125 - parameter-only sub-expressions, once per system
     ODESYS_FN void setup() {
         nfev = 0; njev = 0;
+#if ODESYS_HAS_JTIMES
+        njvev = 0;
+#endif
 %(setup)s
     }
     // template:147-204
@@ -422,6 +471,28 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         AnyODE::ignore(x); AnyODE::ignore(y);
 %(jac_sink)s
     }
+    // template:127-133 - number of stored Jacobian entries, -1 for dense storage
+    ODESYS_FN int get_nnz() const { return ODESYS_NNZ; }
+#if ODESYS_NNZ >= 0
+    // template:311-344 - compressed sparse column: data[nnz], colptrs[ny + 1], rowvals[nnz]
+    template <class Index>
+    ODESYS_FN AnyODE::Status sparse_jac_csc(double x, const double * const ODESYS_RESTRICT y,
+                                            const double * const ODESYS_RESTRICT fy,
+                                            double * const ODESYS_RESTRICT data, Index * const ODESYS_RESTRICT colptrs,
+                                            Index * const ODESYS_RESTRICT rowvals) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(fy);
+%(csc)s
+    }
+#endif
+#if ODESYS_HAS_JTIMES
+    // template:214-243 - Jv = J(x, y) v without forming J
+    ODESYS_FN AnyODE::Status jtimes(const double * const ODESYS_RESTRICT v, double * const ODESYS_RESTRICT Jv,
+                                    double x, const double * const ODESYS_RESTRICT y,
+                                    const double * const ODESYS_RESTRICT fy) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(fy); AnyODE::ignore(v);
+%(jtimes)s
+    }
+#endif
     // template:295-309
     ODESYS_FN double get_dx0(double x, const double * const y) {
         AnyODE::ignore(x); AnyODE::ignore(y);
@@ -463,7 +534,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         return bad;
     }
 #endif
-''' % dict(invar=invar_body, bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
+''' % dict(csc=csc_body, jtimes=jtimes_body, invar=invar_body, bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
            rhs_sink=rhs_sink_body, jac_sink=jac_sink_body, fs=fs_body, dxmax=dxmax_body, roots=roots_body)
 
     text = '''// -*- mode: read-only -*-
@@ -496,4 +567,5 @@ typedef OdeSysT<double *> OdeSysRef;
     return GeneratedCode(text, ny, nparams, np_tot, np_used, npcse, flops,
                          has_jac=bool(nj) or 'p_jac' in ns_over,
                          autonomous=bool(odesys.autonomous_exprs), has_first_step=has_fs,
-                         has_dx_max=has_dx_max, nroots=nroots, jac_nnz=jac_nnz)
+                         has_dx_max=has_dx_max, nroots=nroots, jac_nnz=jac_nnz, nnz=nnz,
+                         has_jtimes=has_jtimes)

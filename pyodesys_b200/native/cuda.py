@@ -190,6 +190,10 @@ class CudaModule:
             _d, _i32, _i32, _i32, _d, ctypes.c_int, ctypes.POINTER(Options)]
         lib.pyodesys_cuda_eval.restype = ctypes.c_int
         lib.pyodesys_cuda_eval.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d, _d]
+        lib.pyodesys_cuda_eval_jtimes.restype = ctypes.c_int
+        lib.pyodesys_cuda_eval_jtimes.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d]
+        lib.pyodesys_cuda_eval_sparse_jac.restype = ctypes.c_int
+        lib.pyodesys_cuda_eval_sparse_jac.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _i32, _i32]
         lib.pyodesys_cuda_lu_solve.restype = ctypes.c_int
         lib.pyodesys_cuda_lu_solve.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _i32]
         lib.pyodesys_cuda_host_alloc.restype = ctypes.c_void_p
@@ -203,6 +207,8 @@ class CudaModule:
         self.ninvar = max(0, int(self.query('ninvar')))
         self.np_tot = int(self.query('np_tot'))
         self.has_jac = bool(self.query('has_jac'))
+        self.nnz = int(self.query('nnz'))  # -1: dense storage (template:131-133)
+        self.has_jtimes = bool(self.query('has_jtimes'))
 
     def query(self, key):
         return self.lib.pyodesys_cuda_query(key.encode())
@@ -436,6 +442,30 @@ class CudaModule:
         self._check(self.lib.pyodesys_cuda_eval(device, n, _ptr(x), _ptr(y), _ptr(params), _ptr(f),
                                                 _ptr(J), _ptr(dfdt)))
         return f, J, dfdt
+
+    def eval_jtimes(self, x, y, params, v, device=0):
+        """ ``J(x, y) v`` for a batch by the generated ``OdeSys::jtimes`` """
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        n = y.shape[0]
+        x = np.ascontiguousarray(np.broadcast_to(np.asarray(x, dtype=np.float64), (n,)))
+        params = np.ascontiguousarray(params, dtype=np.float64).reshape(n, self.np_tot)
+        v = np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.float64), (n, self.ny)))
+        out = np.empty((n, self.ny))
+        self._check(self.lib.pyodesys_cuda_eval_jtimes(device, n, _ptr(x), _ptr(y), _ptr(params), _ptr(v), _ptr(out)))
+        return out
+
+    def eval_sparse_jac(self, x, y, params, device=0):
+        """ ``(data[n, nnz], colptrs[ny + 1], rowvals[nnz])`` by the generated ``OdeSys::sparse_jac_csc`` """
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        n = y.shape[0]
+        x = np.ascontiguousarray(np.broadcast_to(np.asarray(x, dtype=np.float64), (n,)))
+        params = np.ascontiguousarray(params, dtype=np.float64).reshape(n, self.np_tot)
+        data = np.empty((n, max(self.nnz, 0)))
+        colptrs = np.zeros(self.ny + 1, dtype=np.int32)
+        rowvals = np.zeros(max(self.nnz, 0), dtype=np.int32)
+        self._check(self.lib.pyodesys_cuda_eval_sparse_jac(device, n, _ptr(x), _ptr(y), _ptr(params), _ptr(data),
+                                                           _ptr(colptrs, _i32), _ptr(rowvals, _i32)))
+        return data, colptrs, rowvals
 
     def lu_solve(self, A, b, device=0):
         A = np.ascontiguousarray(A, dtype=np.float64)

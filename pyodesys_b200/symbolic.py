@@ -62,9 +62,9 @@ class SymbolicSys(ODESys):
     sparse = False
 
     def __init__(self, dep_exprs, indep=None, params=None, jac=True, dfdx=True,
-                 first_step_expr=None, roots=None, backend=None, lower_bounds=None,
+                 jtimes=False, first_step_expr=None, roots=None, backend=None, lower_bounds=None,
                  upper_bounds=None, linear_invariants=None, nonlinear_invariants=None,
-                 init_indep=None, init_dep=None, **kwargs):
+                 init_indep=None, init_dep=None, sparse=False, **kwargs):
         self.be = get_backend(backend)
         pairs = list(dep_exprs.items()) if isinstance(dep_exprs, dict) else list(dep_exprs)
         self.dep, exprs = zip(*pairs)
@@ -81,6 +81,8 @@ class SymbolicSys(ODESys):
             params = all_free
         self.params = tuple(params)
         self._jac = jac
+        self._dense_jac = jac
+        self._jtimes = tuple(jtimes) if hasattr(jtimes, '__iter__') else jtimes  # symbolic.py:247
         self._dfdx = dfdx
         self.first_step_expr = first_step_expr
         self.roots = roots
@@ -113,6 +115,12 @@ class SymbolicSys(ODESys):
         super().__init__(**kwargs)
         self.linear_invariants = linear_invariants
         self.nonlinear_invariants = nonlinear_invariants
+        self.sparse = sparse
+        if self.sparse:  # symbolic.py:302-303
+            if jac is not True:
+                raise ValueError("sparse=True derives the CSC Jacobian itself: pass jac=True")
+            self.get_jac()
+            self.nnz = len(self._rowvals)
 
     @property
     def ny(self):
@@ -161,15 +169,39 @@ class SymbolicSys(ODESys):
 
     # -- derivation ---------------------------------------------------------------------
     def get_jac(self):
-        """ ``pyodesys/symbolic.py:637-650`` (dense branch). """
+        """ ``pyodesys/symbolic.py:637-650``: the dense ny x ny matrix, or with ``sparse=True`` the row of the nnz
+        structurally non-zero entries in compressed-sparse-column order (``_colptrs``, ``_rowvals`` beside it). """
         if self._jac is True:
-            f = self.be.Matrix(1, self.ny, self.exprs)
-            self._jac = f.jacobian(self.be.Matrix(1, self.ny, self.dep))
+            if self.sparse is True:
+                self._jac, self._colptrs, self._rowvals = self.be.sparse_jacobian_csc(self.exprs, self.dep)
+            else:
+                self._jac = self.get_dense_jac()
         elif self._jac is False:
             return False
         elif not hasattr(self._jac, 'tolist'):
             self._jac = self.be.Matrix(self._jac)
         return self._jac
+
+    def get_dense_jac(self):
+        """ The ny x ny Jacobian whatever the storage hint: the CUDA kernels factorise dense matrices in registers
+        or shared memory.  For a sparse system it is rebuilt from the CSC triple, so the kernels consume exactly
+        the entries ``sparse_jac_csc`` produces. """
+        if self._dense_jac is True:
+            if self.sparse is True:
+                data = self.get_jac()
+                rows = [[0]*self.ny for _ in range(self.ny)]
+                for col in range(self.ny):
+                    for k in range(self._colptrs[col], self._colptrs[col + 1]):
+                        rows[self._rowvals[k]][col] = data[k]
+                self._dense_jac = self.be.Matrix(rows)
+            else:
+                f = self.be.Matrix(1, self.ny, self.exprs)
+                self._dense_jac = f.jacobian(self.be.Matrix(1, self.ny, self.dep))
+        elif self._dense_jac is False:
+            return False
+        elif not hasattr(self._dense_jac, 'tolist'):
+            self._dense_jac = self.be.Matrix(self._dense_jac)
+        return self._dense_jac
 
     def get_dfdx(self):
         """ ``pyodesys/symbolic.py:674-684`` """
@@ -185,7 +217,16 @@ class SymbolicSys(ODESys):
         return self._dfdx
 
     def get_jtimes(self):
-        return False
+        """ ``pyodesys/symbolic.py:652-665``: ``(v, J(y) v)`` as the directional derivative of ``exprs`` along v. """
+        if self._jtimes is False:
+            return False
+        if self._jtimes is True:
+            r = self.be.Dummy('r')
+            v = tuple(self.be.Dummy('v_{0}'.format(i)) for i in range(self.ny))
+            f = self.be.Matrix(1, self.ny, self.exprs)
+            f = f.subs([(x_i, x_i + r*v_i) for x_i, v_i in zip(self.dep, v)])
+            self._jtimes = tuple(zip(v, f.diff(r).subs(r, 0)))
+        return tuple(zip(*self._jtimes))
 
     # -- numeric callbacks (used by tests to cross-check generated device code) -----------
     def _callback(self, exprs):
@@ -204,7 +245,7 @@ class SymbolicSys(ODESys):
         y = np.asarray(y, dtype=np.float64)
         xs = np.broadcast_to(np.asarray(x, dtype=np.float64), y.shape[:-1])[..., None]
         p = np.broadcast_to(np.asarray(p, dtype=np.float64), y.shape[:-1] + (np.shape(p)[-1],))
-        jac = self.get_jac()
+        jac = self.get_dense_jac()
         flat = [jac[i, j] for i in range(self.ny) for j in range(self.ny)]
         out = self._callback(flat)(np.concatenate((xs, y, p), axis=-1))
         return out.reshape(y.shape[:-1] + (self.ny, self.ny))
@@ -253,8 +294,8 @@ class SymbolicSys(ODESys):
                 if k == 'linear_invariants' and val is not None:
                     val = val.tolist()
                 kwargs[k] = val
-        if 'jac' not in kwargs and getattr(ori, '_jac', True) is not True:
-            kwargs['jac'] = ori._jac
+        if 'jac' not in kwargs and getattr(ori, '_dense_jac', True) is not True and not getattr(ori, 'sparse', False):
+            kwargs['jac'] = ori._dense_jac
         if 'dfdx' not in kwargs and getattr(ori, '_dfdx', True) is not True:
             kwargs['dfdx'] = ori._dfdx
         kwargs.setdefault('backend', ori.be)

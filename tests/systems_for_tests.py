@@ -301,12 +301,43 @@ def chain6_roots(compile=True):
         systems.decay_chain_rhs, 6, 5, compile=compile, roots_cb=lambda x, y, p, be: [y[0] - y[1], y[1] - y[2]]))
 
 
+def _damped_osc(x, y, p):
+    """ damped harmonic oscillator of ``pyodesys/native/tests/test_cvode.py:198-204`` (nu=0.01, k=m=1) """
+    return [y[1], -1.0 * y[0] - 0.01 * y[1]]
+
+
+def osc_jtimes(compile=True):
+    """ ``test_jtimes_native_cvode`` (``native/tests/test_cvode.py:198-217``): jac=True, jtimes=True """
+    return _get(('osc_jtimes', compile), lambda: NativeCudaSys.from_callback(
+        _damped_osc, 2, 0, jac=True, jtimes=True, compile=compile))
+
+
+def osc_sparse(compile=True):
+    """ ``test_sparse_jac_native_cvode`` (``native/tests/test_cvode.py:221-238``): jac=True, sparse=True """
+    return _get(('osc_sparse', compile), lambda: NativeCudaSys.from_callback(
+        _damped_osc, 2, 0, jac=True, sparse=True, compile=compile))
+
+
+def decay_k43_sparse(compile=True):
+    """ ``test_SymbolicSys_jacobian_sparse`` (``pyodesys/tests/test_symbolic.py:145-153``) """
+    return _get(('decay_k43_sparse', compile), lambda: NativeCudaSys.from_callback(
+        systems.decay_dydt_factory([4, 3]), 3, 0, sparse=True, compile=compile))
+
+
+def robertson_jtimes_sparse(compile=True):
+    """ Robertson (``pyodesys/tests/_robertson.py:98-101``) with both alternative Jacobian forms: non-linear
+    entries, parameters in the products """
+    return _get(('robertson_jts', compile), lambda: NativeCudaSys.from_callback(
+        systems.robertson_f, 3, 3, jtimes=True, sparse=True, compile=compile))
+
+
 def all_systems(compile=True):
     fns = [expy, decay_err, decay3_dxmax, decay3_first_step, decay3, decay_k43, decay_named, forced, lu6,
            nojac, bounded, loglog_decay4, lin_decay4, loglog_robertson, partsolved_loglog_decay3,
            partsolved_loglog_decay3_multi, growth_root, chain3_roots_0, chain3_roots_1, chain3_roots_2,
            chain3_roots_all, chain3_roots_partsolved_1, leaky_invariant, leaky_chain6, scaled_chain4, decay3_nonneg,
-           partsolved_family, power_decay, chain6_roots]
+           partsolved_family, power_decay, chain6_roots, osc_jtimes, osc_sparse, decay_k43_sparse,
+           robertson_jtimes_sparse]
     out = {}
     for f in fns:
         obj = f(compile=compile)

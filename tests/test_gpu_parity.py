@@ -744,3 +744,74 @@ def test_release_and_failed_call_leave_the_library_usable(cuda_device):
         mod.integrate_predefined_arrays(y0, np.array([0.0, 1.0]), np.full((1000, 3), 2.0), 1e-8, 1e-8, kernel=3)
     third = dec.integrate([0, 1.0], y0, np.full((1000, 1), 2.0))
     assert np.array_equal(np.array(ref.yout), np.array(third.yout))
+
+
+# ---- the alternative Jacobian forms: jtimes (matrix-free product) and sparse_jac_csc ----------------------------
+def test_generated_jtimes_and_sparse_jacobian(cuda_device):
+    """ device ``OdeSys::jtimes`` / ``sparse_jac_csc`` (template:214-243,311-344) against lambdified sympy and the
+    oracle's compilation of the same generated text """
+    s = tsys.robertson_jtimes_sparse()
+    mod = s._native.mod
+    assert mod.has_jtimes and mod.nnz == 7
+    rng = np.random.default_rng(12)
+    n = 1025
+    y = rng.uniform(0.1, 2, size=(n, 3))
+    p = rng.uniform(0.1, 2, size=(n, 3)) * [0.04, 1e4, 3e7]
+    v = rng.standard_normal((n, 3))
+    pf = full_params(y, p)
+    J = s.j_numeric(0.0, y, pf)
+    ref = np.einsum('nij,nj->ni', J, v)
+    Jv = mod.eval_jtimes(0.0, y, pf, v)
+    assert np.allclose(Jv, ref, rtol=1e-13, atol=1e-13*np.abs(ref).max())
+    orc = build_oracle(s._native)
+    Jvo = orc.eval_jtimes(0.0, y, pf, v)
+    assert np.allclose(Jv, Jvo, rtol=1e-13, atol=4e-16*np.abs(Jvo).max())
+    data, colptrs, rowvals = mod.eval_sparse_jac(0.0, y, pf)
+    do, co, ro = orc.eval_sparse_jac(0.0, y, pf, 7)
+    assert np.array_equal(colptrs, co) and np.array_equal(rowvals, ro)  # index work: bit-exact
+    assert colptrs.tolist() == list(s._colptrs) and rowvals.tolist() == list(s._rowvals)
+    assert np.allclose(data, do, rtol=1e-14, atol=0)
+    dense = np.zeros_like(J)
+    for c in range(3):
+        for k in range(colptrs[c], colptrs[c + 1]):
+            dense[:, rowvals[k], c] = data[:, k]
+    assert np.allclose(dense, J, rtol=1e-14, atol=0)
+    _f, Jd, _ = mod.eval_rhs_jac(0.0, y, pf)
+    assert np.array_equal(Jd, dense)  # the kernels' dense matrix is assembled from the CSC entries
+    # systems generated without the options say so instead of returning garbage
+    plain = systems.robertson()._native.mod
+    assert plain.nnz == -1 and not plain.has_jtimes
+    with pytest.raises(RuntimeError, match='jtimes'):
+        plain.eval_jtimes(0.0, y, pf, v)
+    with pytest.raises(RuntimeError, match='sparse'):
+        plain.eval_sparse_jac(0.0, y, pf)
+
+
+@pytest.mark.parametrize('which', ['sparse', 'jtimes'])
+def test_damped_oscillator_sparse_and_jtimes_systems(cuda_device, which):
+    """ ``test_sparse_jac_native_cvode`` / ``test_jtimes_native_cvode`` (native/tests/test_cvode.py:198-238):
+    damped oscillator to t = 100 at atol = rtol = 1e-12 against the closed form, N = 64 copies batched """
+    nu, x0 = 0.01, 1.0
+    odesys = tsys.osc_sparse() if which == 'sparse' else tsys.osc_jtimes()
+    n = 64
+    xout = np.tile(np.linspace(0, 100, 41), (n, 1))
+    y0 = np.tile([x0, 0.0], (n, 1))
+    res = odesys.integrate(xout, y0, atol=1e-12, rtol=1e-12, nsteps=20000, method='bdf')
+    w = (1.0 - nu**2/4.0)**0.5
+    a = (x0**2 + (nu*x0/2)**2/w**2)**0.5
+    phi = np.arctan(nu*x0/(2*x0*w))
+    for r in (res[0], res[n - 1]):
+        ref = a*np.exp(-nu*r.xout/2)*np.cos(w*r.xout - phi)
+        assert r.info['success'] and r.info['njev'] > 0
+        assert np.allclose(r.yout[:, 0], ref, rtol=1e-8, atol=1e-8)
+
+
+def test_sparse_decay_chain_against_bateman(cuda_device):
+    """ ``test_SymbolicSys_jacobian_sparse`` (pyodesys/tests/test_symbolic.py:145-153) """
+    k, y0 = (4, 3), (5, 4, 2)
+    odesys = tsys.decay_k43_sparse()
+    assert odesys.nnz == 4
+    xout, yout, info = odesys.integrate(np.linspace(0, 2, 20), y0, atol=1e-12, rtol=1e-12, nsteps=1000)
+    ref = bateman_full(y0, list(k) + [0], xout - xout[0])
+    assert info['success']
+    assert np.allclose(yout, ref, rtol=1e-10, atol=1e-10)

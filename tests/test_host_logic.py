@@ -34,6 +34,7 @@ def test_c_abi_library_exports_every_declared_symbol():
     names = _declared_symbols()
     assert {'pyodesys_cuda_integrate_predefined', 'pyodesys_cuda_integrate_adaptive', 'pyodesys_cuda_info',
             'pyodesys_cuda_query', 'pyodesys_cuda_last_error', 'pyodesys_cuda_eval', 'pyodesys_cuda_lu_solve',
+            'pyodesys_cuda_eval_jtimes', 'pyodesys_cuda_eval_sparse_jac',
             'pyodesys_cuda_launch_count', 'pyodesys_cuda_host_alloc', 'pyodesys_cuda_host_free',
             'pyodesys_cuda_release'} <= set(names)
     for sysobj in (systems.robertson(), systems.vdp(), systems.radiolysis()):
@@ -243,3 +244,48 @@ def test_bench_reference_arm_contract():
     cb = d['cpu_baseline']
     assert cb['kind'] in ('port', 'reference') and cb['cores'] >= 1 and cb['value'] == d['value'] and cb['sample']
     assert d['e2e'] == {"value": d['value'], "unit": d['unit'], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+
+def test_jtimes_and_sparse_jacobian_codegen_against_sympy():
+    """ ``OdeSys::jtimes`` / ``sparse_jac_csc`` / ``get_nnz`` (odesys_anyode_template.cpp:214-243,311-344,131-133)
+    generated from ``SymbolicSys.get_jtimes`` / ``be.sparse_jacobian_csc`` (symbolic.py:652-665,641): the oracle
+    compiles the same generated text as plain C++; checked against lambdified sympy J and J v """
+    import systems_for_tests as tsys
+    from oracle import build_oracle
+    s = tsys.robertson_jtimes_sparse(compile=False)
+    gen = s._native.gen
+    assert gen.has_jtimes and gen.nnz == 7 and s.nnz == 7
+    assert list(s._colptrs) == [0, 2, 5, 7] and list(s._rowvals) == [0, 1, 0, 1, 2, 0, 1]
+    plain = systems.robertson(compile=False)._native.gen
+    assert plain.nnz == -1 and not plain.has_jtimes
+    orc = build_oracle(s._native)
+    rng = np.random.default_rng(11)
+    n = 33
+    y = rng.uniform(0.1, 2, size=(n, 3))
+    p = rng.uniform(0.1, 2, size=(n, 3)) * [0.04, 1e4, 3e7]
+    v = rng.standard_normal((n, 3))
+    pf = np.concatenate((p, y), axis=1)
+    J = s.j_numeric(0.0, y, pf)
+    Jv = orc.eval_jtimes(0.0, y, pf, v)
+    ref = np.einsum('nij,nj->ni', J, v)
+    assert np.allclose(Jv, ref, rtol=1e-13, atol=1e-13*np.abs(ref).max())
+    data, colptrs, rowvals = orc.eval_sparse_jac(0.0, y, pf, s.nnz)
+    assert colptrs.tolist() == list(s._colptrs) and rowvals.tolist() == list(s._rowvals)
+    dense = np.zeros_like(J)
+    for c in range(3):
+        for k in range(colptrs[c], colptrs[c + 1]):
+            dense[:, rowvals[k], c] = data[:, k]
+    assert np.allclose(dense, J, rtol=1e-14, atol=0)
+    # the dense Jacobian the kernels factorise is assembled from the same CSC entries
+    _f, Jd, _ = orc.eval_rhs_jac(0.0, y, pf)
+    assert np.array_equal(Jd, dense)
+    # the damped oscillator of native/tests/test_cvode.py:198-238: constant Jacobian [[0, 1], [-w0^2, -nu]]
+    osc = tsys.osc_jtimes(compile=False)
+    yo = rng.standard_normal((4, 2))
+    vo = rng.standard_normal((4, 2))
+    Jvo = build_oracle(osc._native).eval_jtimes(0.0, yo, yo, vo)
+    assert np.allclose(Jvo, np.stack((vo[:, 1], -vo[:, 0] - 0.01*vo[:, 1]), axis=1), rtol=1e-15, atol=1e-15)
+    sp_ = tsys.osc_sparse(compile=False)
+    assert sp_.nnz == 3 and list(sp_._colptrs) == [0, 1, 3] and list(sp_._rowvals) == [1, 0, 1]
+    with pytest.raises(RuntimeError):
+        build_oracle(systems.robertson(compile=False)._native).eval_jtimes(0.0, y, pf, v)
