@@ -44,6 +44,8 @@ extern "C" {
 #endif
 
 #define PYODESYS_CUDA_ABI_VERSION 3
+#define PYODESYS_CUDA_LINSOL_DENSE 0
+#define PYODESYS_CUDA_LINSOL_GMRES 1
 
 /* integration methods (``method=`` keyword of the reference wrappers) */
 #define PYODESYS_CUDA_RK4 0        /* fixed step classical Runge-Kutta (pyodesys/integrators.py:17-61) */
@@ -105,7 +107,13 @@ typedef struct pyodesys_cuda_options {
      * arrays follow ptr_kind like every other array; max_roots == 0 (or a system without roots) switches it off. */
     int32_t return_on_root;          /* adaptive mode: the first root ends the integration; its row is the last one */
     int32_t max_roots;               /* capacity per system of root_out / root_indices */
-    int32_t reserved;
+    int32_t linear_solver;           /* method bdf: PYODESYS_CUDA_LINSOL_DENSE (0, default: LU of I - c J in registers;
+                                        what cvode's dense and klu solvers do for ny <= 8) or
+                                        PYODESYS_CUDA_LINSOL_GMRES (1): matrix-free Newton-Krylov on OdeSys::jtimes
+                                        (cvode ``linear_solver='gmres', with_jtimes=True``, _cvode_wrapper.pyx:88-92;
+                                        test_cvode.py:198-217).  No Jacobian is formed (njev stays 0) and
+                                        counters[PYODESYS_CUDA_C_NLU] then counts the J v products (``njvev``).
+                                        (This slot was ``reserved`` = 0 up to ABI v3: old callers get the default.) */
     double *root_out;                /* [n, max_roots, 1 + ny]: rows (x_root, y(x_root)) */
     int32_t *root_indices;           /* [n, max_roots]: adaptive: the row of xyout that holds the root;
                                         predefined: index of the first output point at or behind the root */

@@ -131,6 +131,7 @@ class BatchInfo:
         self.timings = timings or {}
         self.method = method
         self.roots = None  # event-function outputs (root_out / root_indices / nroots_found arrays), if any
+        self.krylov = False  # matrix-free Newton iteration: the factorisation counter holds the J v products
 
     @property
     def params(self):
@@ -157,6 +158,8 @@ class BatchInfo:
         d['n_rhs_evals'] = d['nfev']
         d['dense_n_dls_jac_evals'] = d['njev']
         d['n_lu'] = d.pop('nlu')
+        if self.krylov:  # cvode's name for the products (_cvode_wrapper.pyx:59-75; asserted by test_cvode.py:215)
+            d['njvev'], d['n_lu'] = d['n_lu'], 0
         d['n_solve'] = d.pop('nsolve')
         d['n_err_test_fails'] = d.pop('nreject')
         d['time_wall'] = self.time_wall

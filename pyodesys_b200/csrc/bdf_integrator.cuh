@@ -46,6 +46,78 @@ struct BdfSink {
     __device__ __forceinline__ void setdfdt(int, double) {}
 };
 
+#if ODESYS_HAS_JTIMES
+// Matrix-free linear solve of the Newton iteration (the role of cvode's SPGMR with the user's jtimes,
+// ``linear_solver='gmres', with_jtimes=True``: pyodesys/native/tests/test_cvode.py:198-217): full GMRES on
+// A = I - c J(t, yref), A v formed as v - c * OdeSys::jtimes(v).  Modified Gram-Schmidt Arnoldi with Givens
+// rotations, at most NY iterations (exact in exact arithmetic for an NY-dimensional system), x0 = 0.
+// ``b`` holds the right-hand side on entry and the solution on return; returns the number of J v products.
+// The basis is indexed at run time and lives in local memory: this is the option for systems where forming and
+// factorising J is the expensive part, not the throughput path of the headline configs.
+template <class Sys>
+__device__ __noinline__ int gmres_solve(Sys &sys, double t, const double *yref, double c, double *b) {
+    double V[NY + 1][NY], H[NY + 1][NY], cs[NY], sn[NY], g[NY + 1];
+    double beta = 0.0;
+    for (int i = 0; i < NY; ++i) beta = fma(b[i], b[i], beta);
+    beta = sqrt(beta);
+    if (!(beta > 0.0)) return 0;  // b == 0 (x = 0), or NaN: the caller's norm test sees it
+    const double ibeta = 1.0 / beta;
+    for (int i = 0; i < NY; ++i) V[0][i] = b[i] * ibeta;
+    for (int i = 0; i <= NY; ++i) g[i] = 0.0;
+    g[0] = beta;
+    int m = 0, nmv = 0;
+#pragma unroll 1
+    for (int j = 0; j < NY; ++j) {
+        double w[NY], Jv[NY];
+        sys.jtimes(V[j], Jv, t, yref, nullptr);
+        nmv += 1;
+        for (int i = 0; i < NY; ++i) w[i] = fma(-c, Jv[i], V[j][i]);
+        for (int k = 0; k <= j; ++k) {
+            double d = 0.0;
+            for (int i = 0; i < NY; ++i) d = fma(w[i], V[k][i], d);
+            H[k][j] = d;
+            for (int i = 0; i < NY; ++i) w[i] = fma(-d, V[k][i], w[i]);
+        }
+        for (int k = 0; k <= j; ++k) {  // second Gram-Schmidt pass: keeps the basis orthogonal to rounding
+            double d = 0.0;
+            for (int i = 0; i < NY; ++i) d = fma(w[i], V[k][i], d);
+            H[k][j] += d;
+            for (int i = 0; i < NY; ++i) w[i] = fma(-d, V[k][i], w[i]);
+        }
+        double hn = 0.0;
+        for (int i = 0; i < NY; ++i) hn = fma(w[i], w[i], hn);
+        hn = sqrt(hn);
+        for (int k = 0; k < j; ++k) {
+            const double hk = H[k][j], hk1 = H[k + 1][j];
+            H[k][j] = fma(cs[k], hk, sn[k] * hk1);
+            H[k + 1][j] = fma(-sn[k], hk, cs[k] * hk1);
+        }
+        const double hjj = H[j][j];
+        const double den = sqrt(fma(hjj, hjj, hn * hn));
+        if (!(den > 0.0)) break;  // A singular on the Krylov space (or NaN): solve with what is there
+        cs[j] = hjj / den;
+        sn[j] = hn / den;
+        H[j][j] = den;
+        g[j + 1] = -sn[j] * g[j];
+        g[j] = cs[j] * g[j];
+        m = j + 1;
+        if (hn <= 1e-14 * den || fabs(g[j + 1]) <= 1e-16 * beta || j + 1 == NY) break;
+        const double ihn = 1.0 / hn;
+        for (int i = 0; i < NY; ++i) V[j + 1][i] = w[i] * ihn;
+    }
+    double yk[NY];
+    for (int i = m - 1; i >= 0; --i) {
+        double sacc = g[i];
+        for (int k = i + 1; k < m; ++k) sacc = fma(-H[i][k], yk[k], sacc);
+        yk[i] = sacc / H[i][i];
+    }
+    for (int i = 0; i < NY; ++i) b[i] = 0.0;
+    for (int k = 0; k < m; ++k)
+        for (int i = 0; i < NY; ++i) b[i] = fma(yk[k], V[k][i], b[i]);
+    return nmv;
+}
+#endif
+
 template <> struct Stepper<M_BDF> {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
@@ -68,6 +140,7 @@ template <> struct Stepper<M_BDF> {
     float newton_tol, safety;
     int order, n_equal;
     bool have_lu, jac_current, fresh, newton_failed;
+    bool krylov;  // Newton corrections by gmres_solve on OdeSys::jtimes: no Jacobian, no factorisation
 
     __device__ __forceinline__ double alpha(int k) const { return (1.0 - kBdfKappa[k]) * kBdfGamma[k]; }
     __device__ __forceinline__ double errconst(int k) const { return fma(kBdfKappa[k], kBdfGamma[k], 1.0 / (k + 1)); }
@@ -117,7 +190,12 @@ template <> struct Stepper<M_BDF> {
         int bad = eval_rhs(sys, a, t, y, f0);  // D[1] = f0, scaled by h at the first attempt
 #pragma unroll
         for (int i = 0; i < NY; ++i) Dx(1, i) = f0[i];
-        bad |= eval_jac(sys, t, y);
+#if ODESYS_HAS_JTIMES
+        krylov = a.linear_solver == 1;
+#else
+        krylov = false;
+#endif
+        if (!krylov) bad |= eval_jac(sys, t, y);
         jac_current = true;
         return bad;
     }
@@ -205,8 +283,9 @@ template <> struct Stepper<M_BDF> {
         err = 2.0;
 #pragma unroll
         for (int i = 0; i < NY; ++i) ynew[i] = Dx(0, i);
+        if (krylov) jac_current = true;  // J is applied at (tnew, ypred) by every product
         for (int pass = 0; pass < 2 && !converged; ++pass) {
-            if (!have_lu || c != c_lu) {
+            if (!krylov && (!have_lu || c != c_lu)) {
 #pragma unroll
                 for (int r = 0; r < NY; ++r)
 #pragma unroll
@@ -230,6 +309,10 @@ template <> struct Stepper<M_BDF> {
                 if (st != 0) break;
 #pragma unroll
                 for (int i = 0; i < NY; ++i) dy[i] = fma(c, f[i], -psi[i]) - d[i];
+#if ODESYS_HAS_JTIMES
+                if (krylov) cnt.nlu += gmres_solve(sys, tnew, ypred, c, dy);  // the nlu slot counts J v products (njvev)
+                else
+#endif
                 lin_solve<false>(W, piv, dy);
                 cnt.nsolve += 1;
                 const float nrm = rms(dy);

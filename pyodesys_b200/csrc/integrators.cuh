@@ -56,6 +56,7 @@ struct KernelArgs {
     double get_dx_max_factor;
     int error_outside_bounds;
     double max_invariant_violation;  // != 0: rhs reports a recoverable error when an invariant drifts (template:191-198)
+    int linear_solver;      // BDF: 0 = dense LU of I - c J, 1 = matrix-free GMRES on OdeSys::jtimes (no Jacobian formed)
     // event functions (OdeSys::roots, template:377-396): located on the dense output of every accepted step
     int max_roots;          // capacity per system of root_out / root_indices (0 = no root finding)
     int return_on_root;     // adaptive mode: the first root ends the integration (its row is the last one)

@@ -267,6 +267,12 @@ int check_common(const Common &q) {
         if (pick_kernel(q.method, q.opt) == 3)
             return fail("the shared-memory thread kernel does not locate event functions: pass kernel=1 or kernel=2");
     }
+    if (q.opt && q.opt->linear_solver != PYODESYS_CUDA_LINSOL_DENSE) {
+        if (q.opt->linear_solver != PYODESYS_CUDA_LINSOL_GMRES) return fail("unknown linear_solver %d", q.opt->linear_solver);
+        if (!ODESYS_HAS_JTIMES) return fail("linear_solver gmres needs a system generated with jtimes=True");
+        if (q.method != PYODESYS_CUDA_BDF || !ODESYS_THREAD_BDF)
+            return fail("linear_solver gmres is the matrix-free Newton iteration of method bdf (ny <= 8)");
+    }
     if (q.opt && q.opt->max_invariant_violation != 0.0) {
         if (ODESYS_NINVAR == 0) return fail("max_invariant_violation given but the system defines no invariants");
         if (pick_kernel(q.method, q.opt) == 3) return fail("the shared-memory thread kernel has no invariant guard");
@@ -287,6 +293,7 @@ void fill_args(KernelArgs &a, const Common &q) {
     a.get_dx_max_factor = q.opt ? q.opt->get_dx_max_factor : 0.0;
     a.error_outside_bounds = q.opt ? q.opt->error_outside_bounds : 0;
     a.max_invariant_violation = q.opt ? q.opt->max_invariant_violation : 0.0;
+    a.linear_solver = q.opt ? q.opt->linear_solver : 0;
 #if ODESYS_NROOTS > 0
     if (q.opt && q.opt->max_roots > 0) {
         a.max_roots = q.opt->max_roots;

@@ -60,11 +60,21 @@ class Options(ctypes.Structure):
                 ('kernel', ctypes.c_int32),
                 ('return_on_root', ctypes.c_int32),
                 ('max_roots', ctypes.c_int32),
-                ('reserved', ctypes.c_int32),
+                ('linear_solver', ctypes.c_int32),
                 ('root_out', ctypes.c_void_p),
                 ('root_indices', ctypes.c_void_p),
                 ('nroots_found', ctypes.c_void_p),
                 ('counters_ld', ctypes.c_int64)]
+
+
+def _linear_solver_id(linear_solver='default', with_jtimes=False):
+    key = str(linear_solver).lower()
+    table = {'default': 0, 'dense': 0, 'klu': 0, 'lapack': 0, 'gmres': 1}
+    if key not in table:
+        raise ValueError("Unknown linear_solver: %s (dense, klu, gmres)" % linear_solver)
+    if table[key] == 1 and not with_jtimes:
+        raise ValueError("linear_solver='gmres' is matrix-free here: pass with_jtimes=True (system with jtimes=True)")
+    return table[key]
 
 
 def cache_dir():
@@ -270,14 +280,18 @@ class CudaModule:
 
     @staticmethod
     def _options(get_dx_max_factor=0.0, error_outside_bounds=False, xout_shared=False, schedule=0,
-                 blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, kernel=0, **unknown):
+                 blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, kernel=0,
+                 linear_solver='default', with_jacobian=None, with_jtimes=False, **unknown):
         if unknown:
             raise TypeError("Unknown keyword arguments: %s" % ', '.join(sorted(unknown)))
+        # cvode's names (_cvode_wrapper.pyx:88-92): 'dense' / 'klu' factorise the ny x ny iteration matrix (here: in
+        # registers; for a sparse=True system it is assembled from the CSC entries), 'gmres' is matrix-free on jtimes
+        linsol = _linear_solver_id(linear_solver, with_jtimes)
         sched = {'auto': 0, 'static': 1, 'dynamic': 2}.get(schedule, schedule)
         return Options(float(get_dx_max_factor or 0.0), float(max_invariant_violation or 0.0),
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
                        int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
-                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, 0,
+                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, linsol,
                        None, None, None, 0)
 
     def _root_buffers(self, opts, n, kw_roots):
@@ -647,6 +661,7 @@ class NativeCudaSys(SymbolicSys):
                               return_on_error, nt=intern_x.shape[-1], timings=_tdict(timings), method=method, iv=iv)
         n = len(binfo)
         binfo.roots = roots or None
+        binfo.krylov = _linear_solver_id(kwargs.get('linear_solver', 'default'), kwargs.get('with_jtimes', False)) == 1
         binfo.time_wall = binfo.timings.get('kernel', 0.0)/max(n, 1)
         binfo.time_cpu = (time.time() - t0)/max(n, 1)
         _raise_on_failure(binfo.status, return_on_error)

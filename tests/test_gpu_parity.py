@@ -796,13 +796,22 @@ def test_damped_oscillator_sparse_and_jtimes_systems(cuda_device, which):
     n = 64
     xout = np.tile(np.linspace(0, 100, 41), (n, 1))
     y0 = np.tile([x0, 0.0], (n, 1))
-    res = odesys.integrate(xout, y0, atol=1e-12, rtol=1e-12, nsteps=20000, method='bdf')
+    if which == 'sparse':
+        kw = dict(linear_solver='klu', with_jacobian=True)
+    else:
+        kw = dict(linear_solver='gmres', with_jtimes=True, with_jacobian=False)
+    res = odesys.integrate(xout, y0, atol=1e-12, rtol=1e-12, nsteps=20000, method='bdf', **kw)
     w = (1.0 - nu**2/4.0)**0.5
     a = (x0**2 + (nu*x0/2)**2/w**2)**0.5
     phi = np.arctan(nu*x0/(2*x0*w))
     for r in (res[0], res[n - 1]):
         ref = a*np.exp(-nu*r.xout/2)*np.cos(w*r.xout - phi)
-        assert r.info['success'] and r.info['njev'] > 0
+        assert r.info['success']
+        if which == 'sparse':
+            assert r.info['njev'] > 0
+        else:  # test_cvode.py:215-216
+            assert r.info['njvev'] > 0
+            assert r.info['njev'] == 0
         assert np.allclose(r.yout[:, 0], ref, rtol=1e-8, atol=1e-8)
 
 
@@ -815,3 +824,41 @@ def test_sparse_decay_chain_against_bateman(cuda_device):
     ref = bateman_full(y0, list(k) + [0], xout - xout[0])
     assert info['success']
     assert np.allclose(yout, ref, rtol=1e-10, atol=1e-10)
+
+
+def test_matrix_free_newton_krylov_bdf_on_robertson(cuda_device):
+    """ ``linear_solver='gmres', with_jtimes=True``: stiff Robertson to t = 1e5 with the Newton corrections solved by
+    GMRES on ``OdeSys::jtimes``; every trajectory within max(10 rtol |y|, 10 atol) of the dense-LU BDF kernel and of
+    the oracle's BDF (tolerance of BASELINE.json's north_star), no Jacobian evaluated """
+    s = tsys.robertson_jtimes_sparse()
+    rng = np.random.default_rng(21)
+    n = 777
+    k = np.array([0.04, 1e4, 3e7])*10**rng.uniform(-0.5, 0.5, size=(n, 3))
+    y0 = np.tile([1.0, 0.0, 0.0], (n, 1))
+    rtol, atol = 1e-8, 1e-12
+    xout = np.array([0.0, 1.0, 1e3, 1e5])
+    kw = dict(atol=atol, rtol=rtol, nsteps=50000, method='bdf', force_predefined=True)
+    res_k = s.integrate(xout, y0, k, linear_solver='gmres', with_jtimes=True, **kw)
+    res_d = s.integrate(xout, y0, k, **kw)
+    yk = np.array([r.yout for r in res_k])
+    yd = np.array([r.yout for r in res_d])
+    # both are BDF solutions at rtol: they differ by their (different) accepted global errors
+    ratio = (np.abs(yk - yd)/np.maximum(10*rtol*np.abs(yd), 10*atol)).max()
+    print('gmres vs dense BDF: max err/tol = %.3g' % ratio)
+    assert ratio <= 1.0
+    assert np.abs(yk.sum(axis=2) - 1).max() < 1e-6  # global error of two BDF runs, mass is only conserved to that
+    info = res_k[0].info
+    assert info['success'] and info['njev'] == 0 and info['njvev'] > 0 and info['n_lu'] == 0
+    assert res_d[0].info['njev'] > 0 and 'njvev' not in res_d[0].info
+    # independent referee: the oracle's BDF at a 100 x tighter tolerance
+    mod = s._native
+    orc = build_oracle(mod)
+    m = 64
+    yo, nreached, status, _c = orc.integrate_predefined(y0[:m], np.tile(xout, (m, 1)), full_params(y0[:m], k[:m]),
+                                                        [atol*1e-2], rtol*1e-2, mxsteps=500000, method='bdf')
+    assert (status == 0).all()
+    ratio_o = (np.abs(yk[:m] - yo)/np.maximum(10*rtol*np.abs(yo), 10*atol)).max()
+    print('gmres BDF vs tight oracle BDF: max err/tol = %.3g' % ratio_o)
+    assert ratio_o <= 1.0
+    with pytest.raises((RuntimeError, ValueError), match='jtimes'):
+        systems.robertson().integrate(xout, y0[:2], k[:2], linear_solver='gmres', with_jtimes=True, **kw)
