@@ -123,6 +123,7 @@ class OracleModule:
         lib.oracle_eval.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _d, _d]
         lib.oracle_set_extras.argtypes = [ctypes.c_double, ctypes.c_int, ctypes.c_int, _d, _i32, _i32]
         lib.oracle_lu_solve.argtypes = [ctypes.c_int64, _d, _d, _d, _i32]
+        lib.oracle_set_linear_solver.argtypes = [ctypes.c_int]
         lib.oracle_eval_jtimes.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _d]
         lib.oracle_eval_sparse_jac.argtypes = [ctypes.c_int64, _d, _d, _d, _d, _i32, _i32]
 
@@ -140,6 +141,12 @@ class OracleModule:
 
     def _reset_extras(self):
         self.lib.oracle_set_extras(0.0, 0, 0, None, None, None)
+        self.lib.oracle_set_linear_solver(0)
+
+    def set_linear_solver(self, which):
+        """ 'gmres': the next integrate call (method='bdf') solves its Newton corrections matrix-free on jtimes """
+        if self.lib.oracle_set_linear_solver({'dense': 0, 'gmres': 1}[which]) != 0:
+            raise RuntimeError("oracle: system generated without jtimes")
 
     def max_threads(self):
         return int(self.lib.oracle_max_threads())

@@ -56,6 +56,7 @@ struct Settings {
     double *root_out;       // [n, max_roots, 1 + NY]
     int32_t *root_indices;  // [n, max_roots]
     int32_t *nroots_found;  // [n]
+    int linear_solver;      // BDF: 0 dense LU, 1 matrix-free GMRES on OdeSys::jtimes (oracle_set_linear_solver)
 };
 Settings g_extras = {};
 
@@ -429,6 +430,66 @@ const int BDF_MAXORD = 5;
 const int BDF_NEWTON_MAXITER = 4;
 const double bdf_kappa[6] = {0, -0.1850, -1.0 / 9, -0.0823, -0.0415, 0};
 
+#if ODESYS_HAS_JTIMES
+// Full GMRES (x0 = 0, at most NY iterations, two-pass modified Gram-Schmidt, Givens rotations) on
+// A = I - c J(t, yref) with A v = v - c jtimes(v); b: right-hand side in, solution out; returns the products used.
+// This is this project's own matrix-free solve (role of cvode's SPGMR + user jtimes, test_cvode.py:198-217), stated
+// here with plain sums (no fma) independently of the kernel's register code.
+int gmres_solve(OdeSys &sys, double t, const double *yref, double c, double *b) {
+    double V[NY + 1][NY], H[NY + 1][NY], cs_[NY], sn_[NY], g[NY + 1];
+    double beta = 0;
+    for (int i = 0; i < NY; ++i) beta += b[i] * b[i];
+    beta = std::sqrt(beta);
+    if (!(beta > 0)) return 0;
+    for (int i = 0; i < NY; ++i) V[0][i] = b[i] / beta;
+    for (int i = 0; i <= NY; ++i) g[i] = 0;
+    g[0] = beta;
+    int m = 0, nmv = 0;
+    for (int j = 0; j < NY; ++j) {
+        double w[NY], Jv[NY];
+        sys.jtimes(V[j], Jv, t, yref, nullptr);
+        nmv += 1;
+        for (int i = 0; i < NY; ++i) w[i] = V[j][i] - c * Jv[i];
+        for (int k = 0; k <= j; ++k) H[k][j] = 0;
+        for (int pass = 0; pass < 2; ++pass)
+            for (int k = 0; k <= j; ++k) {
+                double dt = 0;
+                for (int i = 0; i < NY; ++i) dt += w[i] * V[k][i];
+                H[k][j] += dt;
+                for (int i = 0; i < NY; ++i) w[i] -= dt * V[k][i];
+            }
+        double hn = 0;
+        for (int i = 0; i < NY; ++i) hn += w[i] * w[i];
+        hn = std::sqrt(hn);
+        for (int k = 0; k < j; ++k) {
+            const double hk = H[k][j], hk1 = H[k + 1][j];
+            H[k][j] = cs_[k] * hk + sn_[k] * hk1;
+            H[k + 1][j] = -sn_[k] * hk + cs_[k] * hk1;
+        }
+        const double den = std::sqrt(H[j][j] * H[j][j] + hn * hn);
+        if (!(den > 0)) break;
+        cs_[j] = H[j][j] / den;
+        sn_[j] = hn / den;
+        H[j][j] = den;
+        g[j + 1] = -sn_[j] * g[j];
+        g[j] = cs_[j] * g[j];
+        m = j + 1;
+        if (hn <= 1e-14 * den || std::fabs(g[j + 1]) <= 1e-16 * beta || j + 1 == NY) break;
+        for (int i = 0; i < NY; ++i) V[j + 1][i] = w[i] / hn;
+    }
+    double yk[NY];
+    for (int i = m - 1; i >= 0; --i) {
+        double acc = g[i];
+        for (int k = i + 1; k < m; ++k) acc -= H[i][k] * yk[k];
+        yk[i] = acc / H[i][i];
+    }
+    for (int i = 0; i < NY; ++i) b[i] = 0;
+    for (int k = 0; k < m; ++k)
+        for (int i = 0; i < NY; ++i) b[i] += yk[k] * V[k][i];
+    return nmv;
+}
+#endif
+
 struct BDF : StepperBase {
     double D[BDF_MAXORD + 3][NY];
     double Jm[NY * NY];
@@ -442,6 +503,7 @@ struct BDF : StepperBase {
     Settings cs;
     int order = 1, n_equal = 0;
     bool have_lu = false, jac_current = false, fresh = true, newton_failed = false;
+    bool krylov = false;
     bool adaptive() const override { return true; }
 
     static double rms(const double *v, const double *sc) {
@@ -471,7 +533,8 @@ struct BDF : StepperBase {
         for (int i = 0; i < NY; ++i) D[0][i] = y[i];
         int bad = w.rhs(t, y, f0);
         double dfdt[NY];
-        bad |= w.sys.dense_jac_rmaj(t, y, f0, Jm, NY, dfdt);
+        krylov = ODESYS_HAS_JTIMES && w.cfg->linear_solver == 1;
+        if (!krylov) bad |= w.sys.dense_jac_rmaj(t, y, f0, Jm, NY, dfdt);
         jac_current = true;
         return bad;
     }
@@ -533,8 +596,9 @@ struct BDF : StepperBase {
         bool converged = false;
         int n_iter = 0;
         newton_failed = false;
+        if (krylov) jac_current = true;
         while (!converged) {
-            if (!have_lu || c != c_lu) {
+            if (!krylov && (!have_lu || c != c_lu)) {
                 for (int r = 0; r < NY; ++r)
                     for (int q = 0; q < NY; ++q) lu.A(r, q) = (r == q ? 1.0 : 0.0) - c * Jm[r * NY + q];
                 lu.factor();
@@ -553,6 +617,10 @@ struct BDF : StepperBase {
                 const int st = w.rhs(tnew, yk, f);
                 if (st != 0 || !all_finite(f)) break;
                 for (int i = 0; i < NY; ++i) dy[i] = c * f[i] - psi[i] - d[i];
+#if ODESYS_HAS_JTIMES
+                if (krylov) w.nlu += gmres_solve(w.sys, tnew, ypred, c, dy);
+                else
+#endif
                 lu.solve(dy);
                 w.nsolve += 1;
                 const double dy_norm = rms(dy, scale);
@@ -967,6 +1035,7 @@ Settings make_settings(const double *atol, int natol, double rtol, double get_dx
     c.root_out = g_extras.root_out;
     c.root_indices = g_extras.root_indices;
     c.nroots_found = g_extras.nroots_found;
+    c.linear_solver = g_extras.linear_solver;
     return c;
 }
 
@@ -990,6 +1059,14 @@ int oracle_set_extras(double max_invariant_violation, int return_on_root, int ma
     g_extras.root_out = root_out;
     g_extras.root_indices = root_indices;
     g_extras.nroots_found = nroots_found;
+    return 0;
+}
+
+// BDF only: 1 = the Newton corrections are solved by GMRES on OdeSys::jtimes (no Jacobian, no factorisation;
+// counters[3] then counts the J v products) - the CPU restatement of csrc/bdf_integrator.cuh gmres_solve
+int oracle_set_linear_solver(int which) {
+    if (which != 0 && !(which == 1 && ODESYS_HAS_JTIMES)) return -1;
+    g_extras.linear_solver = which;
     return 0;
 }
 

@@ -850,14 +850,24 @@ def test_matrix_free_newton_krylov_bdf_on_robertson(cuda_device):
     info = res_k[0].info
     assert info['success'] and info['njev'] == 0 and info['njvev'] > 0 and info['n_lu'] == 0
     assert res_d[0].info['njev'] > 0 and 'njvev' not in res_d[0].info
-    # independent referee: the oracle's BDF at a 100 x tighter tolerance
-    mod = s._native
-    orc = build_oracle(mod)
+    # the oracle's restatement of the same matrix-free iteration (same tolerances), and as an independent referee
+    # its dense BDF at a 100 x tighter tolerance
+    orc = build_oracle(s._native)
     m = 64
-    yo, nreached, status, _c = orc.integrate_predefined(y0[:m], np.tile(xout, (m, 1)), full_params(y0[:m], k[:m]),
-                                                        [atol*1e-2], rtol*1e-2, mxsteps=500000, method='bdf')
+    pf = full_params(y0[:m], k[:m])
+    orc.set_linear_solver('gmres')
+    yo, _nr, status, co = orc.integrate_predefined(y0[:m], np.tile(xout, (m, 1)), pf, [atol], rtol, mxsteps=50000,
+                                                   method='bdf')
+    assert (status == 0).all() and (co[2] == 0).all() and (co[3] > 0).all()
+    ratio_m = (np.abs(yk[:m] - yo)/np.maximum(10*rtol*np.abs(yo), 10*atol)).max()
+    print('gmres BDF kernel vs oracle gmres BDF: max err/tol = %.3g' % ratio_m)
+    assert ratio_m <= 1.0
+    steps_k = np.array([res_k[i].info['n_steps'] for i in range(m)])
+    assert np.abs(steps_k - co[0]).max() <= 0.05*co[0].max()  # same controller: step counts agree to a few percent
+    yt, _nr, status, _c = orc.integrate_predefined(y0[:m], np.tile(xout, (m, 1)), pf, [atol*1e-2], rtol*1e-2,
+                                                   mxsteps=500000, method='bdf')
     assert (status == 0).all()
-    ratio_o = (np.abs(yk[:m] - yo)/np.maximum(10*rtol*np.abs(yo), 10*atol)).max()
+    ratio_o = (np.abs(yk[:m] - yt)/np.maximum(10*rtol*np.abs(yt), 10*atol)).max()
     print('gmres BDF vs tight oracle BDF: max err/tol = %.3g' % ratio_o)
     assert ratio_o <= 1.0
     with pytest.raises((RuntimeError, ValueError), match='jtimes'):

@@ -266,3 +266,38 @@ def test_bdf_oracle_adaptive_rows_and_dense_output():
     y, nr, st, cn = orc.integrate_predefined(y0, xo, full_params(y0, p), 1e-9, 1e-9, mxsteps=50000, method='bdf')
     assert st[0] == 0 and nr[0] == 41
     assert np.allclose(y[0, :, 0], 2*np.sin(3*xo), atol=2e-6, rtol=0)
+
+
+def test_oracle_matrix_free_bdf_against_closed_form_and_dense():
+    """ the oracle's Newton-Krylov BDF (GMRES on the generated ``jtimes``): the reference's damped oscillator
+    (native/tests/test_cvode.py:198-217: closed form, njvev > 0, njev == 0) and Robertson against the oracle's own
+    dense-LU BDF within max(10 rtol |y|, 10 atol) """
+    import systems_for_tests as tsys
+    from systems_for_tests import full_params
+    from oracle import build_oracle
+    nu, x0 = 0.01, 1.0
+    osc = build_oracle(tsys.osc_jtimes(compile=False)._native)
+    xout = np.linspace(0, 100, 41)[None, :]
+    y0 = np.array([[x0, 0.0]])
+    osc.set_linear_solver('gmres')
+    yout, nreached, status, c = osc.integrate_predefined(y0, xout, y0, [1e-12], 1e-12, mxsteps=20000, method='bdf')
+    assert status[0] == 0 and c[2, 0] == 0 and c[3, 0] > 0
+    w = (1.0 - nu**2/4.0)**0.5
+    a = (x0**2 + (nu*x0/2)**2/w**2)**0.5
+    phi = np.arctan(nu*x0/(2*x0*w))
+    ref = a*np.exp(-nu*xout[0]/2)*np.cos(w*xout[0] - phi)
+    assert np.allclose(yout[0, :, 0], ref, rtol=1e-8, atol=1e-8)
+    rob = build_oracle(tsys.robertson_jtimes_sparse(compile=False)._native)
+    rng = np.random.default_rng(21)
+    n = 8
+    k = np.array([0.04, 1e4, 3e7])*10**rng.uniform(-0.5, 0.5, size=(n, 3))
+    y0 = np.tile([1.0, 0.0, 0.0], (n, 1))
+    xo = np.tile([0.0, 1.0, 1e3, 1e5], (n, 1))
+    rob.set_linear_solver('gmres')
+    yk, _n, st, ck = rob.integrate_predefined(y0, xo, full_params(y0, k), [1e-12], 1e-8, mxsteps=50000, method='bdf')
+    yd, _n, st2, cd = rob.integrate_predefined(y0, xo, full_params(y0, k), [1e-12], 1e-8, mxsteps=50000, method='bdf')
+    assert (st == 0).all() and (st2 == 0).all()
+    assert (ck[2] == 0).all() and (cd[2] > 0).all()  # the setting does not outlive the call
+    assert (np.abs(yk - yd) <= np.maximum(1e-7*np.abs(yd), 1e-11)).all()
+    with pytest.raises(RuntimeError):
+        build_oracle(tsys.decay3(compile=False)._native).set_linear_solver('gmres')
