@@ -102,11 +102,18 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def mark(self):
+        """ the timed region starts now: nvidia-smi was started before the warm-up (its start-up takes longer than a
+        short timed region), only the samples from here on are reported """
+        self.t_mark = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t_end = time.perf_counter()
+        time.sleep(0.03)  # let the sample taken at the end of the region arrive
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -114,7 +121,13 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, power = [], [], set(), []
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        for ln in self.lines:
+        t0 = getattr(self, 't_mark', 0.0)
+        window = [ln for t, ln in self.lines if t0 <= t <= t_end + 0.025]
+        where = 'timed region'
+        if not window:  # region shorter than the sampling period: the last samples of the warm-up (same load)
+            window = [ln for _t, ln in self.lines[-3:]]
+            where = 'end of warm-up (timed region shorter than the 20 ms sampling period)'
+        for ln in window:
             parts = [p.strip() for p in ln.split(',')]
             if len(parts) < 8:
                 continue
@@ -128,7 +141,8 @@ class ClockSampler:
                 if val.lower().startswith('active'):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(power) if power else None, "samples": len(sm), "window": where,
+                "reasons": sorted(reasons)}
 
 
 def fp64_peak(device, seconds=1.5):
@@ -257,6 +271,9 @@ def _main():
             method='rosenbrock4', device=local_rank, stream=stream.cuda_stream, xout_shared=True,
             schedule=args.schedule, blocks_per_sm=args.blocks_per_sm)
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()  # before the peak measurement: nvidia-smi needs a few hundred ms to deliver its first line
     peak_best = peak_sus = None
     if rank == 0:
         peak_best, peak_sus = fp64_peak(local_rank)
@@ -267,10 +284,8 @@ def _main():
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     torch.cuda.synchronize(dev)
+    sampler.mark()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kernel_s = 0.0
     for k in range(args.steps):

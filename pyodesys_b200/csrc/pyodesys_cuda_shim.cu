@@ -27,6 +27,7 @@
 #include "pyodesys_cuda.h"
 
 #include <algorithm>
+#include <vector>
 #include <atomic>
 #include <thread>
 #include <chrono>
@@ -936,29 +937,44 @@ int pyodesys_cuda_release(int device) {
     return 0;
 }
 
+// scratch device buffers of the verification hooks: freed on every return path
+extern "C++" {
+struct Scratch {
+    std::vector<void *> ptrs;
+    ~Scratch() { for (void *p : ptrs) cudaFree(p); }
+    template <class T> T *get(size_t count) {
+        void *p = nullptr;
+        if (cudaMalloc(&p, (count ? count : 1) * sizeof(T)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        ptrs.push_back(p);
+        return (T *)p;
+    }
+};
+}
+#define SCRATCH(var, T, count) T *var = scratch.get<T>(count); if (!var) return fail("out of device memory in a verification hook")
+
 int pyodesys_cuda_eval(int device, int64_t n, const double *x, const double *y, const double *params, double *f,
                        double *jac, double *dfdt) {
     if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
     if (n <= 0) return 0;
     CU_CHECK(cudaSetDevice(device));
     const size_t nn = (size_t)n;
-    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *df = nullptr, *dj = nullptr, *dd = nullptr;
-    CU_CHECK(cudaMalloc(&dx, nn * 8));
-    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
-    CU_CHECK(cudaMalloc(&df, nn * NY * 8));
+    Scratch scratch;
+    SCRATCH(dx, double, nn);
+    SCRATCH(dy, double, nn * NY);
+    SCRATCH(dp, double, nn * NP_TOT);
+    SCRATCH(df, double, nn * NY);
+    double *dj = nullptr, *dd = nullptr;
+    if (jac) { SCRATCH(t, double, nn * NY * NY); dj = t; }
+    if (jac && dfdt) { SCRATCH(t, double, nn * NY); dd = t; }
     CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
     CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
     if (NP_TOT) CU_CHECK(cudaMemcpy(dp, params, nn * NP_TOT * 8, cudaMemcpyHostToDevice));
-    if (jac) CU_CHECK(cudaMalloc(&dj, nn * NY * NY * 8));
-    if (jac && dfdt) CU_CHECK(cudaMalloc(&dd, nn * NY * 8));
     eval_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dx, dy, dp, df, dj, dd);
     g_launches.fetch_add(1);
     CU_CHECK(cudaGetLastError());
     CU_CHECK(cudaMemcpy(f, df, nn * NY * 8, cudaMemcpyDeviceToHost));
     if (dj) CU_CHECK(cudaMemcpy(jac, dj, nn * NY * NY * 8, cudaMemcpyDeviceToHost));
     if (dd) CU_CHECK(cudaMemcpy(dfdt, dd, nn * NY * 8, cudaMemcpyDeviceToHost));
-    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(df); cudaFree(dj); cudaFree(dd);
     return 0;
 }
 
@@ -972,12 +988,12 @@ int pyodesys_cuda_eval_jtimes(int device, int64_t n, const double *x, const doub
     if (n <= 0) return 0;
     CU_CHECK(cudaSetDevice(device));
     const size_t nn = (size_t)n;
-    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *dv = nullptr, *dout = nullptr;
-    CU_CHECK(cudaMalloc(&dx, nn * 8));
-    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
-    CU_CHECK(cudaMalloc(&dv, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dout, nn * NY * 8));
+    Scratch scratch;
+    SCRATCH(dx, double, nn);
+    SCRATCH(dy, double, nn * NY);
+    SCRATCH(dp, double, nn * NP_TOT);
+    SCRATCH(dv, double, nn * NY);
+    SCRATCH(dout, double, nn * NY);
     CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
     CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
     CU_CHECK(cudaMemcpy(dv, v, nn * NY * 8, cudaMemcpyHostToDevice));
@@ -986,7 +1002,6 @@ int pyodesys_cuda_eval_jtimes(int device, int64_t n, const double *x, const doub
     g_launches.fetch_add(1);
     CU_CHECK(cudaGetLastError());
     CU_CHECK(cudaMemcpy(Jv, dout, nn * NY * 8, cudaMemcpyDeviceToHost));
-    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(dv); cudaFree(dout);
     return 0;
 #endif
 }
@@ -1000,15 +1015,14 @@ int pyodesys_cuda_eval_sparse_jac(int device, int64_t n, const double *x, const 
 #else
     if (n <= 0) return 0;
     CU_CHECK(cudaSetDevice(device));
-    const size_t nn = (size_t)n, nz = ODESYS_NNZ > 0 ? ODESYS_NNZ : 1;
-    double *dx = nullptr, *dy = nullptr, *dp = nullptr, *dd = nullptr;
-    int32_t *dc = nullptr, *dr = nullptr;
-    CU_CHECK(cudaMalloc(&dx, nn * 8));
-    CU_CHECK(cudaMalloc(&dy, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dp, nn * (NP_TOT ? NP_TOT : 1) * 8));
-    CU_CHECK(cudaMalloc(&dd, nn * nz * 8));
-    CU_CHECK(cudaMalloc(&dc, (NY + 1) * 4));
-    CU_CHECK(cudaMalloc(&dr, nz * 4));
+    const size_t nn = (size_t)n;
+    Scratch scratch;
+    SCRATCH(dx, double, nn);
+    SCRATCH(dy, double, nn * NY);
+    SCRATCH(dp, double, nn * NP_TOT);
+    SCRATCH(dd, double, nn * ODESYS_NNZ);
+    SCRATCH(dc, int32_t, NY + 1);
+    SCRATCH(dr, int32_t, ODESYS_NNZ);
     CU_CHECK(cudaMemcpy(dx, x, nn * 8, cudaMemcpyHostToDevice));
     CU_CHECK(cudaMemcpy(dy, y, nn * NY * 8, cudaMemcpyHostToDevice));
     if (NP_TOT) CU_CHECK(cudaMemcpy(dp, params, nn * NP_TOT * 8, cudaMemcpyHostToDevice));
@@ -1020,7 +1034,6 @@ int pyodesys_cuda_eval_sparse_jac(int device, int64_t n, const double *x, const 
         CU_CHECK(cudaMemcpy(rowvals, dr, ODESYS_NNZ * 4, cudaMemcpyDeviceToHost));
     }
     CU_CHECK(cudaMemcpy(colptrs, dc, (NY + 1) * 4, cudaMemcpyDeviceToHost));
-    cudaFree(dx); cudaFree(dy); cudaFree(dp); cudaFree(dd); cudaFree(dc); cudaFree(dr);
     return 0;
 #endif
 }
@@ -1028,17 +1041,17 @@ int pyodesys_cuda_eval_sparse_jac(int device, int64_t n, const double *x, const 
 int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double *b, double *x, int32_t *ok) {
     if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
 #if ODESYS_NY > 16
+    (void)n; (void)A; (void)b; (void)x; (void)ok;
     return fail("the register LU hook is limited to ny <= 16");
 #else
     if (n <= 0) return 0;
     CU_CHECK(cudaSetDevice(device));
     const size_t nn = (size_t)n;
-    double *dA = nullptr, *db = nullptr, *dx = nullptr;
-    int32_t *dok = nullptr;
-    CU_CHECK(cudaMalloc(&dA, nn * NY * NY * 8));
-    CU_CHECK(cudaMalloc(&db, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dx, nn * NY * 8));
-    CU_CHECK(cudaMalloc(&dok, nn * 4));
+    Scratch scratch;
+    SCRATCH(dA, double, nn * NY * NY);
+    SCRATCH(db, double, nn * NY);
+    SCRATCH(dx, double, nn * NY);
+    SCRATCH(dok, int32_t, nn);
     CU_CHECK(cudaMemcpy(dA, A, nn * NY * NY * 8, cudaMemcpyHostToDevice));
     CU_CHECK(cudaMemcpy(db, b, nn * NY * 8, cudaMemcpyHostToDevice));
     lu_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, dA, db, dx, dok);
@@ -1046,7 +1059,6 @@ int pyodesys_cuda_lu_solve(int device, int64_t n, const double *A, const double 
     CU_CHECK(cudaGetLastError());
     CU_CHECK(cudaMemcpy(x, dx, nn * NY * 8, cudaMemcpyDeviceToHost));
     CU_CHECK(cudaMemcpy(ok, dok, nn * 4, cudaMemcpyDeviceToHost));
-    cudaFree(dA); cudaFree(db); cudaFree(dx); cudaFree(dok);
     return 0;
 #endif
 }
