@@ -408,8 +408,10 @@ class CudaModule:
 
     # -- reference-shaped entry points --------------------------------------------------------
     @staticmethod
-    def _nfo(i, n, status, counters, timings, mode, nreached=None, roots=None):
+    def _nfo(i, n, status, counters, timings, mode, nreached=None, roots=None, krylov=False):
         d = {k: int(counters[j, i]) for j, k in enumerate(BatchInfo.counter_names)}
+        if krylov:  # matrix-free Newton iteration: the factorisation slot counts the J v products
+            d['njvev'], d['nlu'] = d['nlu'], 0
         d['n_rhs_evals'] = d['nfev']
         d['dense_n_dls_jac_evals'] = d['njev']
         d['time_wall'] = float(timings[0])/n
@@ -430,7 +432,8 @@ class CudaModule:
             return_on_error, roots_sink=roots, **kw)
         _raise_on_failure(status, return_on_error)
         n = yout.shape[0]
-        return yout, [self._nfo(i, n, status, counters, timings, 'predefined', nreached, roots) for i in range(n)]
+        kry = _linear_solver_id(kw.get('linear_solver', 'default'), kw.get('with_jtimes', False)) == 1
+        return yout, [self._nfo(i, n, status, counters, timings, 'predefined', nreached, roots, kry) for i in range(n)]
 
     def integrate_adaptive(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                            mxsteps=0, method=None, autorestart=0, return_on_error=False, **kw):
@@ -442,7 +445,8 @@ class CudaModule:
         n = xyout.shape[0]
         xs = [xyout[i, :nrows[i], 0] for i in range(n)]
         ys = [xyout[i, :nrows[i], 1:] for i in range(n)]
-        return xs, ys, [self._nfo(i, n, status, counters, timings, 'adaptive', None, roots) for i in range(n)]
+        kry = _linear_solver_id(kw.get('linear_solver', 'default'), kw.get('with_jtimes', False)) == 1
+        return xs, ys, [self._nfo(i, n, status, counters, timings, 'adaptive', None, roots, kry) for i in range(n)]
 
     # -- verification hooks -----------------------------------------------------------------
     def eval_rhs_jac(self, x, y, params, device=0, jac=True):

@@ -289,3 +289,18 @@ def test_jtimes_and_sparse_jacobian_codegen_against_sympy():
     assert sp_.nnz == 3 and list(sp_._colptrs) == [0, 1, 3] and list(sp_._rowvals) == [1, 0, 1]
     with pytest.raises(RuntimeError):
         build_oracle(systems.robertson(compile=False)._native).eval_jtimes(0.0, y, pf, v)
+
+
+def test_linear_solver_names_of_the_cvode_wrapper():
+    """ ``linear_solver`` / ``with_jtimes`` (_cvode_wrapper.pyx:88-92): dense and klu map to the register LU, gmres to
+    the matrix-free iteration and needs the generated product """
+    from pyodesys_b200.native.cuda import _linear_solver_id, NativeCudaCode, Options
+    assert _linear_solver_id() == 0 and _linear_solver_id('dense') == 0 and _linear_solver_id('klu') == 0
+    assert _linear_solver_id('gmres', with_jtimes=True) == 1
+    with pytest.raises(ValueError, match='with_jtimes'):
+        _linear_solver_id('gmres')
+    with pytest.raises(ValueError, match='Unknown linear_solver'):
+        _linear_solver_id('bicgstab', with_jtimes=True)
+    # the slot that was ``reserved`` in ABI v3 keeps its offset (old callers passed 0 = dense)
+    assert Options.linear_solver.offset == Options.max_roots.offset + 4
+    assert Options.root_out.offset == Options.linear_solver.offset + 4
