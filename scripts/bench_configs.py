@@ -52,7 +52,7 @@ def run(name, sysobj, b, n, reps, x, check=None, **extra):
 def main():
     from pyodesys_b200 import systems
     args = sys.argv[1:]
-    which = [a for a in args if a in ('c1', 'c2', 'c3', 'c4')] or ['c1', 'c2', 'c4']
+    which = [a for a in args if a in ('c1', 'c2', 'c3', 'c3k', 'c4')] or ['c1', 'c2', 'c4']
     n_override = int(args[args.index('--n') + 1]) if '--n' in args else None
     reps = int(args[args.index('--reps') + 1]) if '--reps' in args else 3
     if 'c1' in which:
@@ -83,6 +83,18 @@ def main():
                         "max_mass_error": float(np.abs(res.yout[:, -1].sum(axis=1) - 1).max()),
                         "flags": os.environ.get('PYODESYS_CUDA_NVCC_FLAGS', '')}
             run('C3 Robertson %s final state' % m, rob, b, n, reps, b['x'], check=check)
+    if 'c3k' in which:
+        # C3 inputs through the matrix-free Newton-Krylov BDF (linear_solver='gmres' on the generated jtimes) and, for
+        # comparison, the dense-LU BDF of the same library
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tests'))
+        import systems_for_tests as tsys
+        n = n_override or 10**6
+        b = systems.batch_robertson(n=n)
+        b['method'] = 'bdf'
+        jts = tsys.robertson_jtimes_sparse()
+        run('C3 Robertson bdf gmres (matrix-free, jtimes)', jts, b, n, reps, b['x'], linear_solver='gmres',
+            with_jtimes=True)
+        run('C3 Robertson bdf dense LU (sparse=True system)', jts, b, n, reps, b['x'])
     if 'c4' in which:
         n = n_override or 10**5
         b = systems.batch_radiolysis(n=n)
