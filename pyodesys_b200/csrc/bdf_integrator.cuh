@@ -54,8 +54,13 @@ struct BdfSink {
 // ``b`` holds the right-hand side on entry and the solution on return; returns the number of J v products.
 // The basis is indexed at run time and lives in local memory: this is the option for systems where forming and
 // factorising J is the expensive part, not the throughput path of the headline configs.
+#if ODESYS_NY <= 4
+#define PYODESYS_GMRES_INLINE __forceinline__  // unrolled, all in registers; an out-of-line call would push sys to the stack
+#else
+#define PYODESYS_GMRES_INLINE __noinline__
+#endif
 template <class Sys>
-__device__ __noinline__ int gmres_solve(Sys &sys, double t, const double *yref, double c, double *b) {
+__device__ PYODESYS_GMRES_INLINE int gmres_solve(Sys &sys, double t, const double *yref, double c, double *b) {
     double V[NY + 1][NY], H[NY + 1][NY], cs[NY], sn[NY], g[NY + 1];
     double beta = 0.0;
     for (int i = 0; i < NY; ++i) beta = fma(b[i], b[i], beta);
@@ -66,18 +71,22 @@ __device__ __noinline__ int gmres_solve(Sys &sys, double t, const double *yref, 
     for (int i = 0; i <= NY; ++i) g[i] = 0.0;
     g[0] = beta;
     int m = 0, nmv = 0;
-#pragma unroll 1
+    // ny <= 4: fully unrolled, every index a literal -> basis and Hessenberg matrix in registers
+    constexpr int kUnroll = NY <= 4 ? NY : 1;
+#pragma unroll kUnroll
     for (int j = 0; j < NY; ++j) {
         double w[NY], Jv[NY];
         sys.jtimes(V[j], Jv, t, yref, nullptr);
         nmv += 1;
         for (int i = 0; i < NY; ++i) w[i] = fma(-c, Jv[i], V[j][i]);
+#pragma unroll kUnroll
         for (int k = 0; k <= j; ++k) {
             double d = 0.0;
             for (int i = 0; i < NY; ++i) d = fma(w[i], V[k][i], d);
             H[k][j] = d;
             for (int i = 0; i < NY; ++i) w[i] = fma(-d, V[k][i], w[i]);
         }
+#pragma unroll kUnroll
         for (int k = 0; k <= j; ++k) {  // second Gram-Schmidt pass: keeps the basis orthogonal to rounding
             double d = 0.0;
             for (int i = 0; i < NY; ++i) d = fma(w[i], V[k][i], d);
@@ -87,6 +96,7 @@ __device__ __noinline__ int gmres_solve(Sys &sys, double t, const double *yref, 
         double hn = 0.0;
         for (int i = 0; i < NY; ++i) hn = fma(w[i], w[i], hn);
         hn = sqrt(hn);
+#pragma unroll kUnroll
         for (int k = 0; k < j; ++k) {
             const double hk = H[k][j], hk1 = H[k + 1][j];
             H[k][j] = fma(cs[k], hk, sn[k] * hk1);
@@ -105,20 +115,32 @@ __device__ __noinline__ int gmres_solve(Sys &sys, double t, const double *yref, 
         const double ihn = 1.0 / hn;
         for (int i = 0; i < NY; ++i) V[j + 1][i] = w[i] * ihn;
     }
+    // back substitution on the leading m x m block; loop bounds are compile-time, m enters as a predicate
     double yk[NY];
-    for (int i = m - 1; i >= 0; --i) {
+#pragma unroll kUnroll
+    for (int i = NY - 1; i >= 0; --i) {
         double sacc = g[i];
-        for (int k = i + 1; k < m; ++k) sacc = fma(-H[i][k], yk[k], sacc);
-        yk[i] = sacc / H[i][i];
+#pragma unroll kUnroll
+        for (int k = i + 1; k < NY; ++k)
+            if (k < m) sacc = fma(-H[i][k], yk[k], sacc);
+        yk[i] = (i < m) ? sacc / H[i][i] : 0.0;
     }
+#pragma unroll
     for (int i = 0; i < NY; ++i) b[i] = 0.0;
-    for (int k = 0; k < m; ++k)
-        for (int i = 0; i < NY; ++i) b[i] = fma(yk[k], V[k][i], b[i]);
+#pragma unroll kUnroll
+    for (int k = 0; k < NY; ++k) {
+        if (k < m) {
+#pragma unroll
+            for (int i = 0; i < NY; ++i) b[i] = fma(yk[k], V[k][i], b[i]);
+        }
+    }
     return nmv;
 }
 #endif
 
-template <> struct Stepper<M_BDF> {
+// KRYLOV = false: LU of I - c J in registers;  true: matrix-free (gmres_solve), a kernel of its own so that the
+// dense path carries none of its registers
+template <bool KRYLOV> struct BdfStepper {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 1;
@@ -140,7 +162,7 @@ template <> struct Stepper<M_BDF> {
     float newton_tol, safety;
     int order, n_equal;
     bool have_lu, jac_current, fresh, newton_failed;
-    bool krylov;  // Newton corrections by gmres_solve on OdeSys::jtimes: no Jacobian, no factorisation
+    static constexpr bool krylov = KRYLOV;  // Newton corrections by gmres_solve on OdeSys::jtimes: no Jacobian, no LU
 
     __device__ __forceinline__ double alpha(int k) const { return (1.0 - kBdfKappa[k]) * kBdfGamma[k]; }
     __device__ __forceinline__ double errconst(int k) const { return fma(kBdfKappa[k], kBdfGamma[k], 1.0 / (k + 1)); }
@@ -190,11 +212,6 @@ template <> struct Stepper<M_BDF> {
         int bad = eval_rhs(sys, a, t, y, f0);  // D[1] = f0, scaled by h at the first attempt
 #pragma unroll
         for (int i = 0; i < NY; ++i) Dx(1, i) = f0[i];
-#if ODESYS_HAS_JTIMES
-        krylov = a.linear_solver == 1;
-#else
-        krylov = false;
-#endif
         if (!krylov) bad |= eval_jac(sys, t, y);
         jac_current = true;
         return bad;
@@ -313,7 +330,7 @@ template <> struct Stepper<M_BDF> {
                 if (krylov) cnt.nlu += gmres_solve(sys, tnew, ypred, c, dy);  // the nlu slot counts J v products (njvev)
                 else
 #endif
-                lin_solve<false>(W, piv, dy);
+                    lin_solve<false>(W, piv, dy);
                 cnt.nsolve += 1;
                 const float nrm = rms(dy);
                 if (!(nrm <= 3.0e38f)) break;  // NaN / inf from the rhs
@@ -341,7 +358,7 @@ template <> struct Stepper<M_BDF> {
             if (converged) {
 #pragma unroll
                 for (int i = 0; i < NY; ++i) ynew[i] = yk[i];
-            } else if (jac_current) {
+            } else if (krylov || jac_current) {
                 break;
             } else {
                 double fp[NY];
@@ -457,6 +474,10 @@ template <> struct Stepper<M_BDF> {
         }
     }
 };
+template <> struct Stepper<M_BDF> : BdfStepper<false> {};
+#if ODESYS_HAS_JTIMES
+template <> struct Stepper<M_BDF_KRYLOV> : BdfStepper<true> {};
+#endif
 
 #endif  // ODESYS_HAS_JAC
 

@@ -33,7 +33,7 @@ constexpr int NP_TOT = ODESYS_NP_TOT;
 constexpr int NP_USED = ODESYS_NP_USED;
 constexpr unsigned FULL_MASK = 0xffffffffu;
 
-enum : int { M_RK4 = 0, M_DOPRI5 = 1, M_ROS4 = 2, M_BDF = 3 };
+enum : int { M_RK4 = 0, M_DOPRI5 = 1, M_ROS4 = 2, M_BDF = 3, M_BDF_KRYLOV = 4 };  // 4: BDF, Newton corrections by GMRES on jtimes
 enum : int { ST_OK = 0, ST_MXSTEPS = 1, ST_STEP_TOO_SMALL = 2, ST_RHS = 3, ST_ROWS = 4 };
 enum : int { C_NSTEPS = 0, C_NFEV = 1, C_NJEV = 2, C_NLU = 3, C_NSOLVE = 4, C_NREJECT = 5, NCOUNT = 6 };
 
@@ -962,7 +962,7 @@ __device__ __noinline__ bool locate_roots(St &st, Sys &sys, const KernelArgs &a,
 #ifndef PYODESYS_BDF_MIN_BLOCKS
 #define PYODESYS_BDF_MIN_BLOCKS (ODESYS_NY <= 4 ? 3 : 1)
 #endif
-#define PYODESYS_MIN_BLOCKS_FOR(METHOD) ((METHOD) == M_BDF ? PYODESYS_BDF_MIN_BLOCKS : PYODESYS_MIN_BLOCKS)
+#define PYODESYS_MIN_BLOCKS_FOR(METHOD) (((METHOD) == M_BDF || (METHOD) == M_BDF_KRYLOV) ? PYODESYS_BDF_MIN_BLOCKS : PYODESYS_MIN_BLOCKS)
 // GUARD: compiled with the invariant test of rhs (max_invariant_violation != 0); the unguarded instantiation is the
 // one every other call runs (the test costs 3.6 % on C3 even when it is switched off at run time).
 template <int METHOD, int MODE, int BLOCK, bool GUARD = false>

@@ -223,7 +223,11 @@ template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cud
     case PYODESYS_CUDA_ROSENBROCK4: return fail("rosenbrock4 needs a Jacobian but the system was generated with jac=False");
 #endif
 #if ODESYS_THREAD_BDF
-    case PYODESYS_CUDA_BDF: return launch<M_BDF, MODE>(c, a, stream, bps);
+    case PYODESYS_CUDA_BDF:
+#if ODESYS_HAS_JTIMES
+        if (a.linear_solver == PYODESYS_CUDA_LINSOL_GMRES) return launch<M_BDF_KRYLOV, MODE>(c, a, stream, bps);
+#endif
+        return launch<M_BDF, MODE>(c, a, stream, bps);
 #elif ODESYS_HAS_JAC
     case PYODESYS_CUDA_BDF: return fail("the BDF kernel keeps its difference table in registers and is limited to ny <= 8; use rosenbrock4");
 #else
