@@ -813,6 +813,12 @@ def test_damped_oscillator_sparse_and_jtimes_systems(cuda_device, which):
             assert r.info['njvev'] > 0
             assert r.info['njev'] == 0
         assert np.allclose(r.yout[:, 0], ref, rtol=1e-8, atol=1e-8)
+    # the reference's own call shape: one system, adaptive mode (every accepted step is a row)
+    tout, yout, info = odesys.integrate(100, [x0, 0], atol=1e-12, rtol=1e-12, nsteps=20000, method='bdf', **kw)
+    ref = a*np.exp(-nu*tout/2)*np.cos(w*tout - phi)
+    assert info['success'] and tout[-1] == 100 and len(tout) > 100
+    assert (info['njvev'] > 0 and info['njev'] == 0) if which == 'jtimes' else info['njev'] > 0
+    assert np.allclose(yout[:, 0], ref, rtol=1e-8, atol=1e-8)
 
 
 def test_sparse_decay_chain_against_bateman(cuda_device):
