@@ -324,7 +324,7 @@ def _main():
         pass
     hbm_peak = peaks.get('hbm_gbs', 6650.0)
     # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, per launch of 1e6 systems, from the committed
-    # ``ncu --set full`` capture (profiles/r1d_ros4_ncu_summary.md); only quoted for the configuration it was taken on
+    # ``ncu --set full`` capture (the summary profiles/ncu_traffic.json names); only quoted for the configuration it was taken on
     traffic = None
     try:
         with open(os.path.join(_root, 'profiles', 'ncu_traffic.json')) as fh:
