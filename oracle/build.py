@@ -4,7 +4,7 @@ ORACLE - TEST INFRASTRUCTURE ONLY.
 
 Build recipes:
 
-* :func:`build_oracle` - ``g++ -O2 -fopenmp`` of ``oracle/oracle.cpp`` against the generated header
+* :func:`build_oracle` - ``g++ -O3 -march=native -fopenmp`` of ``oracle/oracle.cpp`` against the generated header
   of one ODE system -> ``oracle/_build/<tag>/liboracle.so`` (+ ctypes wrapper
   :class:`OracleModule`);
 * :func:`build_ref` - compiles the reference's own LAPACK-free LU
@@ -37,14 +37,42 @@ def _p(a, tp=_d):
 
 
 def _oracle_digest():
-    with open(os.path.join(_here, 'oracle.cpp'), 'rb') as fh:
-        return hashlib.sha256(fh.read()).hexdigest()[:12]
+    h = hashlib.sha256()
+    for path in (os.path.join(_here, 'oracle.cpp'), os.path.join(_csrc, 'odesys_prelude.h')):
+        with open(path, 'rb') as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:12]
 
 
-def build_oracle(native_code):
-    """ ``native_code``: a ``pyodesys_b200.native.cuda.NativeCudaCode`` (only its generated header is used). """
+def _cpu_signature():
+    """ ``-march=native`` binaries only run on CPUs with the same instruction sets: the build tag carries the
+    host's flag list, so a box with another CPU rebuilds (g++ is part of the image) instead of loading them """
+    try:
+        with open('/proc/cpuinfo') as fh:
+            for line in fh:
+                if line.startswith('flags'):
+                    return hashlib.sha256(line.encode()).hexdigest()[:8]
+    except OSError:
+        pass
+    return 'generic'
+
+
+# The reference compiles its generated native code with pycompilation's 'fast' option
+# (pyodesys/native/_base.py:41-42: -O3 -march=native -ffast-math -funroll-loops).  The parity oracle keeps IEEE
+# semantics (its NaN / inf tests must work; no FMA contraction, so its LU stays bit-equal to oracle/_ref) and uses
+# -O3 -march=native -ffp-contract=off; the TIMING build (bench.py's cpu_baseline and --impl reference) uses the
+# reference's full flag set.
+FLAGS_PARITY = ['-O3', '-march=native', '-ffp-contract=off']
+FLAGS_TIMING = ['-O3', '-march=native', '-ffast-math', '-funroll-loops']
+
+
+def build_oracle(native_code, timing=False):
+    """ ``native_code``: a ``pyodesys_b200.native.cuda.NativeCudaCode`` (only its generated header is used).
+    ``timing=True``: the reference's 'fast' flags (results equal to ~1e-14; NaN screens are not reliable). """
     native_code.write_source()
-    tag = hashlib.sha256((native_code.gen.digest + _oracle_digest()).encode()).hexdigest()[:16]
+    flags = FLAGS_TIMING if timing else FLAGS_PARITY
+    tag = hashlib.sha256((native_code.gen.digest + _oracle_digest() + _cpu_signature() +
+                          ' '.join(flags)).encode()).hexdigest()[:16]
     out_dir = os.path.join(_here, '_build', tag)
     so = os.path.join(out_dir, 'liboracle.so')
     with _build_lock:
@@ -52,13 +80,15 @@ def build_oracle(native_code):
     if not exists:
         os.makedirs(out_dir, exist_ok=True)
         tmp = so + '.%d.%d.tmp' % (os.getpid(), threading.get_ident())
-        cmd = ['g++', '-O2', '-std=c++17', '-fopenmp', '-shared', '-fPIC', '-I', native_code.build_dir,
-               '-I', _csrc, os.path.join(_here, 'oracle.cpp'), '-o', tmp]
+        cmd = ['g++'] + flags + ['-std=c++17', '-fopenmp', '-shared', '-fPIC', '-I', native_code.build_dir,
+                                 '-I', _csrc, os.path.join(_here, 'oracle.cpp'), '-o', tmp]
         proc = subprocess.run(cmd, capture_output=True, text=True)
         if proc.returncode != 0:
             raise RuntimeError("g++ failed: %s\n%s" % (' '.join(cmd), proc.stderr[-4000:]))
         os.replace(tmp, so)
-    return OracleModule(so)
+    mod = OracleModule(so)
+    mod.flags = ' '.join(flags)
+    return mod
 
 
 def build_ref(force=False):

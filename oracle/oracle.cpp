@@ -497,9 +497,7 @@ struct BDF : StepperBase {
     double gamma_[BDF_MAXORD + 2], alpha_[BDF_MAXORD + 2], errc_[BDF_MAXORD + 2];
     double f0[NY], d[NY], scale[NY];
     double h_cur = 0, c_lu = 0, newton_tol = 0, safety = 0.9;
-    // local error is controlled at BDF_TOL_FACTOR * (atol, rtol): calibrated so that the accumulated error on the
-    // stiff benchmark problems stays inside max(10 rtol |y|, 10 atol); same constant as csrc/bdf_integrator.cuh
-    static constexpr double BDF_TOL_FACTOR = 0.25;
+    // the tolerances arrive already calibrated (odesys_kappa, odesys_prelude.h)
     Settings cs;
     int order = 1, n_equal = 0;
     bool have_lu = false, jac_current = false, fresh = true, newton_failed = false;
@@ -520,8 +518,6 @@ struct BDF : StepperBase {
             errc_[k] = kap * gamma_[k] + 1.0 / (k + 1);
         }
         cs = *w.cfg;
-        cs.rtol *= BDF_TOL_FACTOR;
-        for (int i = 0; i < NY; ++i) cs.atol[i] *= BDF_TOL_FACTOR;
         const double rtol = cs.rtol;
         newton_tol = std::max(10 * DBL_EPSILON / rtol, std::min(0.03, std::sqrt(rtol)));
         order = 1;
@@ -1019,8 +1015,12 @@ void run_batch(const Job &J, const Settings &cfg, int method, int mode, int nthr
 #ifdef _OPENMP
     if (nthreads > 0) omp_set_num_threads(nthreads);
 #endif
+    // calibrated local-error tolerances (odesys_prelude.h, same table as the CUDA shim)
+    Settings eff = cfg;
+    eff.rtol = odesys_effective_rtol(method, cfg.rtol);
+    for (int i = 0; i < NY; ++i) eff.atol[i] = odesys_kappa(method) * cfg.atol[i];
 #pragma omp parallel for schedule(dynamic, 16)
-    for (int64_t s = 0; s < J.n; ++s) run_one(J, cfg, method, mode, s);
+    for (int64_t s = 0; s < J.n; ++s) run_one(J, eff, method, mode, s);
 }
 
 Settings make_settings(const double *atol, int natol, double rtol, double get_dx_max_factor, int eob) {

@@ -28,11 +28,8 @@ namespace pyodesys_cuda {
 namespace bdfc {
 constexpr int MAXORD = 5;
 constexpr int NEWTON_MAXITER = 4;
-// The error test bounds the LOCAL error of one step; on the stiff benchmark problems the accumulated error of
-// a multistep method at the requested rtol is ~20 rtol.  The stepper therefore controls at TOL_FACTOR * (atol,
-// rtol) so that results stay inside the parity band max(10 rtol |y|, 10 atol) (calibrated on C3, oracle/oracle.cpp
-// uses the same factor).
-constexpr double TOL_FACTOR = 0.25;
+// The tolerances reach the stepper already calibrated (kappa = ODESYS_KAPPA_BDF of odesys_prelude.h, applied by the
+// shim; oracle/oracle.cpp applies the same table).
 }  // namespace bdfc
 // gamma_k = sum_{j<=k} 1/j, alpha_k = (1 - kappa_k) gamma_k, errconst_k = kappa_k gamma_k + 1/(k+1),
 // kappa = {0, -0.1850, -1/9, -0.0823, -0.0415, 0}
@@ -190,9 +187,9 @@ template <bool KRYLOV> struct BdfStepper {
         return bad;
     }
     __device__ __forceinline__ int begin(Sys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y) {
-        rtol_ = bdfc::TOL_FACTOR * tol.rtol;
+        rtol_ = tol.rtol;
 #pragma unroll
-        for (int i = 0; i < NY; ++i) atol_[i] = bdfc::TOL_FACTOR * tol.atol[i];
+        for (int i = 0; i < NY; ++i) atol_[i] = tol.atol[i];
         newton_tol = (float)fmax(10.0 * DBL_EPSILON / rtol_, fmin(0.03, sqrt(rtol_)));
         order = 1;
         n_equal = 0;

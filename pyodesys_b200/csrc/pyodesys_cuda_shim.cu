@@ -289,8 +289,9 @@ void fill_args(KernelArgs &a, const Common &q) {
     memset(&a, 0, sizeof(a));
     a.n = q.n;
     a.counters_ld = (q.ptr_kind == 1 && q.opt && q.opt->counters_ld > 0) ? q.opt->counters_ld : q.n;
-    for (int i = 0; i < NY; ++i) a.atol[i] = q.atol[q.natol == 1 ? 0 : i];
-    a.rtol = q.rtol;
+    // calibrated local-error tolerances: kappa(method) * (atol, rtol), see odesys_prelude.h
+    for (int i = 0; i < NY; ++i) a.atol[i] = odesys_kappa(q.method) * q.atol[q.natol == 1 ? 0 : i];
+    a.rtol = odesys_effective_rtol(q.method, q.rtol);
     a.mxsteps = q.mxsteps;
     a.autorestart = q.autorestart;
     a.iv_from_y0 = (q.opt && q.opt->iv_from_y0) ? 1 : 0;

@@ -159,12 +159,12 @@ def test_vdp_and_lorenz_against_reference_lsoda(golden):
     y0 = np.array(g['y0'])
     y, nr, st, cn = orc.integrate_predefined(y0, g['xout'], full_params(y0, [[1.0]]), 1e-10, 1e-10, mxsteps=5000,
                                              method='dopri5')
-    assert within(y, np.array(g['yout']), 1e-10, 1e-10, factor=1e4).all()
+    assert within(y, np.array(g['yout']), 1e-10, 1e-10, factor=10).all()
     g = golden['lorenz_lsoda']
     orc = _orc(systems.lorenz(compile=False))
     y, nr, st, cn = orc.integrate_predefined([g['y0']], g['xout'], full_params([g['y0']], [g['p']]), 1e-11, 1e-11,
                                              mxsteps=5000, method='dopri5')
-    assert within(y[0], np.array(g['yout']), 1e-11, 1e-11, factor=1e4).all()
+    assert within(y[0], np.array(g['yout']), 1e-11, 1e-11, factor=10).all()
 
 
 def test_dense_output_orders():
