@@ -30,8 +30,8 @@
  *   - return value 0 = OK, <0 = argument or CUDA error (text via pyodesys_cuda_last_error);
  *     failure of an individual system is NOT an error return: it is status[i] != 0 and
  *     (predefined mode) nreached[i] < nt, like ``return_on_error`` in the reference;
- *   - one in-flight call per device per library; distinct devices may be driven from
- *     distinct host threads concurrently.
+ *   - one in-flight call per (device, options.ctx_lane) per library; distinct devices - and the two lanes of one
+ *     device - may be driven from distinct host threads concurrently.
  */
 #ifndef PYODESYS_CUDA_H
 #define PYODESYS_CUDA_H
@@ -43,7 +43,7 @@
 extern "C" {
 #endif
 
-#define PYODESYS_CUDA_ABI_VERSION 3
+#define PYODESYS_CUDA_ABI_VERSION 4
 #define PYODESYS_CUDA_LINSOL_DENSE 0
 #define PYODESYS_CUDA_LINSOL_GMRES 1
 
@@ -120,6 +120,12 @@ typedef struct pyodesys_cuda_options {
     int32_t *nroots_found;           /* [n]: roots met (may exceed max_roots; only the first max_roots are stored) */
     int64_t counters_ld;             /* row length of ``counters`` ([NCOUNTERS, counters_ld]); 0 = n.  Lets several
                                         calls (one per device) fill column ranges of ONE array without a gather */
+    /* ABI v4 */
+    int32_t ctx_lane;                /* 0 or 1: which of the two independent call contexts (streams + staging buffers)
+                                        of ``device`` serves this call.  Calls on different lanes of one device may
+                                        run concurrently from two host threads: the persistent blocks of one call
+                                        move onto the SMs as those of the other drain (multi-GPU driver) */
+    int32_t reserved4;
 } pyodesys_cuda_options;
 
 /* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */
@@ -195,6 +201,11 @@ void pyodesys_cuda_host_free(void *ptr);
  * largest batch seen; the role of ``del systems[idx]`` / ``free`` at the end of the Cython wrappers,
  * _cvode_wrapper.pyx:227-233, for state that here outlives a call).  The next call re-creates what it needs. */
 int pyodesys_cuda_release(int device);
+
+/* PCI bus id of CUDA device ``device`` as text ("0000:1b:00.0", len >= 16): the host-side multi-GPU driver binds the
+ * thread that feeds a GPU to the CPUs of the GPU's NUMA node.  pyodesys_cuda_device_count: visible CUDA devices. */
+int pyodesys_cuda_device_pci_bus_id(int device, char *buf, int len);
+int pyodesys_cuda_device_count(void);
 
 /* Number of kernel launches issued by this library since it was loaded (bench bookkeeping). */
 int64_t pyodesys_cuda_launch_count(void);

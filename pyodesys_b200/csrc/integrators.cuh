@@ -79,19 +79,38 @@ struct KernelArgs {
     unsigned int *slice_done;          // device [ceil(n / slice_len)]: retired systems per output slice (nullptr: off)
     unsigned int *slice_flags;         // host-mapped [nslices]: set to 1 once a slice is complete and visible
     int64_t slice_len;
+    unsigned int *abort_flag;          // host-mapped word: != 0 ends a streaming call early (1: host, 2: input time-out)
+    unsigned long long wait_timeout_ns;
 };
 
-// leader lane: block until the inputs of systems [0, hi) are in device memory
-__device__ __forceinline__ void wait_inputs(const unsigned long long *ready, unsigned long long hi) {
+// leader lane: block until the inputs of systems [0, hi) are in device memory.  Returns false when the call was
+// aborted: the host raised ``abort_flag`` (its copy thread failed) or nothing arrived for ``wait_timeout_ns`` of wall
+// clock (%globaltimer) - the kernel then retires without drawing further systems and the call returns an error; the
+// CUDA context stays usable (a trap would have killed every CUDA user of the process).
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ bool wait_inputs(const unsigned long long *ready, volatile unsigned int *abort_flag,
+                                            unsigned long long timeout_ns, unsigned long long hi) {
     const volatile unsigned long long *r = ready;
     if (*r < hi) {
-        const long long t0 = clock64();
+        const unsigned long long t0 = global_ns();
+        unsigned spin = 0;
         while (*r < hi) {
             __nanosleep(200);
-            if (clock64() - t0 > (1ll << 33)) __trap();  // ~4 s: the copy stream died; fail loudly instead of hanging
+            if ((++spin & 255u) == 0u) {  // the flag lives in host-mapped memory: look at it every ~50 us only
+                if (*abort_flag != 0u) return false;
+                if (global_ns() - t0 > timeout_ns) {
+                    *abort_flag = 2u;  // tells the host why, and every other waiting warp to stop as well
+                    return false;
+                }
+            }
         }
     }
     __threadfence();  // loads of the inputs stay behind the flag read
+    return true;
 }
 
 // a system of an output slice retired: the last one of the slice tells the host, which then copies the slice back
@@ -125,6 +144,8 @@ struct Tol {
 #define PYODESYS_INT_CHECKS 0  /* measured on B200: 20.96 ms with, 20.05 ms without (LOP3 + ISETP replace one DSETP) */
 #endif
 __device__ __forceinline__ int hi_abs(double x) { return __double2hiint(x) & 0x7fffffff; }
+// fixed-point log2 of |x|: biased exponent << 18 | top 18 mantissa bits (three of them can be added in 32 bits)
+__device__ __forceinline__ int lg_fix(double x) { return (__double2hiint(x) >> 2) & 0x1fffffff; }
 __device__ __forceinline__ bool finite_all(const double *v) {
     bool ok = true;
 #if PYODESYS_INT_CHECKS
@@ -567,10 +588,12 @@ __constant__ double kRos4[ros4c::NCOEF] = {
 // cofactor formula when that is safe: the determinant's cancellation is measured (|det| against the sum of
 // the magnitudes of its three terms) and has to keep the relative error of W^-1 a factor 100 below rtol;
 // otherwise this lane falls back to the pivoted LU (AnyODE::getrf semantics) and builds W^-1 from three
-// unit-vector solves.  Either way an inaccurate W^-1 acts as a perturbed Jacobian (W-method): it costs
-// step size through the embedded error estimate, it does not corrupt accepted steps silently.
+// unit-vector solves.
 #ifndef PYODESYS_ROS4_INV3
 #define PYODESYS_ROS4_INV3 1
+#endif
+#ifndef PYODESYS_INV3_INTCHECK
+#define PYODESYS_INV3_INTCHECK 1  /* conditioning test of the cofactor inverse on the integer pipe (0: in double) */
 #endif
 template <bool BRANCH_SWAP, class Mat>
 __device__ __forceinline__ bool lin_factor(Mat &W, int *piv, double rtol, Counters &cnt) {
@@ -578,11 +601,35 @@ __device__ __forceinline__ bool lin_factor(Mat &W, int *piv, double rtol, Counte
         const double a00 = W[0], a01 = W[1], a02 = W[2], a10 = W[3], a11 = W[4], a12 = W[5], a20 = W[6],
                      a21 = W[7], a22 = W[8];
         const double c00 = fma(a11, a22, -a12 * a21), c01 = fma(a12, a20, -a10 * a22), c02 = fma(a10, a21, -a11 * a20);
+#if PYODESYS_INV3_INTCHECK
+        // Is the cofactor formula accurate enough?  Its rounding error relative to |W^-1| is ~ eps * mag / |det| with
+        // mag = the sum of the magnitudes of the six triple products of the determinant (this includes the
+        // cancellation inside the 2x2 cofactors, not only that of the final three-term sum - a cofactor that cancels
+        // makes W^-1 inaccurate while |t0| + |t1| + |t2| still looks harmless; round-1 advisor finding).  The test
+        // only needs magnitude classes, so it runs on the integer pipe: lg(x) = (exponent | top 18 mantissa bits) is a
+        // fixed-point log2 (piecewise linear, error < 0.09 bit), products are sums, the six-term sum is replaced by
+        // its largest term (at most 2.6 bits too small); 4 bits of margin cover both (checked against the double
+        // formula on 4e5 random and nearly singular matrices: never "safe" where the double test says "unsafe").
+        // The FP64 pipe, which bounds this kernel, sees none of it.
+        const double det = fma(a00, c00, fma(a01, c01, a02 * c02));
+        const int v00 = lg_fix(a00), v01 = lg_fix(a01), v02 = lg_fix(a02), v10 = lg_fix(a10), v11 = lg_fix(a11),
+                  v12 = lg_fix(a12), v20 = lg_fix(a20), v21 = lg_fix(a21), v22 = lg_fix(a22);
+        const int m0 = v00 + max(v11 + v22, v12 + v21), m1 = v01 + max(v12 + v20, v10 + v22),
+                  m2 = v02 + max(v10 + v21, v11 + v20);
+        const int vmag = max(m0, max(m1, m2)), vdet = lg_fix(det);
+        // log2(|det| / mag) >= log2(100 eps / rtol) + 4, all in units of 2^-18 bit; 2 * (1023 << 18) puts the single
+        // factor det on the scale of a triple product.  Also false for det = 0, denormal, inf, NaN.
+        const int need = (int)((-45.36f + 4.0f - lg2_ftz((float)rtol)) * 262144.0f);
+        const bool safe = (vdet + 2 * (1023 << 18) - vmag >= need) && vdet >= (1 << 18) && vdet < (0x7ff00000 >> 2);
+#else
         const double t0 = a00 * c00, t1 = a01 * c01, t2 = a02 * c02;
         const double det = t0 + t1 + t2;
-        const double mag = fabs(t0) + fabs(t1) + fabs(t2);
+        // the magnitudes of all six triple products: includes the cancellation inside the 2x2 cofactors
+        const double mag = fabs(a00) * (fabs(a11 * a22) + fabs(a12 * a21)) + fabs(a01) * (fabs(a12 * a20) + fabs(a10 * a22)) +
+                           fabs(a02) * (fabs(a10 * a21) + fabs(a11 * a20));
         // eps * mag / |det| <= rtol / 100  (also false for det = 0, NaN, inf)
         const bool safe = fabs(det) * rtol >= (100.0 * DBL_EPSILON) * mag && fabs(det) <= DBL_MAX && mag > 0.0;
+#endif
         bool ok = true;
         if (__builtin_expect(!safe, 0)) {
             ok = lu_factor<NY, false>(W, piv);
@@ -1006,11 +1053,13 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                     base = atomicAdd(a.work_counter, (unsigned long long)__popc(need));
                     if (a.ready != nullptr && base < (unsigned long long)a.n) {
                         const unsigned long long hi = base + (unsigned long long)__popc(need);
-                        wait_inputs(a.ready, hi < (unsigned long long)a.n ? hi : (unsigned long long)a.n);
+                        if (!wait_inputs(a.ready, a.abort_flag, a.wait_timeout_ns,
+                                         hi < (unsigned long long)a.n ? hi : (unsigned long long)a.n))
+                            base = ~0ull;  // aborted: the drawn indices are dropped, the call returns an error
                     }
                 }
                 base = __shfl_sync(FULL_MASK, base, leader);
-                if (!active && !exhausted) s = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                if (!active && !exhausted) s = (base == ~0ull) ? a.n : (int64_t)base + __popc(need & ((1u << lane) - 1u));
             }
         } else if (!active && !exhausted) {
             s += nthreads;

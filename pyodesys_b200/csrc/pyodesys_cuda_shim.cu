@@ -82,7 +82,9 @@ struct DevCtx {
     unsigned int *h_flags = nullptr, *d_flags = nullptr;
 };
 constexpr int kMaxSlices = 64;
-DevCtx g_ctx[kMaxDev];
+constexpr int kLanes = 2;  // independent call contexts per device (options.ctx_lane): two host threads can keep one GPU busy
+DevCtx g_ctx[kMaxDev][kLanes];
+int lane_of(const pyodesys_cuda_options *opt) { return (opt && opt->ctx_lane > 0 && opt->ctx_lane < kLanes) ? opt->ctx_lane : 0; }
 
 int ctx_init(DevCtx &c, int device) {
     CU_CHECK(cudaSetDevice(device));
@@ -98,7 +100,8 @@ int ctx_init(DevCtx &c, int device) {
     CU_CHECK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
     CU_CHECK(cudaHostAlloc((void **)&c.h_ready, kMaxSlices * sizeof(unsigned long long), cudaHostAllocPortable));
-    CU_CHECK(cudaHostAlloc((void **)&c.h_flags, kMaxSlices * sizeof(unsigned int),
+    // [kMaxSlices] completion flags + [1] abort word (kernel <-> host, see wait_inputs in integrators.cuh)
+    CU_CHECK(cudaHostAlloc((void **)&c.h_flags, (kMaxSlices + 1) * sizeof(unsigned int),
                            cudaHostAllocPortable | cudaHostAllocMapped));
     CU_CHECK(cudaHostGetDevicePointer((void **)&c.d_flags, c.h_flags, 0));
     c.ready = true;
@@ -454,6 +457,17 @@ bool is_pinned(const void *ptr) {
     return at.type == cudaMemoryTypeHost;
 }
 
+// wall-clock limit a streaming kernel waits for one input slice (generous: a profiler, a debugger, MPS time slicing
+// or a pageable copy from swapped memory may hold the copies back for seconds)
+unsigned long long wait_timeout_ns() {
+    double s = 60.0;
+    if (const char *env = getenv("PYODESYS_CUDA_WAIT_TIMEOUT_S")) {
+        const double v = atof(env);
+        if (v > 0.0) s = v;
+    }
+    return (unsigned long long)(s * 1e9);
+}
+
 bool streaming_enabled() {
     const char *env = getenv("PYODESYS_CUDA_STREAMING");
     return !(env && env[0] == '0');
@@ -545,7 +559,7 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
     if ((!xout || !yout || !nreached) && n > 0) return fail("xout/yout/nreached must not be NULL");
     if (timings) for (int i = 0; i < PYODESYS_CUDA_NTIMINGS; ++i) timings[i] = 0.0;
     if (n == 0) return 0;
-    DevCtx &c = g_ctx[device];
+    DevCtx &c = g_ctx[device][lane_of(opt)];
     std::lock_guard<std::mutex> lock(c.mtx);
     if (ctx_init(c, device)) return -1;
 
@@ -603,6 +617,8 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
             c.h_ready[j] = (unsigned long long)std::min<int64_t>(n, sp.lo(j) + sp.len);
             c.h_flags[j] = 0;
         }
+        volatile unsigned int *h_abort = c.h_flags + kMaxSlices;
+        *h_abort = 0;
         auto copy_in = [&](int j, cudaStream_t st) -> int {
             const int64_t lo = sp.lo(j), len = sp.size(j, n);
             if (h2d(c, B_Y0, y0, NY * 8, lo, len, st) || h2d(c, B_PARAMS, prow ? params : nullptr, prow * 8, lo, len, st) ||
@@ -635,6 +651,8 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         ak.slice_done = (unsigned int *)c.buf[B_SLICEDONE];
         ak.slice_flags = c.d_flags;
         ak.slice_len = sp.len;
+        ak.abort_flag = c.d_flags + kMaxSlices;
+        ak.wait_timeout_ns = wait_timeout_ns();
         // The remaining input slices are queued by a helper thread that starts BEFORE the launch.  Copies from
         // pageable memory block the calling thread while the driver stages them, so queued from this thread they
         // would either delay the launch (all input copied first) or, queued after it, never be issued under a tool
@@ -657,10 +675,12 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
                 if (copy_in(j, c.stream2)) return -1;
         } else if (sp.n > 1)
             feeder.th = std::thread([&]() {
-                if (cudaSetDevice(device) != cudaSuccess) { feeder.rc = -1; snprintf(feeder.err, sizeof(feeder.err), "cudaSetDevice failed in the copy thread"); return; }
+                // a failure here raises the abort word at once: the kernel must not wait for inputs that never come
+                if (cudaSetDevice(device) != cudaSuccess) { feeder.rc = -1; *h_abort = 1; snprintf(feeder.err, sizeof(feeder.err), "cudaSetDevice failed in the copy thread"); return; }
                 for (int j = 1; j < sp.n; ++j)
                     if (copy_in(j, c.stream2)) {
                         feeder.rc = -1;
+                        *h_abort = 1;
                         memcpy(feeder.err, g_err, sizeof(feeder.err));  // thread-local text of THIS thread
                         return;
                     }
@@ -670,16 +690,17 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         CU_CHECK(cudaEventRecord(c.ev_k1, c.stream));
         if (feeder.th.joinable()) feeder.th.join();  // D2H copies below go to the same stream, behind the inputs
         if (feeder.rc != 0) return fail("%s", feeder.err);
-        for (int j = 0; j < sp.n; ++j) {
-            // wait for the kernel to complete slice j (or to end: then every slice is complete, or it failed)
+        for (int j = 0; j < sp.n && !*h_abort; ++j) {
+            // wait for the kernel to complete slice j (or to end: then every slice is complete, or it failed).
+            // A short spin catches flags that are about to flip; after that the thread sleeps between polls
+            // instead of burning a core per device for the length of the kernel.
             volatile unsigned int *flag = c.h_flags + j;
             for (unsigned spin = 0; !*flag; ++spin) {
-                if ((spin & 63u) == 63u) {
-                    const cudaError_t q = cudaStreamQuery(c.stream);
-                    if (q == cudaSuccess) break;
-                    if (q != cudaErrorNotReady) return fail("streaming kernel failed: %s", cudaGetErrorString(q));
-                    std::this_thread::yield();
-                }
+                if (spin < 512u) continue;
+                const cudaError_t q = cudaStreamQuery(c.stream);
+                if (q == cudaSuccess) break;
+                if (q != cudaErrorNotReady) return fail("streaming kernel failed: %s", cudaGetErrorString(q));
+                std::this_thread::sleep_for(std::chrono::microseconds(spin < 4096u ? 20 : 100));
             }
             std::atomic_thread_fence(std::memory_order_acquire);
             const int64_t lo = sp.lo(j), len = sp.size(j, n);
@@ -694,6 +715,11 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
         CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
         CU_CHECK(cudaStreamSynchronize(c.stream));
+        if (*h_abort)
+            return fail("streaming call aborted: %s (the CUDA context is intact; PYODESYS_CUDA_STREAMING=0 selects the "
+                        "chunked path, PYODESYS_CUDA_WAIT_TIMEOUT_S the limit)",
+                        *h_abort == 2 ? "the kernel waited longer than the time-out for its next input slice"
+                                      : "the input copy thread failed");
         return pipeline_timings(c, timings, t_begin);
     }
     const ChunkPlan plan = plan_chunks(n, ((size_t)NY + prow + (shared_x ? 0 : nt) + (size_t)nt * NY) * 8 + 32);
@@ -765,7 +791,7 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
     if ((!x0 || !xend || !xyout || !nrows) && n > 0) return fail("x0/xend/xyout/nrows must not be NULL");
     if (timings) for (int i = 0; i < PYODESYS_CUDA_NTIMINGS; ++i) timings[i] = 0.0;
     if (n == 0) return 0;
-    DevCtx &c = g_ctx[device];
+    DevCtx &c = g_ctx[device][lane_of(opt)];
     std::lock_guard<std::mutex> lock(c.mtx);
     if (ctx_init(c, device)) return -1;
 
@@ -872,15 +898,18 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
 // in flight on the library streams: the caller is free to release its buffers as soon as the call returns.
 static void drain_after_failure(int device) {
     if (device < 0 || device >= kMaxDev) return;
-    DevCtx &c = g_ctx[device];
-    std::lock_guard<std::mutex> lock(c.mtx);
-    if (!c.ready) return;
     char keep[sizeof(g_err)];
     memcpy(keep, g_err, sizeof(keep));  // keep the first error text
-    cudaSetDevice(device);
-    cudaStreamSynchronize(c.stream);
-    cudaStreamSynchronize(c.stream2);
-    cudaGetLastError();
+    for (int lane = 0; lane < kLanes; ++lane) {
+        DevCtx &c = g_ctx[device][lane];
+        if (!c.mtx.try_lock()) continue;  // the other lane is inside a call of its own: not ours to drain
+        std::lock_guard<std::mutex> lock(c.mtx, std::adopt_lock);
+        if (!c.ready) continue;
+        cudaSetDevice(device);
+        cudaStreamSynchronize(c.stream);
+        cudaStreamSynchronize(c.stream2);
+        cudaGetLastError();
+    }
     memcpy(g_err, keep, sizeof(keep));
 }
 
@@ -914,32 +943,48 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
 // grow to the largest batch seen).  The next call re-creates what it needs.
 int pyodesys_cuda_release(int device) {
     if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
-    DevCtx &c = g_ctx[device];
-    std::lock_guard<std::mutex> lock(c.mtx);
-    if (!c.ready) return 0;
-    CU_CHECK(cudaSetDevice(device));
-    cudaStreamSynchronize(c.stream);
-    cudaStreamSynchronize(c.stream2);
-    for (int b = 0; b < NBUF; ++b) {
-        if (c.buf[b]) cudaFree(c.buf[b]);
-        c.buf[b] = nullptr;
-        c.cap[b] = 0;
+    for (int lane = 0; lane < kLanes; ++lane) {
+        DevCtx &c = g_ctx[device][lane];
+        std::lock_guard<std::mutex> lock(c.mtx);
+        if (!c.ready) continue;
+        CU_CHECK(cudaSetDevice(device));
+        cudaStreamSynchronize(c.stream);
+        cudaStreamSynchronize(c.stream2);
+        for (int b = 0; b < NBUF; ++b) {
+            if (c.buf[b]) cudaFree(c.buf[b]);
+            c.buf[b] = nullptr;
+            c.cap[b] = 0;
+        }
+        cudaFreeHost(c.h_ready);
+        cudaFreeHost(c.h_flags);
+        c.h_ready = nullptr;
+        c.h_flags = c.d_flags = nullptr;
+        for (auto &e : c.ev) cudaEventDestroy(e);
+        cudaEventDestroy(c.ev_k0);
+        cudaEventDestroy(c.ev_k1);
+        cudaEventDestroy(c.ev_fork);
+        cudaEventDestroy(c.ev_join);
+        cudaStreamDestroy(c.stream);
+        cudaStreamDestroy(c.stream2);
+        c.stream = c.stream2 = nullptr;
+        c.ready = false;
+        cudaGetLastError();
     }
-    cudaFreeHost(c.h_ready);
-    cudaFreeHost(c.h_flags);
-    c.h_ready = nullptr;
-    c.h_flags = c.d_flags = nullptr;
-    for (auto &e : c.ev) cudaEventDestroy(e);
-    cudaEventDestroy(c.ev_k0);
-    cudaEventDestroy(c.ev_k1);
-    cudaEventDestroy(c.ev_fork);
-    cudaEventDestroy(c.ev_join);
-    cudaStreamDestroy(c.stream);
-    cudaStreamDestroy(c.stream2);
-    c.stream = c.stream2 = nullptr;
-    c.ready = false;
-    cudaGetLastError();
     return 0;
+}
+
+// PCI bus id ("0000:1b:00.0") of a CUDA device: lets the host side bind the thread that drives a GPU to the CPUs of
+// the GPU's NUMA node (/sys/bus/pci/devices/<id>/local_cpulist).
+int pyodesys_cuda_device_pci_bus_id(int device, char *buf, int len) {
+    if (!buf || len < 16) return fail("pci bus id buffer too small");
+    CU_CHECK(cudaDeviceGetPCIBusId(buf, len, device));
+    return 0;
+}
+
+int pyodesys_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
 }
 
 // scratch device buffers of the verification hooks: freed on every return path

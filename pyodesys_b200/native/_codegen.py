@@ -287,7 +287,8 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
 
     # ---- which leading entries of m_p are referenced at all ---------------------------------
     used = -1
-    all_final = [e for _s, e in common_cses] + list(common_exprs)
+    # (the invariant expressions are emitted outside the CSE'd groups but read m_p like everything else)
+    all_final = [e for _s, e in common_cses] + list(common_exprs) + list(invar)
     psyms = list(odesys.params) + (list(odesys.init_dep) if odesys.append_iv and odesys.init_dep else [])
     for i, ps in enumerate(psyms):
         if any(ps in sympy.sympify(e).free_symbols for e in all_final):

@@ -64,7 +64,9 @@ class Options(ctypes.Structure):
                 ('root_out', ctypes.c_void_p),
                 ('root_indices', ctypes.c_void_p),
                 ('nroots_found', ctypes.c_void_p),
-                ('counters_ld', ctypes.c_int64)]
+                ('counters_ld', ctypes.c_int64),
+                ('ctx_lane', ctypes.c_int32),
+                ('reserved4', ctypes.c_int32)]
 
 
 def _linear_solver_id(linear_solver='default', with_jtimes=False):
@@ -210,6 +212,9 @@ class CudaModule:
         lib.pyodesys_cuda_host_alloc.argtypes = [ctypes.c_size_t]
         lib.pyodesys_cuda_host_free.restype = None
         lib.pyodesys_cuda_host_free.argtypes = [ctypes.c_void_p]
+        lib.pyodesys_cuda_device_pci_bus_id.restype = ctypes.c_int
+        lib.pyodesys_cuda_device_pci_bus_id.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+        lib.pyodesys_cuda_device_count.restype = ctypes.c_int
         self.pinned = PinnedPool(lib)
         self.nparams = int(self.query('nparams'))
         self.ny = int(self.query('ny'))
@@ -281,7 +286,7 @@ class CudaModule:
     @staticmethod
     def _options(get_dx_max_factor=0.0, error_outside_bounds=False, xout_shared=False, schedule=0,
                  blocks_per_sm=0, max_invariant_violation=0.0, iv_from_y0=False, kernel=0,
-                 linear_solver='default', with_jacobian=None, with_jtimes=False, **unknown):
+                 linear_solver='default', with_jacobian=None, with_jtimes=False, ctx_lane=0, **unknown):
         if unknown:
             raise TypeError("Unknown keyword arguments: %s" % ', '.join(sorted(unknown)))
         # cvode's names (_cvode_wrapper.pyx:88-92): 'dense' / 'klu' factorise the ny x ny iteration matrix (here: in
@@ -292,17 +297,22 @@ class CudaModule:
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
                        int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
                        int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, linsol,
-                       None, None, None, 0)
+                       None, None, None, 0, int(ctx_lane), 0)
 
     def _root_buffers(self, opts, n, kw_roots):
         """ Event functions (``roots=`` of the system): attach the three output arrays of ABI v3 to ``opts``.
-        ``kw_roots`` = (roots_sink, return_on_root, max_roots); the arrays are handed back through the sink. """
-        sink, return_on_root, max_roots = kw_roots
+        ``kw_roots`` = (roots_sink, return_on_root, max_roots, roots_out); the arrays are handed back through the
+        sink.  ``roots_out``: caller-provided (root_out, root_indices, nroots_found) - row ranges of batch-wide arrays
+        (:func:`pyodesys_b200.multi.integrate_sharded`). """
+        sink, return_on_root, max_roots, given = kw_roots
         if sink is None or self.nroots == 0 or max_roots <= 0:
             return None
-        root_out = self.pinned.empty((n, max_roots, 1 + self.ny), np.float64)
-        root_indices = self.pinned.empty((n, max_roots), np.int32)
-        nfound = self.pinned.empty((n,), np.int32)
+        if given is None:
+            root_out = self.pinned.empty((n, max_roots, 1 + self.ny), np.float64)
+            root_indices = self.pinned.empty((n, max_roots), np.int32)
+            nfound = self.pinned.empty((n,), np.int32)
+        else:
+            root_out, root_indices, nfound = given
         opts.return_on_root = int(bool(return_on_root))
         opts.max_roots = int(max_roots)
         opts.root_out = root_out.ctypes.data
@@ -313,7 +323,8 @@ class CudaModule:
 
     @staticmethod
     def _pop_roots(kw):
-        return (kw.pop('roots_sink', None), kw.pop('return_on_root', False), int(kw.pop('max_roots', 8)))
+        return (kw.pop('roots_sink', None), kw.pop('return_on_root', False), int(kw.pop('max_roots', 8)),
+                kw.pop('roots_out', None))
 
     def integrate_predefined_arrays(self, y0, xout, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                     mxsteps=0, method=None, autorestart=0, return_on_error=False,
@@ -359,14 +370,15 @@ class CudaModule:
         xend = np.ascontiguousarray(xend, dtype=np.float64).reshape(-1)
         if x0.size != n or xend.size != n:
             raise ValueError("x0/xend need to be of length N")
+        kw_roots = self._pop_roots(kw)
+        opts = self._options(**kw)
+        has_roots = self._root_buffers(opts, n, kw_roots) is not None
         if max_rows is None:
             # a system can never produce more rows than steps it is allowed to take (+ the start)
             steps = int(mxsteps) if mxsteps else 500
             max_rows = steps*(1 + int(autorestart)) + 1
-        kw_roots = self._pop_roots(kw)
-        opts = self._options(**kw)
-        if self._root_buffers(opts, n, kw_roots) is not None:
-            max_rows += kw_roots[2]  # every stored root is one more row
+            if has_roots:
+                max_rows += kw_roots[2]  # every stored root is one more row
         xyout = self.pinned.empty((n, max_rows, 1 + self.ny), np.float64) if out is None else out
         if out_aux is None:
             nrows = self.pinned.empty((n,), np.int32)
@@ -402,6 +414,26 @@ class CudaModule:
             device, n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size, float(rtol),
             _ptr(dx0), _ptr(dx_min), _ptr(dx_max), int(mxsteps), mid, int(autorestart), 0,
             _ptr(yout), _ptr(nreached, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(timings), 1,
+            ctypes.byref(opts))
+        self._check(rc)
+        return timings
+
+    def integrate_adaptive_device(self, n, y0, x0, xend, params, atol, rtol, max_rows, xyout, nrows, status,
+                                  counters=None, dx0=None, dx_min=None, dx_max=None, mxsteps=0, method=None,
+                                  autorestart=0, device=0, stream=None, **kw):
+        """ Device-resident adaptive call (``ptr_kind=1``): ``xyout[n, max_rows, 1 + ny]`` + ``nrows[n]`` stay on
+        the device.  Returns the timings array. """
+        atol = np.ascontiguousarray(np.atleast_1d(atol), dtype=np.float64)
+        if atol.size != 1 and atol.size != self.ny:
+            raise ValueError("atol needs to be of length 1 or %d" % self.ny)
+        mid = METHODS[(method or self.default_method()).lower()]
+        opts = self._options(**kw)
+        opts.stream = stream
+        timings = np.zeros(NTIMINGS)
+        rc = self.lib.pyodesys_cuda_integrate_adaptive(
+            device, n, _ptr(y0), _ptr(x0), _ptr(xend), _ptr(params), _ptr(atol), atol.size, float(rtol),
+            _ptr(dx0), _ptr(dx_min), _ptr(dx_max), int(mxsteps), mid, int(autorestart), 0, int(max_rows),
+            _ptr(xyout), _ptr(nrows, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(timings), 1,
             ctypes.byref(opts))
         self._check(rc)
         return timings
@@ -640,7 +672,7 @@ class NativeCudaSys(SymbolicSys):
         params = np.ascontiguousarray(intern_p, dtype=np.float64)
         t0 = time.time()
         roots = {}
-        if mod.nroots and not (devices is not None and len(devices) > 1):
+        if mod.nroots:
             kwargs['roots_sink'] = roots
         if devices is not None and len(devices) > 1:
             from ..multi import integrate_sharded

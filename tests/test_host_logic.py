@@ -36,14 +36,14 @@ def test_c_abi_library_exports_every_declared_symbol():
             'pyodesys_cuda_query', 'pyodesys_cuda_last_error', 'pyodesys_cuda_eval', 'pyodesys_cuda_lu_solve',
             'pyodesys_cuda_eval_jtimes', 'pyodesys_cuda_eval_sparse_jac',
             'pyodesys_cuda_launch_count', 'pyodesys_cuda_host_alloc', 'pyodesys_cuda_host_free',
-            'pyodesys_cuda_release'} <= set(names)
+            'pyodesys_cuda_release', 'pyodesys_cuda_device_pci_bus_id', 'pyodesys_cuda_device_count'} <= set(names)
     for sysobj in (systems.robertson(), systems.vdp(), systems.radiolysis()):
         lib = ctypes.CDLL(sysobj._native.so_file)
         for nm in names:
             assert hasattr(lib, nm), nm
         lib.pyodesys_cuda_query.restype = ctypes.c_int64
         lib.pyodesys_cuda_query.argtypes = [ctypes.c_char_p]
-        assert lib.pyodesys_cuda_query(b'abi_version') == 3
+        assert lib.pyodesys_cuda_query(b'abi_version') == 4
         assert lib.pyodesys_cuda_query(b'ny') == sysobj.ny
         assert lib.pyodesys_cuda_query(b'np_tot') == len(sysobj.params) + sysobj.ny  # append_iv, core.py:410-411
         assert lib.pyodesys_cuda_query(b'no such key') == -1
@@ -108,6 +108,15 @@ def test_codegen_two_level_cse_and_flop_counts():
     with pytest.raises(NotImplementedError):  # _base.py:128-129
         s.band = (1, 1)
         _codegen.generate(s)
+    # the kernels load only the first np_used parameter columns: an invariant that reads a parameter the right-hand
+    # side does not use must still find it there (round-1 advisor finding)
+    import sympy
+    y0_, y1_, k0_, k1_ = sympy.symbols('y0 y1 k0 k1', real=True)
+    exprs = [(y0_, -k0_*y0_), (y1_, k0_*y0_)]
+    base = native_sys['cuda'](exprs, params=(k0_, k1_), compile=False)
+    assert base._native.gen.np_used == 1
+    sinv = native_sys['cuda'](exprs, params=(k0_, k1_), nonlinear_invariants=[k1_*(y0_ + y1_)], compile=False)
+    assert sinv._native.gen.np_used == 2 and 'm_p[1]' in sinv._native.gen.text.split('void invariants(')[1]
 
 
 def test_generated_header_compiles_as_plain_cxx_and_matches_sympy():
