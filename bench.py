@@ -268,7 +268,7 @@ def pin_to_gpu_numa_node(device, lib=None):
 def cpu_oracle_runner(wl, seconds, nthreads=None):
     """ Returns (sample size, cores, flags, run(n, seed) -> seconds) for the oracle on all host cores. """
     from oracle import build_oracle
-    orc = build_oracle(wl.odesys._native, timing=True)
+    orc = build_oracle(wl.odesys._native, timing=True, method=wl.method)
     cores = nthreads or os.cpu_count() or 1
 
     def run(n, seed):

@@ -64,13 +64,16 @@ def _cpu_signature():
 # reference's full flag set.
 FLAGS_PARITY = ['-O3', '-march=native', '-ffp-contract=off']
 FLAGS_TIMING = ['-O3', '-march=native', '-ffast-math', '-funroll-loops']
+# the BDF stepper (in the reference: the separately compiled CVODE library, not 'fast' code) does not survive
+# -fassociative-math: its difference-table updates get re-associated and the Newton iteration stops converging
+FLAGS_TIMING_BDF = ['-O3', '-march=native', '-ffast-math', '-fno-associative-math', '-funroll-loops']
 
 
-def build_oracle(native_code, timing=False):
+def build_oracle(native_code, timing=False, method=None):
     """ ``native_code``: a ``pyodesys_b200.native.cuda.NativeCudaCode`` (only its generated header is used).
     ``timing=True``: the reference's 'fast' flags (results equal to ~1e-14; NaN screens are not reliable). """
     native_code.write_source()
-    flags = FLAGS_TIMING if timing else FLAGS_PARITY
+    flags = (FLAGS_TIMING_BDF if method == 'bdf' else FLAGS_TIMING) if timing else FLAGS_PARITY
     tag = hashlib.sha256((native_code.gen.digest + _oracle_digest() + _cpu_signature() +
                           ' '.join(flags)).encode()).hexdigest()[:16]
     out_dir = os.path.join(_here, '_build', tag)

@@ -83,7 +83,8 @@ def test_oracle_within_band_of_reference_fixture(g2, key, method):
 def test_cuda_within_band_of_reference_fixture_and_oracle(cuda_device, g2, key, method):
     sysname, xout, y0, p, ref, rtol, atol, nsteps = _inputs(g2, key)
     odesys = getattr(systems, sysname)()
-    res = odesys.integrate(xout, y0, p, atol=atol, rtol=rtol, nsteps=nsteps, method=method)
+    res = odesys.integrate(xout, y0, p, atol=atol, rtol=rtol, nsteps=nsteps, method=method,
+                           force_predefined=True)
     assert (res.info.status == 0).all()
     yg = np.array(res.yout)
     r_fix = band_ratio(yg, ref, rtol, atol)
