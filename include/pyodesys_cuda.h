@@ -97,9 +97,11 @@ typedef struct pyodesys_cuda_options {
      * kernels take m_p[np + i] from y0[i] themselves: no O(N) host concatenation, ny*8 B less H2D per system. */
     int32_t iv_from_y0;
     int32_t params_ld;               /* leading dimension of ``params`` in doubles; 0 = dense rows */
-    int32_t kernel;                  /* Rosenbrock kernel family: 0 auto (1 for ny <= 8, else 2), 1 one system per
-                                        thread in registers, 2 one system per lane group (ny >= 6), 3 one system
-                                        per thread with W / vectors / parameters in shared memory (ny >= 9) */
+    int32_t kernel;                  /* Rosenbrock kernel family: 0 auto (1 for ny <= 8, else 4, or 2 where 4 lacks a
+                                        feature), 1 one system per thread in registers, 2 one system per lane group
+                                        (ny >= 6), 3 one system per thread with W / vectors / parameters in shared
+                                        memory (ny >= 9), 4 block-cooperative (ny >= 9): lane groups for the linear
+                                        algebra, one system per lane for f and J */
     /* ABI v3.  Event functions: OdeSys::roots (odesys_anyode_template.cpp:377-396), consumed by the cvode wrapper
      * (``return_on_root``, ``root_indices``, ``root_out``: _cvode_wrapper.pyx:89,206-213,354-355).  Sign changes of
      * the nroots functions are located on the dense output of each accepted step to 100 eps (|x| + |h|) (thread and

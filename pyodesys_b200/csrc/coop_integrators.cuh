@@ -1,0 +1,617 @@
+// Batched Rosenbrock integrator for sm_100a, ny ~ 9..32: BLOCK-COOPERATIVE.
+//
+//   * linear algebra: one system per lane group (G = 4, 8, 16 or 32 lanes), W = I/(gamma h) - J distributed by rows
+//     in registers, in-place Gauss-Jordan inverse with partial pivoting + six matrix-vector products per step
+//     (g_invert / g_apply of group_integrators.cuh; AnyODE::getrf_callback/getrs_callback semantics,
+//     anyode_blasless.hpp:10-95);
+//   * right-hand side and Jacobian: ONE SYSTEM PER LANE.  The 256 / G systems of a block step in lock-step; for every
+//     evaluation the lane groups stage their state vectors in shared memory (Y[i][system]), one warp ("evaluator",
+//     the role rotates over the warps of the block) evaluates the generated OdeSys::rhs / dense_jac_sink
+//     (odesys_anyode_template.cpp:147-204,246-293) for all systems of the block - state in registers, parameters in
+//     shared memory P[k][system] - and hands f / J back through shared memory.
+//
+// Why: in the lane-group kernel (group_integrators.cuh) every lane of a group evaluates ALL rows of f and J and keeps
+// the R it owns - the generated expressions are straight-line code that only vectorises across systems.  On the
+// radiolysis network (ny = 14, G = 8) that G-fold redundancy was 48 % of the executed instructions, the kernel
+// spilled (368 M local loads per launch) and reached 5.4 % of the FP64 peak (profiles/r1g_c4_attribution.md); with
+// 32-lane groups (ny = 28) it was 1.3 %.  Here an evaluation costs one warp-instruction per 32 systems.
+//
+// Everything per-system that steers the integration (t, h, controller memory, counters, output cursor) is replicated
+// in the lanes of its group, as in group_ros4_kernel.  Supported: predefined and adaptive output, dx0/dx_min/dx_max
+// arrays, autorestart, bounds / non-negativity guards.  Event functions, the invariant guard and the get_dx0 /
+// get_dx_max expressions stay with the lane-group kernel (the shim routes such calls there).
+// Requires integrators.cuh and group_integrators.cuh first.
+#pragma once
+
+namespace pyodesys_cuda {
+
+#if ODESYS_HAS_JAC
+
+#ifndef PYODESYS_COOP_G
+// smallest group (>= 8 lanes) whose lanes keep their rows of W in at most 56 doubles
+#define PYODESYS_COOP_FITS(g) ((((NY + (g) - 1) / (g)) * NY) <= 56)
+#define PYODESYS_COOP_G (PYODESYS_COOP_FITS(8) ? 8 : PYODESYS_COOP_FITS(16) ? 16 : 32)
+#endif
+#ifndef PYODESYS_COOP_MIN_BLOCKS
+#define PYODESYS_COOP_MIN_BLOCKS (ODESYS_NY <= 16 ? 2 : 1)
+#endif
+
+constexpr int kCoopBlock = 256;
+constexpr int kCoopWarps = kCoopBlock / 32;
+
+template <int S> struct SView {  // array-like view with a compile-time stride: v[i] = p[i * S]
+    double *p;
+    __device__ __forceinline__ double &operator[](int i) const { return p[i * S]; }
+};
+
+// Shared memory of one block (doubles).  "[i][system]" arrays have the odd pitch NSYSP: the evaluator (lane = system)
+// reads consecutive words, the lanes of a group (lane = row i) hit distinct banks.
+template <int G> struct CoopLayout {
+    static constexpr int R = (NY + G - 1) / G;
+    static constexpr int NSYS = kCoopBlock / G;    // systems per block
+    static constexpr int NSYSP = NSYS | 1;
+    static constexpr int NYP = NY | 1;              // row pitch of the Jacobian staging
+    static constexpr int NE = (NSYS + 31) / 32;    // evaluator warps per evaluation
+    static constexpr int NPU = NP_USED > 0 ? NP_USED : 1;
+    static constexpr int NPC = ODESYS_NPCSE > 0 ? ODESYS_NPCSE : 1;
+    static constexpr int oP = 0;                                     // parameters [k][system]
+    static constexpr int oPC = oP + NPU * NSYS;                      // parameter-only sub-expressions [k][system]
+    static constexpr int oY = oPC + NPC * NSYS;                      // staged state [i][system]
+    static constexpr int oF = oY + NY * NSYSP;                       // f [i][system]
+    static constexpr int oX = oF + NY * NSYSP;                       // abscissa [system]
+    static constexpr int oDF = oX + NSYS;                            // dfdt [i][system] (non-autonomous systems)
+    static constexpr int oJ = oDF + (ODESYS_AUTONOMOUS ? 0 : NY * NSYSP);  // Jacobian [(i * NYP + j)][system]
+    static constexpr int oScr = oJ + NY * NYP * NSYSP;               // per system: prow[NY], ys[NY] (g_invert / g_apply)
+    static constexpr int oG = oScr + 2 * NY * NSYS;                  // stage increments g1..g5 [k][system][i]
+    static constexpr int oInt = oG + 5 * NY * NSYS;                  // ints: status[NSYS], fresh[NSYS]
+    static constexpr int kDoubles = oInt + NSYS;
+    typedef odesys_anyode::OdeSysT<SView<NSYS>> ESys;
+};
+
+template <int G> struct CoopSinkJ {
+    typedef CoopLayout<G> L;
+    double *J, *DF;  // already offset by the evaluator's system
+    __device__ __forceinline__ void setj(int i, int j, double v) { J[(i * L::NYP + j) * L::NSYSP] = v; }
+    __device__ __forceinline__ void setdfdt(int i, double v) {
+        if (!ODESYS_AUTONOMOUS) DF[i * L::NSYSP] = v;
+    }
+};
+
+// f (and J) for one system of the block, state in registers, parameters / results in shared memory.  One out-of-line
+// copy per variant (a Rosenbrock step has seven evaluation sites); only the evaluator lanes make the call, so the
+// other warps pay neither for its code nor for its register save area.
+template <int G, bool JAC>
+__device__ __noinline__ void coop_eval_one(int e, int error_outside_bounds) {
+    typedef CoopLayout<G> L;
+    extern __shared__ double c_smem[];
+    double *sm = c_smem;
+    typename L::ESys es;
+    es.m_p = SView<L::NSYS>{sm + L::oP + e};
+    es.m_p_cse = SView<L::NSYS>{sm + L::oPC + e};
+    int *ist = reinterpret_cast<int *>(sm + L::oInt);
+    if (ist[L::NSYS + e]) {  // parameters of a new system arrived: parameter-only sub-expressions (template:104-110)
+        es.setup();
+        ist[L::NSYS + e] = 0;
+    }
+    es.nfev = 0;
+    es.njev = 0;
+    double y[NY], f[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) y[i] = sm[L::oY + i * L::NSYSP + e];
+    const double x = sm[L::oX + e];
+    int st = es.rhs(x, y, f);
+#if ODESYS_HAS_BOUNDS
+    if (error_outside_bounds && es.outside_bounds(y)) st = AnyODE::Status::recoverable_error;
+#endif
+#if ODESYS_NONNEGATIVE
+#pragma unroll
+    for (int i = 0; i < NY; ++i)
+        if (y[i] < 0) st = AnyODE::Status::recoverable_error;
+#endif
+    AnyODE::ignore(error_outside_bounds);
+#pragma unroll
+    for (int i = 0; i < NY; ++i) sm[L::oF + i * L::NSYSP + e] = f[i];
+    if (JAC) {
+        CoopSinkJ<G> sink{sm + L::oJ + e, sm + L::oDF + e};
+        st |= es.dense_jac_sink(x, y, sink);
+    }
+    ist[e] = st;
+}
+
+// executed by every thread of the block between two block barriers; the evaluator role rotates over the warps
+template <int G, bool JAC> __device__ __forceinline__ void coop_evaluate(int evalno, int error_outside_bounds) {
+    typedef CoopLayout<G> L;
+    __syncthreads();  // staged states (Y, X) are complete
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rel = (warp - (evalno % kCoopWarps) + kCoopWarps) % kCoopWarps;
+    const int e = rel * 32 + lane;
+    if (rel < L::NE && e < L::NSYS) coop_eval_one<G, JAC>(e, error_outside_bounds);
+    __syncthreads();  // results (F, J, status) are complete
+}
+
+template <int G> struct Coop {
+    typedef CoopLayout<G> L;
+    static constexpr int R = L::R;
+    int sysl;     // local index of this lane's system inside the block
+    int evalno;   // evaluations so far (block uniform): rotates the evaluator role over the warps
+
+    // stage the distributed vector yv, evaluate, bring back the rows this lane owns; returns the callback status
+    template <bool JAC>
+    __device__ __forceinline__ int eval(const Grp<G> &g, const KernelArgs &a, double x, const double *yv, double *f) {
+        extern __shared__ double c_smem[];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (g.owns(r)) c_smem[L::oY + (r * G + g.gl) * L::NSYSP + sysl] = yv[r];
+        if (g.gl == 0) c_smem[L::oX + sysl] = x;
+        coop_evaluate<G, JAC>(evalno, a.error_outside_bounds);
+        evalno += 1;
+#pragma unroll
+        for (int r = 0; r < R; ++r) f[r] = g.owns(r) ? c_smem[L::oF + (r * G + g.gl) * L::NSYSP + sysl] : 0.0;
+        return reinterpret_cast<const int *>(c_smem + L::oInt)[sysl];
+    }
+    // stage increment g_k (k = 0..4) of this lane's rows lives in shared memory (five vectors of R doubles per lane
+    // are the difference between 128 registers with spills and without)
+    __device__ __forceinline__ double gk(const Grp<G> &g, int k, int r) const {
+        extern __shared__ double c_smem[];
+        return g.owns(r) ? c_smem[L::oG + (k * L::NSYS + sysl) * NY + r * G + g.gl] : 0.0;
+    }
+    __device__ __forceinline__ void set_gk(const Grp<G> &g, int k, int r, double v) const {
+        extern __shared__ double c_smem[];
+        if (g.owns(r)) c_smem[L::oG + (k * L::NSYS + sysl) * NY + r * G + g.gl] = v;
+    }
+};
+
+#define RC(name) kRos4[ros4c::name]
+template <int G> struct CoopRos4 {
+    typedef CoopLayout<G> L;
+    static constexpr int R = L::R;
+    double h_old;
+    float err_old;
+    bool first, last_rejected;
+
+    __device__ __forceinline__ void begin() {
+        first = true;
+        last_rejected = false;
+        h_old = 0.0;
+        err_old = 1.0f;
+    }
+
+    // Hairer's starting step (initial_step in integrators.cuh); executed by every thread of the block (two
+    // evaluation slots), the result is used by the groups that asked for it
+    __device__ __forceinline__ double auto_step(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t0,
+                                                const double *y, double span, int &nfev) {
+        double f0[R], y1[R], f1[R];
+        c.template eval<false>(g, a, t0, y, f0);
+        double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (!g.owns(r)) continue;
+            const double isk = fast_rcp<1>(a.atol[r * G + g.gl] + a.rtol * fabs(y[r]) + 1e-300);
+            d0 = fmax(d0, fabs(y[r]) * isk);
+            d1 = fmax(d1, fabs(f0[r]) * isk);
+        }
+        d0 = gmax_d<G>(g, d0);
+        d1 = gmax_d<G>(g, d1);
+        double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+        h0 = fmin(h0, fabs(span));
+        if (!(h0 > 0.0)) h0 = 1e-6;  // idle group (span 0): keep the arithmetic finite
+        const double dir = span >= 0 ? 1.0 : -1.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) y1[r] = fma(dir * h0, f0[r], y[r]);
+        const int st = c.template eval<false>(g, a, t0 + dir * h0, y1, f1);
+        nfev += 2;
+        double d2 = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (!g.owns(r)) continue;
+            const double isk = fast_rcp<1>(a.atol[r * G + g.gl] + a.rtol * fabs(y[r]) + 1e-300);
+            d2 = fmax(d2, fabs(f1[r] - f0[r]) * isk);
+        }
+        d2 = gmax_d<G>(g, d2) / h0;
+        if (st != 0 || !(d2 <= DBL_MAX)) d2 = 0.0;
+        const double dmax = fmax(d1, d2);
+        const double h1 = (dmax <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : fast_pow(0.01 * fast_rcp<1>(dmax), 0.25f);
+        return fmin(fmin(100.0 * h0, h1), fabs(span)) * dir;
+    }
+
+    __device__ __forceinline__ int attempt(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t, const double *y,
+                                           double h, double *ynew, double &err, Counters &cnt) {
+        extern __shared__ double c_smem[];
+        double W[R][NY], dfdt[R], f[R], tmp[R], b[R];
+        int ord[R];
+        int bad = c.template eval<true>(g, a, t, y, f);
+        const double ih = fast_rcp<2>(h);
+        const double diag = 4.0 * ih;  // 1/gamma = 4
+        // W = I/(gamma h) - J: the rows this lane owns, from the Jacobian the evaluator left in shared memory
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int i = g.owns(r) ? r * G + g.gl : 0;
+            const double *row = c_smem + L::oJ + (i * L::NYP) * L::NSYSP + c.sysl;
+#pragma unroll
+            for (int j = 0; j < NY; ++j) {
+                const double v = row[j * L::NSYSP];
+                W[r][j] = g.owns(r) ? ((i == j) ? diag - v : -v) : 0.0;
+            }
+            dfdt[r] = (!ODESYS_AUTONOMOUS && g.owns(r)) ? c_smem[L::oDF + i * L::NSYSP + c.sysl] : 0.0;
+        }
+        if (!g_invert<G>(g, W, ord)) bad |= 1;
+#define G_SOLVE(vec) g_apply<G>(g, W, ord, vec)
+        cnt.nlu += 1;
+        cnt.nsolve += 6;
+#pragma unroll
+        for (int r = 0; r < R; ++r) b[r] = ODESYS_AUTONOMOUS ? f[r] : fma(h * RC(D1), dfdt[r], f[r]);
+        G_SOLVE(b);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            c.set_gk(g, 0, r, b[r]);
+            tmp[r] = fma(RC(A21), b[r], y[r]);
+        }
+        bad |= c.template eval<false>(g, a, fma(RC(C2X), h, t), tmp, f);
+        const double c21 = RC(C21) * ih;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            b[r] = fma(c21, c.gk(g, 0, r), f[r]);
+            if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D2), dfdt[r], b[r]);
+        }
+        G_SOLVE(b);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            c.set_gk(g, 1, r, b[r]);
+            tmp[r] = fma(RC(A32), b[r], fma(RC(A31), c.gk(g, 0, r), y[r]));
+        }
+        bad |= c.template eval<false>(g, a, fma(RC(C3X), h, t), tmp, f);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            b[r] = fma(ih, fma(RC(C32), c.gk(g, 1, r), RC(C31) * c.gk(g, 0, r)), f[r]);
+            if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D3), dfdt[r], b[r]);
+        }
+        G_SOLVE(b);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            c.set_gk(g, 2, r, b[r]);
+            tmp[r] = fma(RC(A43), b[r], fma(RC(A42), c.gk(g, 1, r), fma(RC(A41), c.gk(g, 0, r), y[r])));
+        }
+        bad |= c.template eval<false>(g, a, fma(RC(C4X), h, t), tmp, f);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            b[r] = fma(ih, fma(RC(C43), c.gk(g, 2, r), fma(RC(C42), c.gk(g, 1, r), RC(C41) * c.gk(g, 0, r))), f[r]);
+            if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D4), dfdt[r], b[r]);
+        }
+        G_SOLVE(b);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            c.set_gk(g, 3, r, b[r]);
+            tmp[r] = fma(RC(A54), b[r], fma(RC(A53), c.gk(g, 2, r), fma(RC(A52), c.gk(g, 1, r),
+                                                                          fma(RC(A51), c.gk(g, 0, r), y[r]))));
+        }
+        bad |= c.template eval<false>(g, a, t + h, tmp, f);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            b[r] = fma(ih, fma(RC(C54), c.gk(g, 3, r), fma(RC(C53), c.gk(g, 2, r),
+                               fma(RC(C52), c.gk(g, 1, r), RC(C51) * c.gk(g, 0, r)))), f[r]);
+        G_SOLVE(b);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            c.set_gk(g, 4, r, b[r]);
+            tmp[r] += b[r];
+        }
+        bad |= c.template eval<false>(g, a, t + h, tmp, f);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            b[r] = fma(ih, fma(RC(C65), c.gk(g, 4, r), fma(RC(C64), c.gk(g, 3, r), fma(RC(C63), c.gk(g, 2, r),
+                               fma(RC(C62), c.gk(g, 1, r), RC(C61) * c.gk(g, 0, r))))), f[r]);
+        G_SOLVE(b);
+#undef G_SOLVE
+        double e = 0.0;
+        bool finite = true;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            ynew[r] = tmp[r] + b[r];
+            if (!g.owns(r)) continue;
+            finite = finite && (fabs(ynew[r]) <= DBL_MAX);
+            const double sk = fma(a.rtol, fmax(fabs(y[r]), fabs(ynew[r])), a.atol[r * G + g.gl]) + 1e-300;
+            e = fmax(e, fabs(b[r]) * fast_rcp<1>(sk));
+        }
+        const float ef = gmax_f<G>(g, (float)fmin(e, 3e38));
+        err = (double)ef;
+        if (!(ef <= 3e38f) || __any_sync(g.mask, !finite)) bad |= 1;
+        return bad;
+    }
+
+    // rosenbrock4_controller::try_step (same rule as GroupRos4::control)
+    __device__ __forceinline__ bool control(double err, double &hnext, double h) {
+        constexpr float isafe = 1.0f / 0.9f, fac1 = 5.0f, fac2 = 1.0f / 6.0f;
+        const float ef = (float)fmin(fmax(err, 1e-30), 1e30);
+        const float lg = __log2f(ef);
+        float fac = fmaxf(fac2, fminf(fac1, exp2f(0.25f * lg) * isafe));
+        if (err <= 1.0) {
+            if (!first) {
+                const float ratio = (float)(h_old * fast_rcp<1>(h));
+                float fp = ratio * exp2f(0.25f * (2.0f * lg - __log2f(err_old))) * isafe;
+                fp = fmaxf(fac2, fminf(fac1, fp));
+                fac = fmaxf(fac, fp);
+            }
+            double hn = h * (double)__frcp_rn(fac);
+            first = false;
+            h_old = h;
+            err_old = fmaxf(0.01f, ef);
+            if (last_rejected) hn = (h >= 0.0) ? fmin(hn, h) : fmax(hn, h);
+            last_rejected = false;
+            hnext = hn;
+            return true;
+        }
+        last_rejected = true;
+        hnext = h * (double)__frcp_rn(fac);
+        return false;
+    }
+
+    __device__ __forceinline__ void dense(const Coop<G> &c, const Grp<G> &g, double theta, const double *yold,
+                                          const double *ynew, double *out) {
+        const double s1 = 1.0 - theta;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const double q1 = c.gk(g, 0, r), q2 = c.gk(g, 1, r), q3 = c.gk(g, 2, r), q4 = c.gk(g, 3, r), q5 = c.gk(g, 4, r);
+            const double c3 = fma(RC(D25), q5, fma(RC(D24), q4, fma(RC(D23), q3, fma(RC(D22), q2, RC(D21) * q1))));
+            const double c4 = fma(RC(D35), q5, fma(RC(D34), q4, fma(RC(D33), q3, fma(RC(D32), q2, RC(D31) * q1))));
+            out[r] = yold[r] * s1 + theta * (ynew[r] + s1 * (c3 + theta * c4));
+        }
+    }
+};
+#undef RC
+
+// ----------------------------------------------------------------------------------------------
+// Persistent kernel.  MODE 0: predefined output points, MODE 1: every accepted step.  One iteration of the outer
+// loop = one Rosenbrock step attempt of every system of the block (lock-step), preceded - when some group just
+// loaded a system without a given first step - by the two evaluations of the starting-step heuristic.
+// ----------------------------------------------------------------------------------------------
+template <int G, int MODE>
+__global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros4_kernel(const KernelArgs a) {
+    typedef CoopLayout<G> L;
+    constexpr int R = L::R;
+    extern __shared__ double c_smem[];
+    const int lane = threadIdx.x & 31u;
+    Grp<G> g;
+    g.gl = lane % G;
+    g.lane0 = lane - g.gl;
+    g.mask = (G == 32) ? FULL_MASK : (((1u << (G & 31)) - 1u) << g.lane0);
+    Coop<G> c;
+    c.sysl = threadIdx.x / G;
+    c.evalno = 0;
+    g.prow = c_smem + L::oScr + (size_t)c.sysl * 2 * NY;
+    g.ys = g.prow + NY;
+    int *ist = reinterpret_cast<int *>(c_smem + L::oInt);
+    if (threadIdx.x < 2 * L::NSYS) ist[threadIdx.x] = 0;
+    for (int k = threadIdx.x; k < L::oScr - L::oP; k += kCoopBlock) c_smem[L::oP + k] = 0.0;  // finite garbage for idle slots
+    __syncthreads();
+
+    const int64_t ngroups = (int64_t)gridDim.x * L::NSYS;
+    int64_t s = (int64_t)blockIdx.x * L::NSYS + c.sysl - ngroups;  // static schedule cursor
+
+    CoopRos4<G> st;
+    st.begin();
+    double y[R], t = 0, h = 1.0, tend = 0, dir = 1, hmin = 0, hmax = INFINITY;
+    int64_t steps_left = 0;
+    int k_out = 0, restarts = 0, nfail = 0, nfev = 0, njev = 0;
+    Counters cnt = {0, 0, 0, 0};
+    bool active = false, exhausted = false, need_h = false;
+#pragma unroll
+    for (int r = 0; r < R; ++r) y[r] = 0.0;
+
+    for (;;) {
+        // ---- (B) + (E): termination test of the running system, retire ----------------------------------------
+        if (active) {
+            int status = -1;
+            if (nfail >= (1 << 20)) status = ST_RHS;
+            else if (nfail == -1) status = ST_STEP_TOO_SMALL;
+            else if (nfail == -2) status = ST_ROWS;
+            else if (t == tend) status = ST_OK;
+            else if (steps_left <= 0) {
+                if (restarts > 0) {  // autorestart (_cvode_wrapper.pyx:90): new step budget, re-initialised stepper
+                    restarts -= 1;
+                    steps_left = a.mxsteps;
+                    st.begin();
+                    need_h = true;
+                } else {
+                    status = ST_MXSTEPS;
+                }
+            }
+            if (status >= 0) {
+                if (MODE == 0 && status != ST_OK) {
+                    const double qnan = nan("");
+                    for (int k = k_out; k < a.nt; ++k)
+#pragma unroll
+                        for (int r = 0; r < R; ++r)
+                            if (g.owns(r)) {
+                                const int i = r * G + g.gl;
+                                if (a.yout_soa) a.yout[((int64_t)k * NY + i) * a.n + s] = qnan;
+                                else a.yout[(s * a.nt + k) * NY + i] = qnan;
+                            }
+                }
+                if (g.gl == 0) {
+                    a.status[s] = status;
+                    if (MODE == 0) a.nreached[s] = k_out;
+                    else a.nrows[s] = k_out;
+                    if (a.counters) {
+                        a.counters[C_NSTEPS * a.counters_ld + s] = cnt.nsteps;
+                        a.counters[C_NFEV * a.counters_ld + s] = nfev;
+                        a.counters[C_NJEV * a.counters_ld + s] = njev;
+                        a.counters[C_NLU * a.counters_ld + s] = cnt.nlu;
+                        a.counters[C_NSOLVE * a.counters_ld + s] = cnt.nsolve;
+                        a.counters[C_NREJECT * a.counters_ld + s] = cnt.nreject;
+                    }
+                }
+                active = false;
+            }
+        }
+        // ---- (A) fetch a new system for an idle group ------------------------------------------------------------
+        if (!active && !exhausted) {
+            if (a.work_counter != nullptr) {
+                unsigned long long nxt = 0;
+                if (g.gl == 0) nxt = atomicAdd(a.work_counter, 1ull);
+                s = (int64_t)__shfl_sync(g.mask, nxt, g.lane0);
+            } else {
+                s += ngroups;
+            }
+            if (s >= a.n) {
+                exhausted = true;
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) y[r] = g.owns(r) ? a.y0[s * NY + r * G + g.gl] : 0.0;
+                for (int i = g.gl; i < NP_USED; i += G) {
+                    double v;
+                    if (i >= ODESYS_NPARAMS && a.iv_from_y0) v = a.y0[s * NY + (i - ODESYS_NPARAMS)];
+                    else v = a.params[s * a.params_ld + i];
+                    c_smem[L::oP + i * L::NSYS + c.sysl] = v;
+                }
+                if (g.gl == 0) ist[L::NSYS + c.sysl] = 1;  // the evaluator runs OdeSys::setup() for this slot
+                cnt = {0, 0, 0, 0};
+                nfev = 0;
+                njev = 0;
+                restarts = a.autorestart;
+                nfail = 0;
+                if (MODE == 0) {
+                    const double *xo = a.xout + s * a.xout_stride;
+                    t = xo[0];
+                    tend = xo[a.nt - 1];
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+                        if (g.owns(r)) {
+                            const int i = r * G + g.gl;
+                            if (a.yout_soa) a.yout[(int64_t)i * a.n + s] = y[r];
+                            else a.yout[(s * a.nt) * NY + i] = y[r];
+                        }
+                } else {
+                    t = a.x0[s];
+                    tend = a.xend[s];
+                    double *row = a.xyout + (s * a.max_rows) * (1 + NY);
+                    if (g.gl == 0) row[0] = t;
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+                        if (g.owns(r)) row[1 + r * G + g.gl] = y[r];
+                }
+                k_out = 1;
+                dir = (tend >= t) ? 1.0 : -1.0;
+                hmin = a.dx_min ? a.dx_min[s] : 0.0;
+                hmax = a.dx_max ? a.dx_max[s] : INFINITY;
+                if (!(hmax > 0.0)) hmax = INFINITY;
+                steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
+                st.begin();
+                h = a.dx0 ? a.dx0[s] : 0.0;
+                need_h = (h == 0.0);
+                if (!need_h) h = fabs(h) * dir;
+                active = true;
+                bool fin = true;
+#pragma unroll
+                for (int r = 0; r < R; ++r) fin = fin && (fabs(y[r]) <= DBL_MAX);
+                if (__any_sync(g.mask, !fin)) nfail = 1 << 20;
+                if (tend == t) {
+                    need_h = false;
+                    if (MODE == 0) {  // zero-length span: every requested point equals the start
+                        for (; k_out < a.nt; ++k_out) {
+#pragma unroll
+                            for (int r = 0; r < R; ++r)
+                                if (g.owns(r)) {
+                                    const int i = r * G + g.gl;
+                                    if (a.yout_soa) a.yout[((int64_t)k_out * NY + i) * a.n + s] = y[r];
+                                    else a.yout[(s * a.nt + k_out) * NY + i] = y[r];
+                                }
+                        }
+                    }
+                }
+            }
+        }
+        if (__syncthreads_and(!active)) break;
+        // a system that is about to retire (finished span, failure) idles through this iteration
+        const bool live = active && t != tend && nfail >= 0 && nfail < (1 << 20);
+
+        // ---- starting step size where none was given: two evaluation slots, taken by the whole block ----------------
+        if (__syncthreads_or(live && need_h)) {
+            const double hs = st.auto_step(c, g, a, t, y, live ? tend - t : 0.0, nfev);
+            if (live && need_h) h = hs;
+            else if (active) nfev -= 2;  // slots this system did not use
+            need_h = false;
+        }
+
+        // ---- (C) one trial step of every system of the block -----------------------------------------------------------
+        double hh = live ? h : 1.0;
+        if (fabs(hh) > hmax) hh = dir * hmax;
+        if (fabs(hh) < hmin) hh = dir * hmin;
+        const double rem = tend - t;
+        const bool lands = live && fabs(hh) >= fabs(rem) * (1.0 - 1e-13);
+        double tnew = t + hh;
+        if (lands) {
+            hh = rem;
+            tnew = tend;
+        }
+        double ynew[R], err = 0.0, hnext = hh;
+        Counters scratch = cnt;
+        const int bad = st.attempt(c, g, a, t, y, hh, ynew, err, live ? cnt : scratch);
+        if (!live) continue;
+        nfev += 6;
+        njev += 1;
+        cnt.nsteps += 1;
+        steps_left -= 1;
+        bool ok;
+        if (bad) {
+            ok = false;
+            hnext = 0.25 * hh;
+            nfail += 1;
+            if (nfail >= 12) nfail = 1 << 20;
+            double ignored;
+            st.control(2.0, ignored, hh);
+        } else {
+            ok = st.control(err, hnext, hh);
+            if (ok) nfail = 0;
+        }
+        if (!ok) {
+            cnt.nreject += 1;
+            if (fabs(hnext) <= 16.0 * DBL_EPSILON * fabs(t) || fabs(hnext) == 0.0 || (hmin > 0.0 && fabs(hh) <= hmin))
+                nfail = -1;  // ST_STEP_TOO_SMALL at the top of the next iteration
+            h = hnext;
+        } else {
+            // ---- (D) accepted: emit outputs -----------------------------------------------------------------------
+            if (MODE == 0) {
+                const double *xo = a.xout + s * a.xout_stride;
+                while (k_out < a.nt) {
+                    const double xk = xo[k_out];
+                    if ((xk - tnew) * dir > 0.0) break;
+                    double yo[R];
+                    if (xk == tnew) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) yo[r] = ynew[r];
+                    } else {
+                        st.dense(c, g, (xk - t) / hh, y, ynew, yo);
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+                        if (g.owns(r)) {
+                            const int i = r * G + g.gl;
+                            if (a.yout_soa) a.yout[((int64_t)k_out * NY + i) * a.n + s] = yo[r];
+                            else a.yout[(s * a.nt + k_out) * NY + i] = yo[r];
+                        }
+                    k_out += 1;
+                    steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
+                }
+            } else {
+                if (k_out >= a.max_rows) {
+                    nfail = -2;  // ST_ROWS
+                } else {
+                    double *row = a.xyout + (s * a.max_rows + k_out) * (1 + NY);
+                    if (g.gl == 0) row[0] = tnew;
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+                        if (g.owns(r)) row[1 + r * G + g.gl] = ynew[r];
+                    k_out += 1;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) y[r] = ynew[r];
+            t = tnew;
+            h = hnext;
+        }
+    }
+}
+
+#endif  // ODESYS_HAS_JAC
+
+}  // namespace pyodesys_cuda

@@ -24,6 +24,11 @@
 #if ODESYS_GROUP_KERNEL
 #include "group_integrators.cuh"
 #endif
+// block-cooperative kernel: lane groups for the linear algebra, one system per lane for f and J (default for ny > 8)
+#define ODESYS_COOP_KERNEL (ODESYS_GROUP_KERNEL && ODESYS_NY >= 9)
+#if ODESYS_COOP_KERNEL
+#include "coop_integrators.cuh"
+#endif
 #include "pyodesys_cuda.h"
 
 #include <algorithm>
@@ -163,6 +168,29 @@ template <int MODE> int launch_group(DevCtx &c, const KernelArgs &a, cudaStream_
 }
 #endif
 
+#if ODESYS_COOP_KERNEL
+constexpr int kCoopG = PYODESYS_COOP_G;
+template <int MODE> int launch_coop(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
+    auto kern = coop_ros4_kernel<kCoopG, MODE>;
+    typedef CoopLayout<kCoopG> L;
+    const size_t smem = (size_t)L::kDoubles * sizeof(double);
+    if (smem > 227 * 1024) return fail("ny = %d needs %zu bytes of shared memory per block in the cooperative kernel; use kernel='group'", NY, smem);
+    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kCoopBlock, smem));
+    if (occ < 1) occ = 1;
+    if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
+    int64_t grid = (int64_t)c.sm_count * occ;
+    const int64_t need = (a.n + L::NSYS - 1) / L::NSYS;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kCoopBlock, smem, stream>>>(a);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+#endif
+
 #if ODESYS_SMEM_KERNEL
 // one system per thread, W / vectors / parameters in shared memory, rolled loops (one warp per block)
 template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
@@ -192,9 +220,18 @@ template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t
 // lane-group kernel above.
 int pick_kernel(int method, const pyodesys_cuda_options *opt) {
     const int want = opt ? opt->kernel : 0;
-    if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3) ? -1 : 1;
+    if (want == 1 || method != PYODESYS_CUDA_ROSENBROCK4) return (want == 2 || want == 3 || want == 4) ? -1 : 1;
 #if ODESYS_SMEM_KERNEL
     if (want == 3) return 3;
+#endif
+#if ODESYS_COOP_KERNEL
+    {
+        // what the cooperative kernel does not carry stays with the lane-group kernel
+        const bool extras = opt && ((ODESYS_NROOTS > 0 && opt->max_roots > 0) || opt->max_invariant_violation != 0.0 ||
+                                    (ODESYS_HAS_DX_MAX && opt->get_dx_max_factor > 0.0));
+        if (want == 4) return (extras || ODESYS_HAS_FIRST_STEP) ? -1 : 4;
+        if (want == 0 && NY > 8 && !extras && !ODESYS_HAS_FIRST_STEP) return 4;
+    }
 #endif
 #if ODESYS_GROUP_KERNEL
     if (want == 2) return 2;
@@ -208,9 +245,14 @@ template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cud
     const int family = pick_kernel(method, opt);
     if (family < 0)
         return fail("kernel=%d is not available for this system/method (lane-group kernel: rosenbrock4, Jacobian, ny >= 6; "
-                    "shared-memory thread kernel: rosenbrock4, Jacobian, ny >= 9)", opt ? opt->kernel : 0);
+                    "shared-memory thread kernel and block-cooperative kernel: rosenbrock4, Jacobian, ny >= 9; the "
+                    "cooperative kernel carries no event functions / invariant guard / get_dx0 / get_dx_max)",
+                    opt ? opt->kernel : 0);
 #if ODESYS_GROUP_KERNEL
     if (family == 2) return launch_group<MODE>(c, a, stream, bps);
+#endif
+#if ODESYS_COOP_KERNEL
+    if (family == 4) return launch_coop<MODE>(c, a, stream, bps);
 #endif
 #if ODESYS_SMEM_KERNEL
     if (family == 3) return launch_smem<MODE>(c, a, stream, bps);
@@ -494,7 +536,11 @@ int64_t pyodesys_cuda_query(const char *key) {
         {"np_used", NP_USED}, {"npcse", ODESYS_NPCSE}, {"has_jac", ODESYS_HAS_JAC}, {"autonomous", ODESYS_AUTONOMOUS},
         {"nroots", ODESYS_NROOTS}, {"nnz", ODESYS_NNZ}, {"has_jtimes", ODESYS_HAS_JTIMES}, {"ninvar", ODESYS_NINVAR}, {"flops_rhs", ODESYS_FLOPS_RHS}, {"flops_jac", ODESYS_FLOPS_JAC},
         {"flops_pcse", ODESYS_FLOPS_PCSE}, {"jac_nnz", ODESYS_JAC_NNZ}, {"block_size", kBlock},
-        {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL},
+        {"ncounters", NCOUNT}, {"has_group_kernel", ODESYS_GROUP_KERNEL}, {"has_coop_kernel", ODESYS_COOP_KERNEL},
+#if ODESYS_COOP_KERNEL
+        {"coop_group_size", kCoopG}, {"coop_systems_per_block", CoopLayout<kCoopG>::NSYS},
+        {"coop_smem_bytes", (int64_t)CoopLayout<kCoopG>::kDoubles * 8},
+#endif
         {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF},
 #if ODESYS_SMEM_KERNEL
         {"smem_doubles_per_thread", kSmemDoublesPerThread},

@@ -85,7 +85,7 @@ def cache_dir():
 
 def _csrc_digest():
     h = hashlib.sha256()
-    for fn in ('integrators.cuh', 'bdf_integrator.cuh', 'group_integrators.cuh', 'smem_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
+    for fn in ('integrators.cuh', 'bdf_integrator.cuh', 'group_integrators.cuh', 'coop_integrators.cuh', 'smem_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
         path = os.path.join(_csrc, fn)
         if os.path.exists(path):
             with open(path, 'rb') as fh:
@@ -296,7 +296,7 @@ class CudaModule:
         return Options(float(get_dx_max_factor or 0.0), float(max_invariant_violation or 0.0),
                        int(bool(error_outside_bounds)), int(bool(xout_shared)), int(sched), 0,
                        int(blocks_per_sm), 0, None, int(bool(iv_from_y0)), 0,
-                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3}.get(kernel, kernel)), 0, 0, linsol,
+                       int({'auto': 0, 'thread': 1, 'group': 2, 'thread_smem': 3, 'coop': 4}.get(kernel, kernel)), 0, 0, linsol,
                        None, None, None, 0, int(ctx_lane), 0)
 
     def _root_buffers(self, opts, n, kw_roots):

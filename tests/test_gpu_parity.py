@@ -398,7 +398,7 @@ def test_edge_cases(cuda_device):
 
 
 # ---- larger systems: the three Rosenbrock kernel families ------------------------------------------------------------
-@pytest.mark.parametrize('kernel', ['thread', 'group', 'thread_smem'])
+@pytest.mark.parametrize('kernel', ['thread', 'group', 'thread_smem', 'coop'])
 def test_radiolysis_kernel_families_vs_oracle(cuda_device, kernel):
     """ C4 (radiolysis network of examples/_chem_kinet.py:57-85, ny=14, 54 rate parameters): register, lane-group and
     shared-memory kernels against the CPU oracle on the same seeded batch, dense output included """
