@@ -161,6 +161,132 @@ template <int G> struct Coop {
     }
 };
 
+// ---- in-place inverse for a block that steps in lock-step --------------------------------------------------------
+// Same result layout as g_invert (group_integrators.cuh): after the elimination a[r][m] = (W^-1)[ord[r]][p_m].  What
+// differs is how a pivot step is organised, because in the lane-group version the bookkeeping of a step (pivot search
+// with per-group membermasks - the hardware serialises REDUX / SHFL over the distinct masks of a warp -, the owner
+// copying its row to shared memory element by element under a predicate) was 3/4 of the executed instructions and the
+// top stall site (profiles/r2c_coop14_by_line.txt):
+//   * every lane of the warp is converged here, so all reductions are xor-shuffles with the full mask (offsets < G
+//     stay inside a group) - no serialisation;
+//   * THRESHOLD pivoting: the natural row k is the pivot whenever it is unused and |a_kk| >= max_i |a_ik| / 8 over
+//     the unused rows (magnitudes compared on the high words).  Its owner (lane k % G, slot k / G) is known at
+//     compile time: the row is broadcast with 2 NY shuffles from a fixed lane, nothing is selected, nothing staged.
+//     Relaxed pivoting with threshold 1/8 bounds the multipliers by 8 (strict partial pivoting: by 1) - the standard
+//     trade of sparse direct solvers; W = I/(gamma h) - J of a kinetics network takes this path almost always;
+//   * otherwise (warp vote) the step falls back to strict partial pivoting with the pivot row published through
+//     shared memory by whichever lane owns it.
+template <int G> __device__ __forceinline__ int gmax_i_full(int v) {
+#pragma unroll
+    for (int off = G / 2; off > 0; off /= 2) v = max(v, __shfl_xor_sync(FULL_MASK, v, off));
+    return v;
+}
+#ifndef PYODESYS_COOP_PIVOT_SHIFT
+#define PYODESYS_COOP_PIVOT_SHIFT 3  /* natural pivot accepted down to 2^-3 of the column maximum */
+#endif
+template <int G> __device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord) {
+    constexpr int R = Grp<G>::R;
+    static_assert(R <= 4 && G <= 32, "pivot key packs the slot in 2 bits, the lane in 5");
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < R; ++r) ord[r] = g.owns(r) ? NY : -1;
+#pragma unroll
+    for (int k = 0; k < NY; ++k) {
+        const int kl = k % G, ks = k / G;  // owner lane (inside the group) and slot of the natural row
+        int best = -1, bslot = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int hi = (ord[r] == NY) ? (__double2hiint(a[r][k]) & 0x7fffffff) : -1;
+            if (hi > best) {
+                best = hi;
+                bslot = r;
+            }
+        }
+        // key: magnitude class (top 24 of the 31 bits) | slot | inverted lane: the maximum is also the first lane on ties
+        const int key = (best < 0) ? -1 : ((best & ~127) | (bslot << 5) | (G - 1 - g.gl));
+        const int kmax = gmax_i_full<G>(key);
+        const int mx = (kmax < 0) ? -1 : (kmax & ~127);
+        ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
+        const int nat_here = (ord[ks] == NY) ? (__double2hiint(a[ks][k]) & 0x7fffffff) : -1;
+        const int nat = __shfl_sync(FULL_MASK, nat_here, g.lane0 + kl);
+        const bool natural = nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx;
+        if (__all_sync(FULL_MASK, natural)) {
+            double prow[NY];
+#pragma unroll
+            for (int j = 0; j < NY; ++j) prow[j] = __shfl_sync(FULL_MASK, a[ks][j], g.lane0 + kl);
+            const bool mine = (g.gl == kl);
+            if (mine) ord[ks] = k;
+            const double d = fast_rcp<2>(prow[k]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool piv = (r == ks) && mine;
+                const double m = piv ? d : -a[r][k] * d;
+#pragma unroll
+                for (int j = 0; j < NY; ++j) {
+                    if (j == k) continue;
+                    const double base = (r == ks) ? (mine ? 0.0 : a[r][j]) : a[r][j];
+                    a[r][j] = fma(m, prow[j], base);
+                }
+                a[r][k] = m;
+            }
+        } else {
+            const int pl = G - 1 - (kmax & 31), ps = (kmax >> 5) & 3;
+            const bool mine = (g.gl == pl);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (mine && r == ps) {
+                    ord[r] = k;
+#pragma unroll
+                    for (int j = 0; j < NY; ++j) {
+                        g.prow[j] = a[r][j];
+                        a[r][j] = 0.0;
+                    }
+                }
+            }
+            __syncwarp();
+            const double d = fast_rcp<2>(g.prow[k]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const double m = (ord[r] != k) ? -a[r][k] * d : d;
+#pragma unroll
+                for (int j = 0; j < NY; ++j) {
+                    if (j == k) continue;
+                    a[r][j] = fma(m, g.prow[j], a[r][j]);
+                }
+                a[r][k] = m;
+            }
+            __syncwarp();
+        }
+    }
+    return ok;
+}
+
+// x = W^-1 b (see g_apply); full-warp synchronisation
+template <int G> __device__ __forceinline__ void c_apply(const Grp<G> &g, const double (*a)[NY], const int *ord,
+                                                         double *b) {
+    constexpr int R = Grp<G>::R;
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (g.owns(r)) g.prow[ord[r]] = b[r];
+    __syncwarp();
+    double acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+#pragma unroll
+    for (int m = 0; m < NY; ++m) {
+        const double bm = g.prow[m];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = fma(a[r][m], bm, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (g.owns(r)) g.ys[ord[r]] = acc[r];
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? g.ys[r * G + g.gl] : 0.0;
+}
+
 #define RC(name) kRos4[ros4c::name]
 template <int G> struct CoopRos4 {
     typedef CoopLayout<G> L;
@@ -234,8 +360,8 @@ template <int G> struct CoopRos4 {
             }
             dfdt[r] = (!ODESYS_AUTONOMOUS && g.owns(r)) ? c_smem[L::oDF + i * L::NSYSP + c.sysl] : 0.0;
         }
-        if (!g_invert<G>(g, W, ord)) bad |= 1;
-#define G_SOLVE(vec) g_apply<G>(g, W, ord, vec)
+        if (!c_invert<G>(g, W, ord)) bad |= 1;
+#define G_SOLVE(vec) c_apply<G>(g, W, ord, vec)
         cnt.nlu += 1;
         cnt.nsolve += 6;
 #pragma unroll

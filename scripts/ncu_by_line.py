@@ -1,0 +1,56 @@
+#!/usr/bin/env python
+"""Attribute the executed warp instructions of one profiled kernel to source lines (no GPU needed).
+
+    python scripts/ncu_by_line.py <report.ncu-rep> <lib.so> <kernel-mangled-substring> [top]
+
+ncu's ``--page source --print-source sass`` lists every SASS instruction of the kernel (callees included) with its
+executed count; ``nvdisasm -g`` of the cubin inside <lib.so> gives the (innermost) file:line of the same instructions
+in the same order.  Printed: executed warp instructions per file, per line (top N) and per opcode class.
+"""
+import collections, csv, io, os, re, subprocess, sys, tempfile
+
+rep, so, pat = sys.argv[1:4]
+top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'sass'], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(out)))
+hdr = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
+H = rows[hdr]
+ci, cs, ct = H.index('Instructions Executed'), H.index('Source'), H.index('Thread Instructions Executed')
+cw = H.index('# Samples') if '# Samples' in H else None
+sass = [(r[cs].strip(), int(r[ci]), int(r[ct]), int(r[cw]) if cw is not None else 0) for r in rows[hdr + 1:] if len(r) == len(H)]
+tmp = tempfile.mkdtemp()
+subprocess.run(['cuobjdump', '-xelf', 'all', os.path.abspath(so)], cwd=tmp, capture_output=True)
+cub = [f for f in os.listdir(tmp) if f.endswith('.cubin')][0]
+dis = subprocess.run(['nvdisasm', '-g', '-c', os.path.join(tmp, cub)], capture_output=True, text=True).stdout.splitlines()
+start = next(i for i, l in enumerate(dis) if l.startswith('.text.') and pat in l)
+lines, cur = [], ('?', 0)
+for l in dis[start + 1:]:
+    if l.startswith('//-----') or (l.startswith('.text.') and pat not in l):
+        break
+    m = re.search(r'//## File "([^"]+)", line (\d+)', l)
+    if m:
+        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+        continue
+    m = re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);', l)
+    if m:
+        lines.append((cur, m.group(2).strip()))
+if len(lines) != len(sass):
+    print('warning: %d disassembled vs %d profiled instructions' % (len(lines), len(sass)))
+n = min(len(lines), len(sass))
+tot = sum(s[1] for s in sass[:n])
+byfile, byline, byop, samples = (collections.Counter() for _ in range(4))
+for (loc, txt), (src, cnt, thr, smp) in zip(lines[:n], sass[:n]):
+    byfile[loc[0]] += cnt
+    byline[loc] += cnt
+    samples[loc] += smp
+    op = txt.split()[1] if txt.startswith('@') else txt.split()[0]
+    byop[op.split('.')[0]] += cnt
+print('total executed warp instructions: %.4g' % tot)
+for f, c in byfile.most_common():
+    print('%6.2f %%  %s' % (100.0*c/tot, f))
+print('--- lines')
+for (f, ln), c in byline.most_common(top):
+    print('%6.2f %%  samples %6d  %s:%d' % (100.0*c/tot, samples[(f, ln)], f, ln))
+print('--- opcodes')
+for op, c in byop.most_common(25):
+    print('%6.2f %%  %s' % (100.0*c/tot, op))
