@@ -32,11 +32,18 @@ namespace pyodesys_cuda {
 #define PYODESYS_COOP_FITS(g) ((((NY + (g) - 1) / (g)) * NY) <= 56)
 #define PYODESYS_COOP_G (PYODESYS_COOP_FITS(8) ? 8 : PYODESYS_COOP_FITS(16) ? 16 : 32)
 #endif
+// Threads per block.  The systems of a block step in lock-step and every evaluation is a serial phase of ONE warp
+// (the others wait at the barrier), so what keeps an SM busy is the number of independent blocks on it, not the size
+// of a block: 128 threads = 3 blocks per SM at 168 registers (4 at 128 registers spill: local memory shares the
+// load/store data path that bounds the kernel).
+#ifndef PYODESYS_COOP_BLOCK
+#define PYODESYS_COOP_BLOCK 128
+#endif
 #ifndef PYODESYS_COOP_MIN_BLOCKS
-#define PYODESYS_COOP_MIN_BLOCKS (ODESYS_NY <= 16 ? 2 : 1)
+#define PYODESYS_COOP_MIN_BLOCKS ((ODESYS_NY <= 16 ? 384 : 256) / PYODESYS_COOP_BLOCK)
 #endif
 
-constexpr int kCoopBlock = 256;
+constexpr int kCoopBlock = PYODESYS_COOP_BLOCK;
 constexpr int kCoopWarps = kCoopBlock / 32;
 
 template <int S> struct SView {  // array-like view with a compile-time stride: v[i] = p[i * S]
@@ -61,9 +68,9 @@ template <int G> struct CoopLayout {
     static constexpr int oX = oF + NY * NSYSP;                       // abscissa [system]
     static constexpr int oDF = oX + NSYS;                            // dfdt [i][system] (non-autonomous systems)
     static constexpr int oJ = oDF + (ODESYS_AUTONOMOUS ? 0 : NY * NSYSP);  // Jacobian [(i * NYP + j)][system]
-    static constexpr int oScr = oJ + NY * NYP * NSYSP;               // per system: prow[NY], ys[NY] (g_invert / g_apply)
-    static constexpr int oG = oScr + 2 * NY * NSYS;                  // stage increments g1..g5 [k][system][i]
-    static constexpr int oInt = oG + 5 * NY * NSYS;                  // ints: status[NSYS], fresh[NSYS]
+    static constexpr int NYE = NY + (NY & 1);                        // vectors that are moved 16 bytes at a time
+    static constexpr int oScr = (oJ + NY * NYP * NSYSP + 1) & ~1;    // per system: two staging vectors [NYE] (16-byte aligned)
+    static constexpr int oInt = oScr + 2 * NYE * NSYS;               // ints: status[NSYS], fresh[NSYS]
     static constexpr int kDoubles = oInt + NSYS;
     typedef odesys_anyode::OdeSysT<SView<NSYS>> ESys;
 };
@@ -80,8 +87,7 @@ template <int G> struct CoopSinkJ {
 // f (and J) for one system of the block, state in registers, parameters / results in shared memory.  One out-of-line
 // copy per variant (a Rosenbrock step has seven evaluation sites); only the evaluator lanes make the call, so the
 // other warps pay neither for its code nor for its register save area.
-template <int G, bool JAC>
-__device__ __noinline__ void coop_eval_one(int e, int error_outside_bounds) {
+template <int G> __device__ __noinline__ void coop_eval_rhs(int e, int error_outside_bounds) {
     typedef CoopLayout<G> L;
     extern __shared__ double c_smem[];
     double *sm = c_smem;
@@ -111,29 +117,69 @@ __device__ __noinline__ void coop_eval_one(int e, int error_outside_bounds) {
     AnyODE::ignore(error_outside_bounds);
 #pragma unroll
     for (int i = 0; i < NY; ++i) sm[L::oF + i * L::NSYSP + e] = f[i];
-    if (JAC) {
-        CoopSinkJ<G> sink{sm + L::oJ + e, sm + L::oDF + e};
-        st |= es.dense_jac_sink(x, y, sink);
-    }
     ist[e] = st;
+}
+// the Jacobian at the state that coop_eval_rhs just evaluated (one copy of each generated body in the kernel: the
+// loop has to fit the instruction cache)
+template <int G> __device__ __noinline__ void coop_eval_jac(int e) {
+    typedef CoopLayout<G> L;
+    extern __shared__ double c_smem[];
+    double *sm = c_smem;
+    typename L::ESys es;
+    es.m_p = SView<L::NSYS>{sm + L::oP + e};
+    es.m_p_cse = SView<L::NSYS>{sm + L::oPC + e};
+    es.nfev = 0;
+    es.njev = 0;
+    double y[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) y[i] = sm[L::oY + i * L::NSYSP + e];
+    CoopSinkJ<G> sink{sm + L::oJ + e, sm + L::oDF + e};
+    const int st = es.dense_jac_sink(sm[L::oX + e], y, sink);
+    int *ist = reinterpret_cast<int *>(sm + L::oInt);
+    ist[e] |= st;
 }
 
 // executed by every thread of the block between two block barriers; the evaluator role rotates over the warps
-template <int G, bool JAC> __device__ __forceinline__ void coop_evaluate(int evalno, int error_outside_bounds) {
+template <int G, bool JAC> __device__ __forceinline__ long long coop_evaluate(int evalno, int error_outside_bounds) {
     typedef CoopLayout<G> L;
     __syncthreads();  // staged states (Y, X) are complete
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rel = (warp - (evalno % kCoopWarps) + kCoopWarps) % kCoopWarps;
     const int e = rel * 32 + lane;
-    if (rel < L::NE && e < L::NSYS) coop_eval_one<G, JAC>(e, error_outside_bounds);
+    long long body = 0;
+#ifdef PYODESYS_COOP_PROFILE
+    const long long t_body = clock64();
+#endif
+    if (rel < L::NE && e < L::NSYS) {
+        coop_eval_rhs<G>(e, error_outside_bounds);
+        if (JAC) coop_eval_jac<G>(e);
+#ifdef PYODESYS_COOP_PROFILE
+        body = clock64() - t_body;
+#endif
+    }
     __syncthreads();  // results (F, J, status) are complete
+    return body;
 }
+
+// -DPYODESYS_COOP_PROFILE: per-phase SM cycles (clock64, summed over warps) are added to the eight 64-bit words at
+// KernelArgs::root_out (the cooperative kernel locates no event functions): 0 evaluations incl. both barriers,
+// 1 evaluator body, 2 inverse, 3 solves, 4 everything, 5 warp count
+#ifdef PYODESYS_COOP_PROFILE
+#define COOP_T0(var) const long long var = clock64()
+#define COOP_ACC(slot, var) c.prof[slot] += clock64() - var
+#else
+#define COOP_T0(var)
+#define COOP_ACC(slot, var)
+#endif
 
 template <int G> struct Coop {
     typedef CoopLayout<G> L;
     static constexpr int R = L::R;
     int sysl;     // local index of this lane's system inside the block
     int evalno;   // evaluations so far (block uniform): rotates the evaluator role over the warps
+#ifdef PYODESYS_COOP_PROFILE
+    long long prof[10];
+#endif
 
     // stage the distributed vector yv, evaluate, bring back the rows this lane owns; returns the callback status
     template <bool JAC>
@@ -143,21 +189,19 @@ template <int G> struct Coop {
         for (int r = 0; r < R; ++r)
             if (g.owns(r)) c_smem[L::oY + (r * G + g.gl) * L::NSYSP + sysl] = yv[r];
         if (g.gl == 0) c_smem[L::oX + sysl] = x;
-        coop_evaluate<G, JAC>(evalno, a.error_outside_bounds);
+#ifdef PYODESYS_COOP_PROFILE
+        const long long t_ev = clock64();
+#endif
+        const long long body = coop_evaluate<G, JAC>(evalno, a.error_outside_bounds);
+        AnyODE::ignore(body);
+#ifdef PYODESYS_COOP_PROFILE
+        prof[0] += clock64() - t_ev;
+        prof[1] += body;
+#endif
         evalno += 1;
 #pragma unroll
         for (int r = 0; r < R; ++r) f[r] = g.owns(r) ? c_smem[L::oF + (r * G + g.gl) * L::NSYSP + sysl] : 0.0;
         return reinterpret_cast<const int *>(c_smem + L::oInt)[sysl];
-    }
-    // stage increment g_k (k = 0..4) of this lane's rows lives in shared memory (five vectors of R doubles per lane
-    // are the difference between 128 registers with spills and without)
-    __device__ __forceinline__ double gk(const Grp<G> &g, int k, int r) const {
-        extern __shared__ double c_smem[];
-        return g.owns(r) ? c_smem[L::oG + (k * L::NSYS + sysl) * NY + r * G + g.gl] : 0.0;
-    }
-    __device__ __forceinline__ void set_gk(const Grp<G> &g, int k, int r, double v) const {
-        extern __shared__ double c_smem[];
-        if (g.owns(r)) c_smem[L::oG + (k * L::NSYS + sysl) * NY + r * G + g.gl] = v;
     }
 };
 
@@ -170,12 +214,12 @@ template <int G> struct Coop {
 //   * every lane of the warp is converged here, so all reductions are xor-shuffles with the full mask (offsets < G
 //     stay inside a group) - no serialisation;
 //   * THRESHOLD pivoting: the natural row k is the pivot whenever it is unused and |a_kk| >= max_i |a_ik| / 8 over
-//     the unused rows (magnitudes compared on the high words).  Its owner (lane k % G, slot k / G) is known at
-//     compile time: the row is broadcast with 2 NY shuffles from a fixed lane, nothing is selected, nothing staged.
-//     Relaxed pivoting with threshold 1/8 bounds the multipliers by 8 (strict partial pivoting: by 1) - the standard
-//     trade of sparse direct solvers; W = I/(gamma h) - J of a kinetics network takes this path almost always;
-//   * otherwise (warp vote) the step falls back to strict partial pivoting with the pivot row published through
-//     shared memory by whichever lane owns it.
+//     the unused rows (magnitudes compared on the high words), otherwise the row with the largest |a_ik|.  Relaxed
+//     pivoting with threshold 1/8 bounds the multipliers by 8 (strict partial pivoting: by 1) - the standard trade of
+//     sparse direct solvers.  W = I/(gamma h) - J of a kinetics network keeps its natural order almost always, and
+//     then W^-1 comes out in variable order: the solves skip one of their two permutations through shared memory;
+//   * the pivot row is published by its owner with 16-byte stores and read back by every lane with 16-byte
+//     broadcast loads (a 64-bit shuffle costs two wavefront slots per double on the same data path).
 template <int G> __device__ __forceinline__ int gmax_i_full(int v) {
 #pragma unroll
     for (int off = G / 2; off > 0; off /= 2) v = max(v, __shfl_xor_sync(FULL_MASK, v, off));
@@ -184,113 +228,140 @@ template <int G> __device__ __forceinline__ int gmax_i_full(int v) {
 #ifndef PYODESYS_COOP_PIVOT_SHIFT
 #define PYODESYS_COOP_PIVOT_SHIFT 3  /* natural pivot accepted down to 2^-3 of the column maximum */
 #endif
-template <int G> __device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord) {
+// 16-byte shared-memory moves of a vector of NY doubles (buffer length NYE = NY rounded up to even, 16-byte aligned):
+// the shared-memory / shuffle data path is what bounds this kernel (56 % of its peak in profiles/r2e_coop14.txt, the
+// FP64 pipe 17 %), and a 16-byte access moves two doubles per wavefront slot
+template <int N> __device__ __forceinline__ void lds_vec(const double *buf, double *v) {
+    const double2 *b2 = reinterpret_cast<const double2 *>(buf);
+#pragma unroll
+    for (int j = 0; j < N / 2; ++j) {
+        const double2 q = b2[j];
+        v[2 * j] = q.x;
+        v[2 * j + 1] = q.y;
+    }
+    if (N & 1) v[N - 1] = buf[N - 1];
+}
+template <int N> __device__ __forceinline__ void sts_vec(double *buf, const double *v) {
+    double2 *b2 = reinterpret_cast<double2 *>(buf);
+#pragma unroll
+    for (int j = 0; j < N / 2; ++j) b2[j] = make_double2(v[2 * j], v[2 * j + 1]);
+    if (N & 1) buf[N - 1] = v[N - 1];
+}
+
+// The pivot loop is ROLLED: the kernel is bound by instruction fetch, not by any execution pipe (ncu: the GPC-level
+// instruction cache at 78 % of its peak request rate, 13 % of the SM instruction-cache requests missing, while FP64
+// sat at 17 % and the shared-memory data path at 56 %; run time did not move with occupancy, block size or spills).
+// Fully unrolled, the NY pivot steps were 54 KB of the 94 KB loop body.  Register arrays only allow literal indices,
+// so every step works on PHYSICAL column 0 and shifts the columns left by one while it updates them
+//     a[r][j-1] <- a[r][j] + m_r * prow[j]   (j = 1..NY-1),      a[r][NY-1] <- m_r  (the new column of the inverse)
+// - after NY steps every logical column is back at its own position.  The pivot row (lane pl, slot ps; natural or
+// searched) is picked with selects, so one code path serves both cases.
+template <int G> __device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord, bool &identity) {
     constexpr int R = Grp<G>::R;
     static_assert(R <= 4 && G <= 32, "pivot key packs the slot in 2 bits, the lane in 5");
     bool ok = true;
+    identity = true;  // every pivot so far was the natural one: W^-1 comes out in variable order
 #pragma unroll
     for (int r = 0; r < R; ++r) ord[r] = g.owns(r) ? NY : -1;
-#pragma unroll
+    int kl = 0, ks = 0;  // owner lane (inside the group) and slot of the natural row k
+#pragma unroll 1
     for (int k = 0; k < NY; ++k) {
-        const int kl = k % G, ks = k / G;  // owner lane (inside the group) and slot of the natural row
-        int best = -1, bslot = 0;
+        double *buf = (k & 1) ? g.ys : g.prow;  // two staging vectors in turn: one warp synchronisation per step
+        int best = -1, bslot = 0, nat_here = -1;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int hi = (ord[r] == NY) ? (__double2hiint(a[r][k]) & 0x7fffffff) : -1;
+            const int hi = (ord[r] == NY) ? (__double2hiint(a[r][0]) & 0x7fffffff) : -1;
             if (hi > best) {
                 best = hi;
                 bslot = r;
             }
+            if (r == ks) nat_here = hi;
         }
         // key: magnitude class (top 24 of the 31 bits) | slot | inverted lane: the maximum is also the first lane on ties
         const int key = (best < 0) ? -1 : ((best & ~127) | (bslot << 5) | (G - 1 - g.gl));
         const int kmax = gmax_i_full<G>(key);
         const int mx = (kmax < 0) ? -1 : (kmax & ~127);
         ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
-        const int nat_here = (ord[ks] == NY) ? (__double2hiint(a[ks][k]) & 0x7fffffff) : -1;
         const int nat = __shfl_sync(FULL_MASK, nat_here, g.lane0 + kl);
         const bool natural = nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx;
-        if (__all_sync(FULL_MASK, natural)) {
-            double prow[NY];
+        identity = identity && natural;
+        const int pl = natural ? kl : G - 1 - (kmax & 31), ps = natural ? ks : (kmax >> 5) & 3;
+        const bool mine = (g.gl == pl);
+        double prow[NY];
 #pragma unroll
-            for (int j = 0; j < NY; ++j) prow[j] = __shfl_sync(FULL_MASK, a[ks][j], g.lane0 + kl);
-            const bool mine = (g.gl == kl);
-            if (mine) ord[ks] = k;
-            const double d = fast_rcp<2>(prow[k]);
+        for (int j = 0; j < NY; ++j) {
+            double v = a[0][j];
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const bool piv = (r == ks) && mine;
-                const double m = piv ? d : -a[r][k] * d;
+            for (int r = 1; r < R; ++r) v = (ps == r) ? a[r][j] : v;
+            prow[j] = v;
+        }
+        if (mine) sts_vec<NY>(buf, prow);
+        __syncwarp();
+        lds_vec<NY>(buf, prow);
+        const double d = fast_rcp<2>(prow[0]);
 #pragma unroll
-                for (int j = 0; j < NY; ++j) {
-                    if (j == k) continue;
-                    const double base = (r == ks) ? (mine ? 0.0 : a[r][j]) : a[r][j];
-                    a[r][j] = fma(m, prow[j], base);
-                }
-                a[r][k] = m;
+        for (int r = 0; r < R; ++r) {
+            const bool piv = mine && (ps == r);
+            if (piv) ord[r] = k;
+            double m = -a[r][0] * d;
+#pragma unroll
+            for (int j = 1; j < NY; ++j) a[r][j - 1] = fma(m, prow[j], a[r][j]);
+            if (piv) {  // the pivot row itself: d * row, and d on the diagonal (one lane per group)
+#pragma unroll
+                for (int j = 1; j < NY; ++j) a[r][j - 1] = d * prow[j];
+                m = d;
             }
-        } else {
-            const int pl = G - 1 - (kmax & 31), ps = (kmax >> 5) & 3;
-            const bool mine = (g.gl == pl);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (mine && r == ps) {
-                    ord[r] = k;
-#pragma unroll
-                    for (int j = 0; j < NY; ++j) {
-                        g.prow[j] = a[r][j];
-                        a[r][j] = 0.0;
-                    }
-                }
-            }
-            __syncwarp();
-            const double d = fast_rcp<2>(g.prow[k]);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const double m = (ord[r] != k) ? -a[r][k] * d : d;
-#pragma unroll
-                for (int j = 0; j < NY; ++j) {
-                    if (j == k) continue;
-                    a[r][j] = fma(m, g.prow[j], a[r][j]);
-                }
-                a[r][k] = m;
-            }
-            __syncwarp();
+            a[r][NY - 1] = m;
+        }
+        kl += 1;
+        if (kl == G) {
+            kl = 0;
+            ks += 1;
         }
     }
+    identity = __all_sync(FULL_MASK, identity);
     return ok;
 }
 
-// x = W^-1 b (see g_apply); full-warp synchronisation
+// x = W^-1 b with the in-place inverse of c_invert: a[r][m] = (W^-1)[ord[r]][p_m].  The right-hand side is staged in
+// pivot order (bs[ord[r]] = b[r]), every lane reads all of it (broadcast, 16 bytes at a time) and forms the R dot
+// products of its rows; the results are in variable order already when every pivot was the natural one (identity),
+// otherwise they go through shared memory once more.
 template <int G> __device__ __forceinline__ void c_apply(const Grp<G> &g, const double (*a)[NY], const int *ord,
-                                                         double *b) {
+                                                         bool identity, double *b) {
     constexpr int R = Grp<G>::R;
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < R; ++r)
         if (g.owns(r)) g.prow[ord[r]] = b[r];
     __syncwarp();
-    double acc[R];
+    double bs[NY], acc[R];
+    lds_vec<NY>(g.prow, bs);
 #pragma unroll
     for (int r = 0; r < R; ++r) acc[r] = 0.0;
 #pragma unroll
     for (int m = 0; m < NY; ++m) {
-        const double bm = g.prow[m];
 #pragma unroll
-        for (int r = 0; r < R; ++r) acc[r] = fma(a[r][m], bm, acc[r]);
+        for (int r = 0; r < R; ++r) acc[r] = fma(a[r][m], bs[m], acc[r]);
     }
+    if (identity) {
 #pragma unroll
-    for (int r = 0; r < R; ++r)
-        if (g.owns(r)) g.ys[ord[r]] = acc[r];
-    __syncwarp();
+        for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? acc[r] : 0.0;
+    } else {
 #pragma unroll
-    for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? g.ys[r * G + g.gl] : 0.0;
+        for (int r = 0; r < R; ++r)
+            if (g.owns(r)) g.ys[ord[r]] = acc[r];
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? g.ys[r * G + g.gl] : 0.0;
+    }
 }
 
 #define RC(name) kRos4[ros4c::name]
 template <int G> struct CoopRos4 {
     typedef CoopLayout<G> L;
     static constexpr int R = L::R;
+    double g1[R], g2[R], g3[R], g4[R], g5[R];  // stage increments of the last attempt (dense output needs them)
     double h_old;
     float err_old;
     bool first, last_rejected;
@@ -345,6 +416,7 @@ template <int G> struct CoopRos4 {
         extern __shared__ double c_smem[];
         double W[R][NY], dfdt[R], f[R], tmp[R], b[R];
         int ord[R];
+        bool identity;
         int bad = c.template eval<true>(g, a, t, y, f);
         const double ih = fast_rcp<2>(h);
         const double diag = 4.0 * ih;  // 1/gamma = 4
@@ -360,8 +432,16 @@ template <int G> struct CoopRos4 {
             }
             dfdt[r] = (!ODESYS_AUTONOMOUS && g.owns(r)) ? c_smem[L::oDF + i * L::NSYSP + c.sysl] : 0.0;
         }
-        if (!c_invert<G>(g, W, ord)) bad |= 1;
-#define G_SOLVE(vec) c_apply<G>(g, W, ord, vec)
+        {
+            COOP_T0(t_inv);
+            if (!c_invert<G>(g, W, ord, identity)) bad |= 1;
+            COOP_ACC(2, t_inv);
+        }
+#ifdef PYODESYS_COOP_PROFILE
+#define G_SOLVE(vec) { COOP_T0(t_s); c_apply<G>(g, W, ord, identity, vec); COOP_ACC(3, t_s); }
+#else
+#define G_SOLVE(vec) c_apply<G>(g, W, ord, identity, vec)
+#endif
         cnt.nlu += 1;
         cnt.nsolve += 6;
 #pragma unroll
@@ -369,63 +449,63 @@ template <int G> struct CoopRos4 {
         G_SOLVE(b);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            c.set_gk(g, 0, r, b[r]);
+            g1[r] = b[r];
             tmp[r] = fma(RC(A21), b[r], y[r]);
         }
         bad |= c.template eval<false>(g, a, fma(RC(C2X), h, t), tmp, f);
         const double c21 = RC(C21) * ih;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            b[r] = fma(c21, c.gk(g, 0, r), f[r]);
+            b[r] = fma(c21, g1[r], f[r]);
             if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D2), dfdt[r], b[r]);
         }
         G_SOLVE(b);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            c.set_gk(g, 1, r, b[r]);
-            tmp[r] = fma(RC(A32), b[r], fma(RC(A31), c.gk(g, 0, r), y[r]));
+            g2[r] = b[r];
+            tmp[r] = fma(RC(A32), b[r], fma(RC(A31), g1[r], y[r]));
         }
         bad |= c.template eval<false>(g, a, fma(RC(C3X), h, t), tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            b[r] = fma(ih, fma(RC(C32), c.gk(g, 1, r), RC(C31) * c.gk(g, 0, r)), f[r]);
+            b[r] = fma(ih, fma(RC(C32), g2[r], RC(C31) * g1[r]), f[r]);
             if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D3), dfdt[r], b[r]);
         }
         G_SOLVE(b);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            c.set_gk(g, 2, r, b[r]);
-            tmp[r] = fma(RC(A43), b[r], fma(RC(A42), c.gk(g, 1, r), fma(RC(A41), c.gk(g, 0, r), y[r])));
+            g3[r] = b[r];
+            tmp[r] = fma(RC(A43), b[r], fma(RC(A42), g2[r], fma(RC(A41), g1[r], y[r])));
         }
         bad |= c.template eval<false>(g, a, fma(RC(C4X), h, t), tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            b[r] = fma(ih, fma(RC(C43), c.gk(g, 2, r), fma(RC(C42), c.gk(g, 1, r), RC(C41) * c.gk(g, 0, r))), f[r]);
+            b[r] = fma(ih, fma(RC(C43), g3[r], fma(RC(C42), g2[r], RC(C41) * g1[r])), f[r]);
             if (!ODESYS_AUTONOMOUS) b[r] = fma(h * RC(D4), dfdt[r], b[r]);
         }
         G_SOLVE(b);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            c.set_gk(g, 3, r, b[r]);
-            tmp[r] = fma(RC(A54), b[r], fma(RC(A53), c.gk(g, 2, r), fma(RC(A52), c.gk(g, 1, r),
-                                                                          fma(RC(A51), c.gk(g, 0, r), y[r]))));
+            g4[r] = b[r];
+            tmp[r] = fma(RC(A54), b[r], fma(RC(A53), g3[r], fma(RC(A52), g2[r],
+                                                                          fma(RC(A51), g1[r], y[r]))));
         }
         bad |= c.template eval<false>(g, a, t + h, tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r)
-            b[r] = fma(ih, fma(RC(C54), c.gk(g, 3, r), fma(RC(C53), c.gk(g, 2, r),
-                               fma(RC(C52), c.gk(g, 1, r), RC(C51) * c.gk(g, 0, r)))), f[r]);
+            b[r] = fma(ih, fma(RC(C54), g4[r], fma(RC(C53), g3[r],
+                               fma(RC(C52), g2[r], RC(C51) * g1[r]))), f[r]);
         G_SOLVE(b);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            c.set_gk(g, 4, r, b[r]);
+            g5[r] = b[r];
             tmp[r] += b[r];
         }
         bad |= c.template eval<false>(g, a, t + h, tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r)
-            b[r] = fma(ih, fma(RC(C65), c.gk(g, 4, r), fma(RC(C64), c.gk(g, 3, r), fma(RC(C63), c.gk(g, 2, r),
-                               fma(RC(C62), c.gk(g, 1, r), RC(C61) * c.gk(g, 0, r))))), f[r]);
+            b[r] = fma(ih, fma(RC(C65), g5[r], fma(RC(C64), g4[r], fma(RC(C63), g3[r],
+                               fma(RC(C62), g2[r], RC(C61) * g1[r])))), f[r]);
         G_SOLVE(b);
 #undef G_SOLVE
         double e = 0.0;
@@ -476,7 +556,7 @@ template <int G> struct CoopRos4 {
         const double s1 = 1.0 - theta;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const double q1 = c.gk(g, 0, r), q2 = c.gk(g, 1, r), q3 = c.gk(g, 2, r), q4 = c.gk(g, 3, r), q5 = c.gk(g, 4, r);
+            const double q1 = g1[r], q2 = g2[r], q3 = g3[r], q4 = g4[r], q5 = g5[r];
             const double c3 = fma(RC(D25), q5, fma(RC(D24), q4, fma(RC(D23), q3, fma(RC(D22), q2, RC(D21) * q1))));
             const double c4 = fma(RC(D35), q5, fma(RC(D34), q4, fma(RC(D33), q3, fma(RC(D32), q2, RC(D31) * q1))));
             out[r] = yold[r] * s1 + theta * (ynew[r] + s1 * (c3 + theta * c4));
@@ -503,8 +583,12 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
     Coop<G> c;
     c.sysl = threadIdx.x / G;
     c.evalno = 0;
-    g.prow = c_smem + L::oScr + (size_t)c.sysl * 2 * NY;
-    g.ys = g.prow + NY;
+#ifdef PYODESYS_COOP_PROFILE
+    for (int k = 0; k < 10; ++k) c.prof[k] = 0;
+    const long long t_all = clock64();
+#endif
+    g.prow = c_smem + L::oScr + (size_t)c.sysl * 2 * L::NYE;
+    g.ys = g.prow + L::NYE;
     int *ist = reinterpret_cast<int *>(c_smem + L::oInt);
     if (threadIdx.x < 2 * L::NSYS) ist[threadIdx.x] = 0;
     for (int k = threadIdx.x; k < L::oScr - L::oP; k += kCoopBlock) c_smem[L::oP + k] = 0.0;  // finite garbage for idle slots
@@ -524,6 +608,7 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
     for (int r = 0; r < R; ++r) y[r] = 0.0;
 
     for (;;) {
+        COOP_T0(t_top);
         // ---- (B) + (E): termination test of the running system, retire ----------------------------------------
         if (active) {
             int status = -1;
@@ -646,7 +731,10 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
                 }
             }
         }
+        COOP_ACC(6, t_top);
+        COOP_T0(t_bar);
         if (__syncthreads_and(!active)) break;
+        COOP_ACC(7, t_bar);
         // a system that is about to retire (finished span, failure) idles through this iteration
         const bool live = active && t != tend && nfail >= 0 && nfail < (1 << 20);
 
@@ -659,6 +747,7 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
         }
 
         // ---- (C) one trial step of every system of the block -----------------------------------------------------------
+        COOP_T0(t_att);
         double hh = live ? h : 1.0;
         if (fabs(hh) > hmax) hh = dir * hmax;
         if (fabs(hh) < hmin) hh = dir * hmin;
@@ -672,7 +761,9 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
         double ynew[R], err = 0.0, hnext = hh;
         Counters scratch = cnt;
         const int bad = st.attempt(c, g, a, t, y, hh, ynew, err, live ? cnt : scratch);
+        COOP_ACC(8, t_att);
         if (!live) continue;
+        COOP_T0(t_post);
         nfev += 6;
         njev += 1;
         cnt.nsteps += 1;
@@ -735,7 +826,20 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
             t = tnew;
             h = hnext;
         }
+        COOP_ACC(9, t_post);
     }
+#ifdef PYODESYS_COOP_PROFILE
+    if (lane == 0) {
+        unsigned long long *out = reinterpret_cast<unsigned long long *>(a.root_out);
+        atomicAdd(out + 0, (unsigned long long)c.prof[0]);
+        atomicAdd(out + 1, (unsigned long long)c.prof[1]);
+        atomicAdd(out + 2, (unsigned long long)c.prof[2]);
+        atomicAdd(out + 3, (unsigned long long)c.prof[3]);
+        atomicAdd(out + 4, (unsigned long long)(clock64() - t_all));
+        atomicAdd(out + 5, 1ull);
+        for (int k = 6; k < 10; ++k) atomicAdd(out + k, (unsigned long long)c.prof[k]);
+    }
+#endif
 }
 
 #endif  // ODESYS_HAS_JAC

@@ -627,6 +627,9 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         a.y0 = y0; a.params = params; a.xout = xout; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
         a.yout = yout; a.nreached = nreached; a.status = status; a.counters = counters;
         if (want_roots(q)) { a.root_out = opt->root_out; a.root_indices = opt->root_indices; a.nroots_found = opt->nroots_found; }
+#ifdef PYODESYS_COOP_PROFILE
+        if (opt) a.root_out = opt->root_out;  // profiling build: phase counters land here
+#endif
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));
         if (dispatch<0>(c, a, method, stream, bps, opt)) return -1;

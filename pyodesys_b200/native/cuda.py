@@ -399,7 +399,7 @@ class CudaModule:
     def integrate_predefined_device(self, n, nt, y0, xout, params, atol, rtol, yout, nreached, status,
                                     counters=None, dx0=None, dx_min=None, dx_max=None, mxsteps=0,
                                     method=None, autorestart=0, device=0, stream=None, xout_shared=False,
-                                    yout_soa=False, **kw):
+                                    yout_soa=False, debug_buffer=None, **kw):
         """ Device-resident call (``ptr_kind=1``): every array argument is a device address (int,
         e.g. ``tensor.data_ptr()``) on ``device``; nothing is copied.  Returns the timings array. """
         atol = np.ascontiguousarray(np.atleast_1d(atol), dtype=np.float64)
@@ -409,6 +409,8 @@ class CudaModule:
         opts = self._options(xout_shared=xout_shared, **kw)
         opts.yout_soa = int(bool(yout_soa))
         opts.stream = stream
+        if debug_buffer is not None:  # profiling builds (-DPYODESYS_COOP_PROFILE) write their phase counters here
+            opts.root_out = debug_buffer
         timings = np.zeros(NTIMINGS)
         rc = self.lib.pyodesys_cuda_integrate_predefined(
             device, n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size, float(rtol),

@@ -11,13 +11,26 @@ import collections, csv, io, os, re, subprocess, sys, tempfile
 
 rep, so, pat = sys.argv[1:4]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+opfilter = sys.argv[5] if len(sys.argv) > 5 else None  # e.g. LDL: lines of that opcode only
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'sass'], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
 H = rows[hdr]
 ci, cs, ct = H.index('Instructions Executed'), H.index('Source'), H.index('Thread Instructions Executed')
 cw = H.index('# Samples') if '# Samples' in H else None
-sass = [(r[cs].strip(), int(r[ci]), int(r[ct]), int(r[cw]) if cw is not None else 0) for r in rows[hdr + 1:] if len(r) == len(H)]
+cwv = H.index('L1 Wavefronts Shared') if 'L1 Wavefronts Shared' in H else None
+cwx = H.index('L1 Wavefronts Shared Excessive') if 'L1 Wavefronts Shared Excessive' in H else None
+
+
+def _i(v):
+    try:
+        return int(v)
+    except ValueError:
+        return 0
+
+
+sass = [(r[cs].strip(), _i(r[ci]), _i(r[ct]), _i(r[cw]) if cw is not None else 0, _i(r[cwv]) if cwv else 0,
+         _i(r[cwx]) if cwx else 0) for r in rows[hdr + 1:] if len(r) == len(H)]
 tmp = tempfile.mkdtemp()
 subprocess.run(['cuobjdump', '-xelf', 'all', os.path.abspath(so)], cwd=tmp, capture_output=True)
 cub = [f for f in os.listdir(tmp) if f.endswith('.cubin')][0]
@@ -38,8 +51,12 @@ if len(lines) != len(sass):
     print('warning: %d disassembled vs %d profiled instructions' % (len(lines), len(sass)))
 n = min(len(lines), len(sass))
 tot = sum(s[1] for s in sass[:n])
-byfile, byline, byop, samples = (collections.Counter() for _ in range(4))
-for (loc, txt), (src, cnt, thr, smp) in zip(lines[:n], sass[:n]):
+byfile, byline, byop, samples, wav, wavx = (collections.Counter() for _ in range(6))
+for (loc, txt), (src, cnt, thr, smp, wv, wx) in zip(lines[:n], sass[:n]):
+    wav[loc] += wv
+    wavx[loc] += wx
+    if opfilter and not (txt.split()[1] if txt.startswith('@') else txt.split()[0]).startswith(opfilter):
+        continue
     byfile[loc[0]] += cnt
     byline[loc] += cnt
     samples[loc] += smp
@@ -54,3 +71,8 @@ for (f, ln), c in byline.most_common(top):
 print('--- opcodes')
 for op, c in byop.most_common(25):
     print('%6.2f %%  %s' % (100.0*c/tot, op))
+tw = sum(wav.values())
+if tw:
+    print('--- shared-memory / shuffle wavefronts: %.4g, excessive (bank conflicts) %.4g' % (tw, sum(wavx.values())))
+    for loc, v in wav.most_common(top//2):
+        print('%6.2f %%  (%5.1f %% excessive)  %s:%d' % (100.0*v/tw, 100.0*wavx[loc]/max(1, v), loc[0], loc[1]))

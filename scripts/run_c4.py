@@ -22,9 +22,20 @@ d_nr = torch.empty(n, dtype=torch.int32, device=dev)
 d_st = torch.empty(n, dtype=torch.int32, device=dev)
 d_cn = torch.zeros((6, n), dtype=torch.int32, device=dev)
 reps = int(os.environ.get('REPS', '2'))
+d_dbg = torch.zeros(16, dtype=torch.int64, device=dev)
+profile = 'COOP_PROFILE' in os.environ.get('PYODESYS_CUDA_NVCC_FLAGS', '')
 for _ in range(reps):
     tm = mod.integrate_predefined_device(n, nt, d_y0.data_ptr(), d_x.data_ptr(), d_p.data_ptr(), b['atol'], b['rtol'],
                                          d_out.data_ptr(), d_nr.data_ptr(), d_st.data_ptr(), d_cn.data_ptr(),
-                                         mxsteps=b['nsteps'], method=method, xout_shared=True, kernel=kernel)
+                                         mxsteps=b['nsteps'], method=method, xout_shared=True, kernel=kernel,
+                                         debug_buffer=d_dbg.data_ptr() if profile else None)
     print('%s n=%d kernel=%s method=%s: %.3f ms, ok %d, steps %.1f' % (name, n, kernel, method, tm[0]*1e3,
           int((d_st == 0).sum()), float(d_cn[0].float().mean())))
+if profile:
+    v = d_dbg.cpu().numpy().astype(float)
+    v[:5] /= reps
+    v[6:] /= reps
+    nw = v[5]/reps
+    print('per warp (cycles): total %.4g  evaluations incl. barriers %.4g (%.1f %%)  evaluator body %.4g  inverse %.4g (%.1f %%)  '
+          'solves %.4g (%.1f %%)' % (v[4]/nw, v[0]/nw, 100*v[0]/v[4], v[1]/nw, v[2]/nw, 100*v[2]/v[4], v[3]/nw, 100*v[3]/v[4]))
+    print('loop top (retire/fetch) %.1f %%, all-done barrier %.1f %%, attempt %.1f %%, control/output %.1f %%' % tuple(100*v[k]/v[4] for k in (6, 7, 8, 9)))
