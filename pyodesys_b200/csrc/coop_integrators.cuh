@@ -28,19 +28,18 @@ namespace pyodesys_cuda {
 #if ODESYS_HAS_JAC
 
 #ifndef PYODESYS_COOP_G
-// smallest group (>= 8 lanes) whose lanes keep their rows of W in at most 56 doubles
+// smallest group whose lanes keep their rows of W in at most 56 doubles (ny = 14: 4 lanes x 4 rows; ny = 28: 16 x 2)
 #define PYODESYS_COOP_FITS(g) ((((NY + (g) - 1) / (g)) * NY) <= 56)
-#define PYODESYS_COOP_G (PYODESYS_COOP_FITS(8) ? 8 : PYODESYS_COOP_FITS(16) ? 16 : 32)
+#define PYODESYS_COOP_G (PYODESYS_COOP_FITS(4) ? 4 : PYODESYS_COOP_FITS(8) ? 8 : PYODESYS_COOP_FITS(16) ? 16 : 32)
 #endif
 // Threads per block.  The systems of a block step in lock-step and every evaluation is a serial phase of ONE warp
 // (the others wait at the barrier), so what keeps an SM busy is the number of independent blocks on it, not the size
-// of a block: 128 threads = 3 blocks per SM at 168 registers (4 at 128 registers spill: local memory shares the
-// load/store data path that bounds the kernel).
+// of a block: 128 threads, 2 blocks per SM at up to 255 registers (no spills).
 #ifndef PYODESYS_COOP_BLOCK
 #define PYODESYS_COOP_BLOCK 128
 #endif
 #ifndef PYODESYS_COOP_MIN_BLOCKS
-#define PYODESYS_COOP_MIN_BLOCKS ((ODESYS_NY <= 16 ? 384 : 256) / PYODESYS_COOP_BLOCK)
+#define PYODESYS_COOP_MIN_BLOCKS (256 / PYODESYS_COOP_BLOCK)
 #endif
 
 constexpr int kCoopBlock = PYODESYS_COOP_BLOCK;
@@ -254,71 +253,106 @@ template <int N> __device__ __forceinline__ void sts_vec(double *buf, const doub
 // Fully unrolled, the NY pivot steps were 54 KB of the 94 KB loop body.  Register arrays only allow literal indices,
 // so every step works on PHYSICAL column 0 and shifts the columns left by one while it updates them
 //     a[r][j-1] <- a[r][j] + m_r * prow[j]   (j = 1..NY-1),      a[r][NY-1] <- m_r  (the new column of the inverse)
-// - after NY steps every logical column is back at its own position.  The pivot row (lane pl, slot ps; natural or
-// searched) is picked with selects, so one code path serves both cases.
+// - after NY steps every logical column is back at its own position.
+// Two more things keep the instruction count of a step down: the normalisation of the pivot rows is DEFERRED (a
+// pivot row is left as it is - multiplier 0, a one in the new column - and every row is scaled by the reciprocal of
+// its own pivot once, at the end; row operations commute with that scaling), and the loop runs slot by slot
+// (unrolled, R copies of the body) over the lanes of a group (rolled), so that the natural pivot row a[ks] is a
+// literal register row and needs no selects.
+template <int G, int KS>
+__device__ __forceinline__ void c_pivot_step(const Grp<G> &g, double (*a)[NY], int *ord, double *dinv, int k, int kl,
+                                             bool &ok, bool &identity) {
+    constexpr int R = Grp<G>::R;
+    double *buf = (k & 1) ? g.ys : g.prow;  // two staging vectors in turn: one warp synchronisation per step
+    int best = -1, bslot = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int hi = (ord[r] == NY) ? (__double2hiint(a[r][0]) & 0x7fffffff) : -1;
+        if (hi > best) {
+            best = hi;
+            bslot = r;
+        }
+    }
+    const int nat_here = (ord[KS] == NY) ? (__double2hiint(a[KS][0]) & 0x7fffffff) : -1;
+    // key: magnitude class (top 24 of the 31 bits) | slot | inverted lane: the maximum is also the first lane on ties
+    const int key = (best < 0) ? -1 : ((best & ~127) | (bslot << 5) | (G - 1 - g.gl));
+    const int kmax = gmax_i_full<G>(key);
+    const int mx = (kmax < 0) ? -1 : (kmax & ~127);
+    ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
+    const int nat = __shfl_sync(FULL_MASK, nat_here, g.lane0 + kl);
+    const bool natural = nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx;
+    double prow[NY];
+    bool piv[R];
+    if (__all_sync(FULL_MASK, natural)) {
+        const bool mine = (g.gl == kl);
+#pragma unroll
+        for (int r = 0; r < R; ++r) piv[r] = (r == KS) && mine;
+        if (mine) {
+#pragma unroll
+            for (int j = 0; j < NY; ++j) buf[j] = a[KS][j];
+        }
+    } else {
+        identity = false;
+        const int pl = natural ? kl : G - 1 - (kmax & 31), ps = natural ? KS : (kmax >> 5) & 3;
+        const bool mine = (g.gl == pl);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            piv[r] = mine && (ps == r);
+            if (piv[r]) {
+#pragma unroll
+                for (int j = 0; j < NY; ++j) buf[j] = a[r][j];
+            }
+        }
+    }
+    __syncwarp();
+    lds_vec<NY>(buf, prow);
+    const double d = fast_rcp<2>(prow[0]);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (piv[r]) {
+            ord[r] = k;
+            dinv[r] = d;
+        }
+        const double m = piv[r] ? 0.0 : -a[r][0] * d;
+#pragma unroll
+        for (int j = 1; j < NY; ++j) a[r][j - 1] = fma(m, prow[j], a[r][j]);
+        a[r][NY - 1] = piv[r] ? 1.0 : m;
+    }
+}
+
 template <int G> __device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord, bool &identity) {
     constexpr int R = Grp<G>::R;
     static_assert(R <= 4 && G <= 32, "pivot key packs the slot in 2 bits, the lane in 5");
     bool ok = true;
     identity = true;  // every pivot so far was the natural one: W^-1 comes out in variable order
+    double dinv[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) ord[r] = g.owns(r) ? NY : -1;
-    int kl = 0, ks = 0;  // owner lane (inside the group) and slot of the natural row k
-#pragma unroll 1
-    for (int k = 0; k < NY; ++k) {
-        double *buf = (k & 1) ? g.ys : g.prow;  // two staging vectors in turn: one warp synchronisation per step
-        int best = -1, bslot = 0, nat_here = -1;
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int hi = (ord[r] == NY) ? (__double2hiint(a[r][0]) & 0x7fffffff) : -1;
-            if (hi > best) {
-                best = hi;
-                bslot = r;
-            }
-            if (r == ks) nat_here = hi;
-        }
-        // key: magnitude class (top 24 of the 31 bits) | slot | inverted lane: the maximum is also the first lane on ties
-        const int key = (best < 0) ? -1 : ((best & ~127) | (bslot << 5) | (G - 1 - g.gl));
-        const int kmax = gmax_i_full<G>(key);
-        const int mx = (kmax < 0) ? -1 : (kmax & ~127);
-        ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
-        const int nat = __shfl_sync(FULL_MASK, nat_here, g.lane0 + kl);
-        const bool natural = nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx;
-        identity = identity && natural;
-        const int pl = natural ? kl : G - 1 - (kmax & 31), ps = natural ? ks : (kmax >> 5) & 3;
-        const bool mine = (g.gl == pl);
-        double prow[NY];
-#pragma unroll
-        for (int j = 0; j < NY; ++j) {
-            double v = a[0][j];
-#pragma unroll
-            for (int r = 1; r < R; ++r) v = (ps == r) ? a[r][j] : v;
-            prow[j] = v;
-        }
-        if (mine) sts_vec<NY>(buf, prow);
-        __syncwarp();
-        lds_vec<NY>(buf, prow);
-        const double d = fast_rcp<2>(prow[0]);
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const bool piv = mine && (ps == r);
-            if (piv) ord[r] = k;
-            double m = -a[r][0] * d;
-#pragma unroll
-            for (int j = 1; j < NY; ++j) a[r][j - 1] = fma(m, prow[j], a[r][j]);
-            if (piv) {  // the pivot row itself: d * row, and d on the diagonal (one lane per group)
-#pragma unroll
-                for (int j = 1; j < NY; ++j) a[r][j - 1] = d * prow[j];
-                m = d;
-            }
-            a[r][NY - 1] = m;
-        }
-        kl += 1;
-        if (kl == G) {
-            kl = 0;
-            ks += 1;
-        }
+    for (int r = 0; r < R; ++r) {
+        ord[r] = g.owns(r) ? NY : -1;
+        dinv[r] = 0.0;
     }
+    // natural row k = slot ks, lane kl of the group: slots unrolled (literal register rows), lanes rolled
+    if (R > 0) {
+#pragma unroll 1
+        for (int kl = 0; kl < G && kl < NY; ++kl) c_pivot_step<G, 0>(g, a, ord, dinv, kl, kl, ok, identity);
+    }
+    if (R > 1) {
+#pragma unroll 1
+        for (int kl = 0; kl < G && G + kl < NY; ++kl) c_pivot_step<G, 1 % R>(g, a, ord, dinv, G + kl, kl, ok, identity);
+    }
+    if (R > 2) {
+#pragma unroll 1
+        for (int kl = 0; kl < G && 2 * G + kl < NY; ++kl) c_pivot_step<G, 2 % R>(g, a, ord, dinv, 2 * G + kl, kl, ok, identity);
+    }
+    if (R > 3) {
+#pragma unroll 1
+        for (int kl = 0; kl < G && 3 * G + kl < NY; ++kl) c_pivot_step<G, 3 % R>(g, a, ord, dinv, 3 * G + kl, kl, ok, identity);
+    }
+    // deferred normalisation: row p of the inverse is the accumulated row divided by its pivot
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int j = 0; j < NY; ++j) a[r][j] *= dinv[r];
     identity = __all_sync(FULL_MASK, identity);
     return ok;
 }
