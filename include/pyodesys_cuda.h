@@ -166,6 +166,24 @@ int pyodesys_cuda_integrate_adaptive(
     int32_t *status, int32_t *counters, double *timings,
     int ptr_kind, const pyodesys_cuda_options *options);
 
+/* Adaptive mode with COMPACTED output (host pointers; ABI v4).  Same integration as
+ * pyodesys_cuda_integrate_adaptive, but the rows stay on the device: an exclusive scan of the per-system row counts
+ * gives offsets[n + 1] (written to the host array), the rows that were actually written are packed into ONE
+ * contiguous device array [offsets[n], 1 + ny] and pyodesys_cuda_fetch_compact_rows copies exactly those to the
+ * caller - the wrapper of the reference hands back ``result[idx].first + 1`` rows per system
+ * (_cvode_wrapper.pyx:198-205), not the whole preallocated buffer.  System i owns rows offsets[i] .. offsets[i+1]-1;
+ * with event functions root_indices count rows of system i from its first row.  ``max_rows_per_system`` only bounds
+ * the device-side scratch (status PYODESYS_CUDA_ERR_ROWS when a system needs more).  The fetch must follow its
+ * compacting call on the same (device, options.ctx_lane) before the next integrate call on that lane. */
+int pyodesys_cuda_integrate_adaptive_compact(
+    int device, int64_t n, const double *y0, const double *x0, const double *xend, const double *params,
+    const double *atol, int natol, double rtol, const double *dx0, const double *dx_min, const double *dx_max,
+    int64_t mxsteps, int method, int autorestart, int return_on_error, int64_t max_rows_per_system,
+    int64_t *offsets,      /* host [n + 1] */
+    int32_t *status, int32_t *counters, double *timings, const pyodesys_cuda_options *options);
+int pyodesys_cuda_fetch_compact_rows(int device, int ctx_lane, double *rows /* host [offsets[n], 1 + ny] */,
+                                     int64_t nrows_total);
+
 /* Verification hooks (host pointers): evaluate the generated OdeSys::rhs / dense_jac_rmaj
  * (odesys_anyode_template.cpp:147-204,246-293) for a batch, and run the in-register LU that
  * the Rosenbrock stepper uses (role of AnyODE::getrf_callback/getrs_callback,

@@ -385,8 +385,7 @@ def integrate_auto_switch(odes, kw, x, y0, params=(), **kwargs):
     ``odes[0]`` integrates first with its entry of every iterable in ``kw`` (typically a small ``nsteps`` and
     ``return_on_error=True``); systems that did not reach the end are restarted from where they stopped with
     ``odes[1]`` and so on.  Adaptive mode only (``x`` = (x0, xend) per system), like the reference.  The
-    restart is one batched call per formulation: systems that already finished go through it as zero-length
-    spans.  Returns one :class:`Result` (or a list for a batch) whose ``info`` sums ``nfev, njev, time_cpu,
+    restart is one batched call per formulation over the UNFINISHED systems only.  Returns one :class:`Result` (or a list for a batch) whose ``info`` sums ``nfev, njev, time_cpu,
     time_wall`` and carries ``nsys`` = number of formulations used.
     """
     x_arr = np.asarray(x, dtype=np.float64)
@@ -405,34 +404,51 @@ def integrate_auto_switch(odes, kw, x, y0, params=(), **kwargs):
     tot = [dict.fromkeys(sum_keys, 0) for _ in range(n)]
     last_params = None
     used = 0
+    # only what has not finished yet is handed to the next formulation (``pyodesys/core.py:865-908`` restarts what
+    # did not finish; a batch that mostly succeeds in its first formulation costs one small second call)
+    P = params
+    per_system_params = False
+    try:
+        parr = np.asarray(params, dtype=np.float64)
+        if parr.ndim == 2 and parr.shape[0] == n and n > 1:
+            P, per_system_params = parr, True
+    except (TypeError, ValueError):
+        pass
+    todo = np.arange(n)
+    last_params = [None]*n
+    nsys_used = np.zeros(n, dtype=int)
     for oi, ode in enumerate(odes):
         used = oi + 1
         if oi < len(odes) - 1:
             nxt_aut = autonomous(odes[oi + 1])
         call_kw = dict(kwargs)
         call_kw.update({k: v[oi] for k, v in kw.items()})
-        res = ode.integrate(X if batch else X[0], Y0 if batch else Y0[0], params, **call_kw)
+        p_arg = P[todo] if per_system_params else P
+        res = ode.integrate(X[todo] if batch else X[0], Y0[todo] if batch else Y0[0], p_arg, **call_kw)
         legs = res if batch else [res]
-        done = True
-        for i, r in enumerate(legs):
+        unfinished = []
+        for j, r in enumerate(legs):
+            i = int(todo[j])
             xs[i].append(np.asarray(r.xout)[1:] + offset[i])
             ys[i].append(np.asarray(r.yout)[1:])
             for k in sum_keys:
                 if k in r.info:
                     tot[i][k] += r.info[k]
             tot[i]['success'] = r.info['success']
-            done = done and bool(r.info['success'])
-        last_params = [r.params for r in legs]
-        if done or oi == len(odes) - 1:
+            last_params[i] = r.params
+            nsys_used[i] = used
+            if not r.info['success']:
+                unfinished.append(i)
+                xlast = np.asarray(r.xout)[-1]
+                if nxt_aut:
+                    X[i] = (0.0, abs(X[i, -1] - xlast))
+                    offset[i] += xlast
+                else:
+                    X[i, 0] = xlast
+                Y0[i] = np.asarray(r.yout)[-1]
+        if not unfinished or oi == len(odes) - 1:
             break
-        for i, r in enumerate(legs):
-            xlast = np.asarray(r.xout)[-1]
-            if nxt_aut:
-                X[i] = (0.0, abs(X[i, -1] - xlast))
-                offset[i] += xlast
-            else:
-                X[i, 0] = xlast
-            Y0[i] = np.asarray(r.yout)[-1]
+        todo = np.array(unfinished)
     out = [Result(np.concatenate(xs[i]), np.concatenate(ys[i], axis=0), last_params[i], dict(nsys=used, **tot[i]),
                   odes[0]) for i in range(n)]
     return out if batch else out[0]

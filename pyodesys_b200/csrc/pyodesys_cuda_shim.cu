@@ -69,7 +69,7 @@ constexpr int kMaxDev = 64;
 #endif
 constexpr int kBlock = PYODESYS_BLOCK;
 
-enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, B_ROOTOUT, B_ROOTIDX, B_NROOTS, B_READY, B_SLICEDONE, NBUF };
+enum Buf { B_Y0, B_PARAMS, B_XOUT, B_XEND, B_DX0, B_DXMIN, B_DXMAX, B_YOUT, B_NREACHED, B_STATUS, B_COUNTERS, B_WORK, B_ROOTOUT, B_ROOTIDX, B_NROOTS, B_READY, B_SLICEDONE, B_OFFSETS, B_BLOCKSUMS, B_COMPACT, NBUF };
 
 struct DevCtx {
     std::mutex mtx;
@@ -85,6 +85,7 @@ struct DevCtx {
     // host-mapped completion flags the kernel sets per output slice
     unsigned long long *h_ready = nullptr;
     unsigned int *h_flags = nullptr, *d_flags = nullptr;
+    int64_t compact_rows = 0;  // rows left in buf[B_COMPACT] by the last compacting adaptive call
 };
 constexpr int kMaxSlices = 64;
 constexpr int kLanes = 2;  // independent call contexts per device (options.ctx_lane): two host threads can keep one GPU busy
@@ -515,6 +516,86 @@ bool streaming_enabled() {
     return !(env && env[0] == '0');
 }
 
+
+// ---- compaction of the ragged adaptive output ------------------------------------------------------
+// The kernels write every accepted step into bounded per-system buffers xyout[n, max_rows, 1 + ny]; what the caller
+// gets - like the reference's cvode wrapper, which hands back exactly ``result[idx].first + 1`` rows per system
+// (_cvode_wrapper.pyx:198-205) - is ONE contiguous array of the rows that were written plus offsets[n + 1]:
+// exclusive scan of nrows (three small kernels), one warp per system copies its rows (coalesced), and only
+// sum(nrows) * (1 + ny) * 8 bytes cross PCIe instead of n * max_rows * (1 + ny) * 8.
+constexpr int kScanTile = 2048, kScanBlock = 256, kScanPer = kScanTile / kScanBlock;
+__device__ __forceinline__ long long block_exclusive_scan(long long v, long long *total) {
+    __shared__ long long warp_sums[kScanBlock / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    long long inc = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const long long u = __shfl_up_sync(FULL_MASK, inc, off);
+        if (lane >= off) inc += u;
+    }
+    if (lane == 31) warp_sums[w] = inc;
+    __syncthreads();
+    long long base = 0, tot = 0;
+#pragma unroll
+    for (int k = 0; k < kScanBlock / 32; ++k) {
+        const long long ws = warp_sums[k];
+        if (k < w) base += ws;
+        tot += ws;
+    }
+    __syncthreads();
+    *total = tot;
+    return base + inc - v;
+}
+__global__ void scan_tile_sums(const int32_t *nrows, int64_t n, long long *tile_sums) {
+    const int64_t lo = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+    long long v = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPer; ++k)
+        if (lo + k < n) v += nrows[lo + k];
+    long long tot;
+    block_exclusive_scan(v, &tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+__global__ void scan_tiles(long long *tile_sums, int ntiles) {  // one block: exclusive scan in place, carry over passes
+    long long carry = 0;
+    for (int base = 0; base < ntiles; base += kScanBlock) {
+        const int i = base + threadIdx.x;
+        const long long v = i < ntiles ? tile_sums[i] : 0;
+        long long tot;
+        const long long ex = block_exclusive_scan(v, &tot);
+        if (i < ntiles) tile_sums[i] = carry + ex;
+        carry += tot;
+    }
+}
+__global__ void scan_offsets(const int32_t *nrows, int64_t n, const long long *tile_sums, long long *offsets) {
+    const int64_t lo = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+    long long v[kScanPer], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPer; ++k) {
+        v[k] = lo + k < n ? nrows[lo + k] : 0;
+        sum += v[k];
+    }
+    long long tot;
+    long long run = tile_sums[blockIdx.x] + block_exclusive_scan(sum, &tot);
+#pragma unroll
+    for (int k = 0; k < kScanPer; ++k) {
+        if (lo + k < n) offsets[lo + k] = run;
+        run += v[k];
+        if (lo + k == n - 1) offsets[n] = run;
+    }
+}
+__global__ void compact_rows(const double *xyout, const long long *offsets, int64_t n, int64_t max_rows, int rowlen,
+                             double *out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < n; s += nwarps) {
+        const long long o = offsets[s], cnt = (offsets[s + 1] - o) * rowlen;
+        const double *src = xyout + s * max_rows * rowlen;
+        double *dst = out + o * rowlen;
+        for (long long i = lane; i < cnt; i += 32) dst[i] = src[i];
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -830,14 +911,17 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
                                      const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps,
                                      int method, int autorestart, int return_on_error, int64_t max_rows,
                                      double *xyout, int32_t *nrows, int32_t *status, int32_t *counters,
-                                     double *timings, int ptr_kind, const pyodesys_cuda_options *opt) {
+                                     double *timings, int ptr_kind, const pyodesys_cuda_options *opt,
+                                     int64_t *compact_offsets = nullptr) {
     (void)return_on_error;
     const double t_begin = now_s();
     Common q{device, n, y0, params, atol, natol, rtol, dx0, dx_min, dx_max, mxsteps, method, autorestart,
              status, counters, timings, ptr_kind, opt};
     if (check_common(q)) return -1;
     if (max_rows < 2) return fail("max_rows_per_system must be at least 2");
-    if ((!x0 || !xend || !xyout || !nrows) && n > 0) return fail("x0/xend/xyout/nrows must not be NULL");
+    const bool compact = compact_offsets != nullptr;  // rows stay on the device, compacted; see fetch_compact_rows
+    if (compact && ptr_kind != 0) return fail("the compacting call takes host pointers");
+    if ((!x0 || !xend || (!compact && (!xyout || !nrows))) && n > 0) return fail("x0/xend/xyout/nrows must not be NULL");
     if (timings) for (int i = 0; i < PYODESYS_CUDA_NTIMINGS; ++i) timings[i] = 0.0;
     if (n == 0) return 0;
     DevCtx &c = g_ctx[device][lane_of(opt)];
@@ -925,7 +1009,7 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
         if (k == 0) CU_CHECK(cudaEventRecord(c.ev_k0, st));
         if (dispatch<1>(c, ak, method, st, bps, opt)) return -1;
         if (k == plan.nchunks - 1) CU_CHECK(cudaEventRecord(c.ev_k1, st));
-        if (d2h(c, B_YOUT, xyout, row_bytes, lo, len, st) || d2h(c, B_NREACHED, nrows, 4, lo, len, st) ||
+        if ((!compact && (d2h(c, B_YOUT, xyout, row_bytes, lo, len, st) || d2h(c, B_NREACHED, nrows, 4, lo, len, st))) ||
             d2h(c, B_STATUS, status, 4, lo, len, st))
             return -1;
         if (counters)
@@ -938,6 +1022,29 @@ static int integrate_adaptive_impl(int device, int64_t n, const double *y0, cons
     }
     CU_CHECK(cudaEventRecord(c.ev_join, c.stream2));
     CU_CHECK(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+    if (compact) {
+        const int ntiles = (int)((n + kScanTile - 1) / kScanTile);
+        if (ensure(c, B_OFFSETS, (nn + 1) * 8) || ensure(c, B_BLOCKSUMS, (size_t)ntiles * 8)) return -1;
+        const int32_t *d_nrows = (const int32_t *)c.buf[B_NREACHED];
+        long long *d_off = (long long *)c.buf[B_OFFSETS], *d_tiles = (long long *)c.buf[B_BLOCKSUMS];
+        scan_tile_sums<<<ntiles, kScanBlock, 0, c.stream>>>(d_nrows, n, d_tiles);
+        scan_tiles<<<1, kScanBlock, 0, c.stream>>>(d_tiles, ntiles);
+        scan_offsets<<<ntiles, kScanBlock, 0, c.stream>>>(d_nrows, n, d_tiles, d_off);
+        g_launches.fetch_add(3);
+        CU_CHECK(cudaGetLastError());
+        CU_CHECK(cudaMemcpyAsync(compact_offsets, d_off, (nn + 1) * 8, cudaMemcpyDeviceToHost, c.stream));
+        CU_CHECK(cudaStreamSynchronize(c.stream));  // the total decides the size of the compact buffer
+        const int64_t total = compact_offsets[n];
+        c.compact_rows = total;
+        if (total > 0) {
+            if (ensure(c, B_COMPACT, (size_t)total * (1 + NY) * 8)) return -1;
+            const int blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)c.sm_count * 8);
+            compact_rows<<<blocks, 256, 0, c.stream>>>((const double *)c.buf[B_YOUT], d_off, n, max_rows, 1 + NY,
+                                                       (double *)c.buf[B_COMPACT]);
+            g_launches.fetch_add(1);
+            CU_CHECK(cudaGetLastError());
+        }
+    }
     CU_CHECK(cudaEventRecord(c.ev[3], c.stream));
     CU_CHECK(cudaStreamSynchronize(c.stream));
     return pipeline_timings(c, timings, t_begin);
@@ -986,6 +1093,35 @@ int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, co
                                            status, counters, timings, ptr_kind, opt);
     if (rc != 0) drain_after_failure(device);
     return rc;
+}
+
+int pyodesys_cuda_integrate_adaptive_compact(int device, int64_t n, const double *y0, const double *x0,
+                                             const double *xend, const double *params, const double *atol, int natol,
+                                             double rtol, const double *dx0, const double *dx_min, const double *dx_max,
+                                             int64_t mxsteps, int method, int autorestart, int return_on_error,
+                                             int64_t max_rows, int64_t *offsets, int32_t *status, int32_t *counters,
+                                             double *timings, const pyodesys_cuda_options *opt) {
+    if (!offsets) return fail("offsets must not be NULL");
+    if (n == 0) { offsets[0] = 0; return 0; }
+    const int rc = integrate_adaptive_impl(device, n, y0, x0, xend, params, atol, natol, rtol, dx0, dx_min, dx_max,
+                                           mxsteps, method, autorestart, return_on_error, max_rows, nullptr, nullptr,
+                                           status, counters, timings, 0, opt, offsets);
+    if (rc != 0) drain_after_failure(device);
+    return rc;
+}
+
+int pyodesys_cuda_fetch_compact_rows(int device, int ctx_lane, double *rows, int64_t nrows_total) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+    DevCtx &c = g_ctx[device][(ctx_lane > 0 && ctx_lane < kLanes) ? ctx_lane : 0];
+    std::lock_guard<std::mutex> lock(c.mtx);
+    if (!c.ready) return fail("no compacted rows on device %d", device);
+    if (nrows_total != c.compact_rows) return fail("the last compacting call left %lld rows, %lld asked for", (long long)c.compact_rows, (long long)nrows_total);
+    if (nrows_total == 0) return 0;
+    if (!rows) return fail("rows is NULL");
+    CU_CHECK(cudaSetDevice(device));
+    CU_CHECK(cudaMemcpyAsync(rows, c.buf[B_COMPACT], (size_t)nrows_total * (1 + NY) * 8, cudaMemcpyDeviceToHost, c.stream));
+    CU_CHECK(cudaStreamSynchronize(c.stream));
+    return 0;
 }
 
 // Free every device buffer, stream and pinned table this library holds for ``device`` (they are created lazily and

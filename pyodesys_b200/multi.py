@@ -94,7 +94,7 @@ def chunk_size(n, ndevices, target=250000, minimum=32768):
 def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol, rtol, nsteps,
                       first_step, kwargs):
     """ Runs ``mod`` (a :class:`~pyodesys_b200.native.cuda.CudaModule`) on several devices at once. """
-    from .native.cuda import _Ragged, _tdict
+    from .native.cuda import _RaggedPieces, _tdict
     n = y0.shape[0]
     devices = list(devices)
     g = len(devices)
@@ -122,8 +122,7 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
         max_rows = kw.pop('max_rows', None) or steps*(1 + int(kw.get('autorestart', 0))) + 1
         if root_arrays is not None:
             max_rows += max_roots
-        xyout = mod.pinned.empty((n, max_rows, 1 + ny), np.float64)
-        nrows = mod.pinned.empty((n,), np.int32)
+        pieces = []  # compacted rows of every chunk: (first system, rows, offsets)
     else:
         shared_x = intern_x.shape[0] > 1 and intern_x.strides[0] == 0  # one broadcast row (core.to_arrays)
         xout = np.ascontiguousarray(intern_x[0] if shared_x else intern_x, dtype=np.float64)
@@ -158,11 +157,13 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
                     extra = dict(roots_sink={}, return_on_root=return_on_root, max_roots=max_roots,
                                  roots_out=tuple(a[lo:hi] for a in root_arrays))
                 if adaptive:
-                    r = mod.integrate_adaptive_arrays(
+                    pcs, _st, _cn, tm = mod.integrate_adaptive_compact(
                         y0[lo:hi], intern_x[lo:hi, 0], intern_x[lo:hi, 1], params[lo:hi], atol, rtol,
                         dx0=_rows(first_step, lo, hi, n), mxsteps=nsteps, device=dev, max_rows=max_rows,
-                        out=xyout[lo:hi], out_aux=(nrows[lo:hi], status[lo:hi], counters[:, lo:hi], n),
-                        ctx_lane=lane, **extra, **_row_kw(kw, lo, hi, n))
+                        out_aux=(status[lo:hi], counters[:, lo:hi], n), ctx_lane=lane, **extra,
+                        **_row_kw(kw, lo, hi, n))
+                    pieces.extend((lo + plo, rows, off) for plo, rows, off in pcs)  # list.extend is atomic enough
+                    r = (None, None, None, None, tm)
                 else:
                     r = mod.integrate_predefined_arrays(
                         y0[lo:hi], xout if shared_x else xout[lo:hi], params[lo:hi], atol, rtol,
@@ -189,8 +190,10 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
     method = kwargs.get('method') or mod.default_method()
     iv = y0 if kwargs.get('iv_from_y0', False) else None
     if adaptive:
-        binfo = BatchInfo('adaptive', status, None, counters, 0.0, 0.0, _Ragged(xyout, nrows, 0),
-                          _Ragged(xyout, nrows, 1), params, roe, timings=_tdict(tmax), method=method, iv=iv)
+        pieces.sort(key=lambda pc: pc[0])
+        binfo = BatchInfo('adaptive', status, None, counters, 0.0, 0.0, _RaggedPieces(pieces, n, 0),
+                          _RaggedPieces(pieces, n, 1), params, roe, timings=_tdict(tmax), method=method, iv=iv)
+        binfo.d2h_bytes = sum(r_.nbytes + o_.nbytes for _lo, r_, o_ in pieces) + status.nbytes + counters.nbytes
     else:
         binfo = BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, params, roe,
                           nt=nt, timings=_tdict(tmax), method=method, iv=iv)

@@ -200,6 +200,14 @@ class CudaModule:
             ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d, ctypes.c_int, ctypes.c_double,
             _d, _d, _d, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
             _d, _i32, _i32, _i32, _d, ctypes.c_int, ctypes.POINTER(Options)]
+        _i64 = ctypes.POINTER(ctypes.c_int64)
+        lib.pyodesys_cuda_integrate_adaptive_compact.restype = ctypes.c_int
+        lib.pyodesys_cuda_integrate_adaptive_compact.argtypes = [
+            ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d, ctypes.c_int, ctypes.c_double,
+            _d, _d, _d, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
+            _i64, _i32, _i32, _d, ctypes.POINTER(Options)]
+        lib.pyodesys_cuda_fetch_compact_rows.restype = ctypes.c_int
+        lib.pyodesys_cuda_fetch_compact_rows.argtypes = [ctypes.c_int, ctypes.c_int, _d, ctypes.c_int64]
         lib.pyodesys_cuda_eval.restype = ctypes.c_int
         lib.pyodesys_cuda_eval.argtypes = [ctypes.c_int, ctypes.c_int64, _d, _d, _d, _d, _d, _d]
         lib.pyodesys_cuda_eval_jtimes.restype = ctypes.c_int
@@ -395,6 +403,69 @@ class CudaModule:
         self._check(rc)
         _check_nan_y0(y0, status)
         return xyout, nrows, status, counters, timings
+
+    # device scratch of the bounded row buffers of one compacting call (systems beyond it go into further calls)
+    adaptive_scratch_bytes = 4 << 30
+
+    def integrate_adaptive_compact(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
+                                   mxsteps=0, method=None, autorestart=0, return_on_error=False, device=0,
+                                   max_rows=None, out_aux=None, special_settings=None, **kw):
+        """ Adaptive mode, compacted output: ``(pieces, status, counters, timings)`` with ``pieces`` a list of
+        ``(first_system, rows[total, 1 + ny], offsets[m + 1])`` - exactly the rows that were written
+        (``_cvode_wrapper.pyx:198-205``), in page-locked memory.  One piece per device call; a batch is cut into
+        several calls when its bounded device scratch ``n * max_rows * (1 + ny) * 8`` would exceed
+        :attr:`adaptive_scratch_bytes` (round-1 advisor finding: that product used to be allocated - and copied over
+        PCIe - in one piece, 16 GB for 1e6 three-component systems at the default ``nsteps``). """
+        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
+                                                                   kw.get('iv_from_y0', False))
+        x0 = np.ascontiguousarray(x0, dtype=np.float64).reshape(-1)
+        xend = np.ascontiguousarray(xend, dtype=np.float64).reshape(-1)
+        if x0.size != n or xend.size != n:
+            raise ValueError("x0/xend need to be of length N")
+        kw_roots = self._pop_roots(kw)
+        opts = self._options(**kw)
+        has_roots = self._root_buffers(opts, n, kw_roots) is not None
+        if max_rows is None:
+            steps = int(mxsteps) if mxsteps else 500
+            max_rows = steps*(1 + int(autorestart)) + 1 + (kw_roots[2] if has_roots else 0)
+        if out_aux is None:
+            status = self.pinned.empty((n,), np.int32)
+            counters = self.pinned.empty((NCOUNTERS, n), np.int32)
+            opts.counters_ld = n
+        else:  # windows of batch-wide arrays (multi.integrate_sharded)
+            status, counters, opts.counters_ld = out_aux
+        per = max(1, int(self.adaptive_scratch_bytes // (max_rows*(1 + self.ny)*8)))
+        timings = np.zeros(NTIMINGS)
+        pieces = []
+        root_ptrs = (opts.root_out, opts.root_indices, opts.nroots_found) if has_roots else None
+        for lo in range(0, max(n, 1), per):
+            hi = min(n, lo + per)
+            m = hi - lo
+            if m <= 0:
+                break
+            offsets = np.empty(m + 1, dtype=np.int64)
+            t1 = np.zeros(NTIMINGS)
+            if has_roots:  # row windows of the three root arrays
+                mr = kw_roots[2]
+                opts.root_out = root_ptrs[0] + lo*mr*(1 + self.ny)*8
+                opts.root_indices = root_ptrs[1] + lo*mr*4
+                opts.nroots_found = root_ptrs[2] + lo*4
+            sl = slice(lo, hi)
+            rc = self.lib.pyodesys_cuda_integrate_adaptive_compact(
+                device, m, _ptr(y0[sl]), _ptr(x0[sl]), _ptr(xend[sl]), _ptr(params[sl]), _ptr(atol), atol.size,
+                float(rtol), _ptr(None if dx0 is None else dx0[sl]), _ptr(None if dx_min is None else dx_min[sl]),
+                _ptr(None if dx_max is None else dx_max[sl]), int(mxsteps), mid, int(autorestart),
+                int(return_on_error), int(max_rows), offsets.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                _ptr(status[sl], _i32), ctypes.cast(ctypes.c_void_p(counters.ctypes.data + lo*4), _i32), _ptr(t1),
+                ctypes.byref(opts))
+            self._check(rc)
+            total = int(offsets[m])
+            rows = self.pinned.empty((total, 1 + self.ny), np.float64)
+            self._check(self.lib.pyodesys_cuda_fetch_compact_rows(device, int(opts.ctx_lane), _ptr(rows), total))
+            pieces.append((lo, rows, offsets))
+            timings += t1
+        _check_nan_y0(y0, status)
+        return pieces, status, counters, timings
 
     def integrate_predefined_device(self, n, nt, y0, xout, params, atol, rtol, yout, nreached, status,
                                     counters=None, dx0=None, dx_min=None, dx_max=None, mxsteps=0,
@@ -681,12 +752,13 @@ class NativeCudaSys(SymbolicSys):
             binfo = integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol, rtol,
                                       nsteps, first_step, kwargs)
         elif intern_x.shape[-1] == 2 and not force_predefined:
-            xyout, nrows, status, counters, timings = mod.integrate_adaptive_arrays(
+            pieces, status, counters, timings = mod.integrate_adaptive_compact(
                 y0, intern_x[:, 0], intern_x[:, 1], params, atol, rtol, dx0=first_step, mxsteps=nsteps, **kwargs)
-            xs = _Ragged(xyout, nrows, 0)
-            ys = _Ragged(xyout, nrows, 1)
+            xs = _RaggedPieces(pieces, len(status), 0)
+            ys = _RaggedPieces(pieces, len(status), 1)
             binfo = BatchInfo('adaptive', status, None, counters, 0.0, 0.0, xs, ys, intern_p,
                               return_on_error, timings=_tdict(timings), method=method, iv=iv)
+            binfo.d2h_bytes = sum(r.nbytes + o.nbytes for _lo, r, o in pieces) + status.nbytes + counters.nbytes
         else:
             if intern_x.shape[0] > 1 and intern_x.strides[0] == 0:
                 # one broadcast row (core.to_arrays): ship it once (options.xout_shared)
@@ -723,3 +795,31 @@ class _Ragged:
         if self.kind == 0:
             return self.xyout[i, :self.nrows[i], 0]
         return self.xyout[i, :self.nrows[i], 1:]
+
+
+class _RaggedPieces:
+    """ N ragged arrays backed by compacted pieces ``(first_system, rows[total, 1 + ny], offsets[m + 1])``. """
+
+    def __init__(self, pieces, n, kind):
+        self.pieces, self.n, self.kind = pieces, n, kind
+        self.starts = np.array([p[0] for p in pieces], dtype=np.int64)
+
+    def __len__(self):
+        return self.n
+
+    def nrows(self):
+        """ rows per system, [N] """
+        out = np.empty(self.n, dtype=np.int64)
+        for lo, _rows, off in self.pieces:
+            out[lo:lo + off.size - 1] = np.diff(off)
+        return out
+
+    def __getitem__(self, i):
+        if i < 0:
+            i += self.n
+        if not 0 <= i < self.n:
+            raise IndexError(i)
+        k = int(np.searchsorted(self.starts, i, side='right')) - 1
+        lo, rows, off = self.pieces[k]
+        a, b = int(off[i - lo]), int(off[i - lo + 1])
+        return rows[a:b, 0] if self.kind == 0 else rows[a:b, 1:]

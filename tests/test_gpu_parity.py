@@ -883,3 +883,69 @@ def test_matrix_free_newton_krylov_bdf_on_robertson(cuda_device):
     assert ratio_o <= 1.0
     with pytest.raises((RuntimeError, ValueError), match='jtimes'):
         systems.robertson().integrate(xout, y0[:2], k[:2], linear_solver='gmres', with_jtimes=True, **kw)
+
+
+# ---- adaptive mode: compacted output, bounded device scratch, restart of the unfinished subset ----------
+def test_adaptive_output_is_compacted_on_the_device(cuda_device):
+    """ C1 as BASELINE states it (van der Pol, 1e4 initial conditions, adaptive mode, nsteps = 1000): only the rows that
+    were written cross PCIe (round 1 shipped the whole [N, nsteps + 1, 1 + ny] buffer: 240 MB for ~40 MB of rows), and
+    they are the rows of the bounded-buffer call bit for bit - also when the batch does not fit the device scratch in
+    one piece """
+    vd = systems.vdp()
+    mod = vd._native.mod
+    b = systems.batch_vdp(n=10000)
+    x = np.tile([0.0, 10.0], (10000, 1))
+    kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=b['nsteps'], method='dopri5')
+    res = vd.integrate(x, b['y0'], b['params'], **kw)
+    assert (res.info.status == 0).all()
+    nrows = res.info.xout.nrows()
+    rowbytes = 3*8
+    assert res.info.d2h_bytes <= nrows.sum()*rowbytes + 10000*(8 + 4 + 6*4) + 64
+    assert res.info.d2h_bytes < 0.35*10000*1001*rowbytes
+    xy, nr, st, cn, _t = mod.integrate_adaptive_arrays(b['y0'], x[:, 0], x[:, 1], full_params(b['y0'], b['params']),
+                                                       b['atol'], b['rtol'], mxsteps=b['nsteps'], method='dopri5')
+    assert np.array_equal(nr, nrows) and np.array_equal(cn, res.info.counters)
+    for i in (0, 1, 4999, 9999):
+        assert np.array_equal(res[i].xout, xy[i, :nr[i], 0]) and np.array_equal(res[i].yout, xy[i, :nr[i], 1:])
+        assert res[i].xout[-1] == 10.0 and res[i].info['n_steps'] >= nr[i] - 1
+    # scratch limit: 10000 systems x 1001 rows x 24 B = 240 MB -> pieces of <= 1747 systems
+    old = mod.adaptive_scratch_bytes
+    try:
+        mod.adaptive_scratch_bytes = 42 << 20
+        res2 = vd.integrate(x, b['y0'], b['params'], **kw)
+    finally:
+        mod.adaptive_scratch_bytes = old
+    assert len(res2.info.xout.pieces) == 6
+    for i in (0, 1747, 1748, 5000, 9999):
+        assert np.array_equal(res[i].xout, res2[i].xout) and np.array_equal(res[i].yout, res2[i].yout)
+    assert np.array_equal(res.info.counters, res2.info.counters)
+
+
+def test_auto_switch_restarts_only_what_did_not_finish(cuda_device):
+    """ ``integrate_auto_switch`` (pyodesys/core.py:865-908): the second formulation sees the unfinished systems only """
+    from pyodesys_b200 import integrate_chained
+    rtol, atol = 1e-10, 1e-10
+    tsys_, osys = tsys.loglog_decay4(), tsys.lin_decay4()
+    n = 12
+    ks = np.array([[7e13, 3, 2] if i % 4 == 0 else [7.0, 3, 2] for i in range(n)])  # every fourth one is very stiff
+    y0s = np.tile([1.0, 3.0, 2.0, 5.0], (n, 1))
+    seen = []
+
+    class Spy:
+        def __init__(self, inner):
+            self.inner = inner
+
+        def __getattr__(self, name):
+            return getattr(self.inner, name)
+
+        def integrate(self, x, y0, params, **kw):
+            seen.append(np.atleast_2d(y0).shape[0])
+            return self.inner.integrate(x, y0, params, **kw)
+
+    comb = integrate_chained([Spy(tsys_), Spy(osys)], {'nsteps': [60, 5000], 'return_on_error': [True, False]},
+                             [(1e-16, 7)]*n, y0s, ks, atol=atol, rtol=rtol, first_step=1e-14)
+    assert seen[0] == n and len(seen) == 2 and 0 < seen[1] < n
+    for i, res in enumerate(comb):
+        ref = bateman_full(y0s[i], list(ks[i]) + [0], res.xout - res.xout[0])
+        assert res.info['success'] and abs(res.xout[-1] - 7) < 1e-12 and np.all(np.diff(res.xout) >= 0)
+        assert np.allclose(res.yout, ref, rtol=rtol*1000, atol=atol*1000)
