@@ -224,6 +224,8 @@ class CudaModule:
         lib.pyodesys_cuda_device_pci_bus_id.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
         lib.pyodesys_cuda_device_count.restype = ctypes.c_int
         self.pinned = PinnedPool(lib)
+        self._lane_locks = {}  # (device, ctx_lane) -> lock: a compacting call and its fetch form one transaction
+        self._lane_locks_guard = threading.Lock()
         self.nparams = int(self.query('nparams'))
         self.ny = int(self.query('ny'))
         self.nroots = max(0, int(self.query('nroots')))
@@ -451,21 +453,33 @@ class CudaModule:
                 opts.root_indices = root_ptrs[1] + lo*mr*4
                 opts.nroots_found = root_ptrs[2] + lo*4
             sl = slice(lo, hi)
-            rc = self.lib.pyodesys_cuda_integrate_adaptive_compact(
-                device, m, _ptr(y0[sl]), _ptr(x0[sl]), _ptr(xend[sl]), _ptr(params[sl]), _ptr(atol), atol.size,
-                float(rtol), _ptr(None if dx0 is None else dx0[sl]), _ptr(None if dx_min is None else dx_min[sl]),
-                _ptr(None if dx_max is None else dx_max[sl]), int(mxsteps), mid, int(autorestart),
-                int(return_on_error), int(max_rows), offsets.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
-                _ptr(status[sl], _i32), ctypes.cast(ctypes.c_void_p(counters.ctypes.data + lo*4), _i32), _ptr(t1),
-                ctypes.byref(opts))
-            self._check(rc)
-            total = int(offsets[m])
-            rows = self.pinned.empty((total, 1 + self.ny), np.float64)
-            self._check(self.lib.pyodesys_cuda_fetch_compact_rows(device, int(opts.ctx_lane), _ptr(rows), total))
+            with self._lane_locks_guard:
+                lane_lock = self._lane_locks.setdefault((int(device), int(opts.ctx_lane)), threading.Lock())
+            lane_lock.acquire()
+            try:
+                rc = self._compact_call(device, m, y0, x0, xend, params, atol, rtol, dx0, dx_min, dx_max, mxsteps, mid,
+                                        autorestart, return_on_error, max_rows, offsets, status, counters, lo, sl, t1,
+                                        opts)
+                self._check(rc)
+                total = int(offsets[m])
+                rows = self.pinned.empty((total, 1 + self.ny), np.float64)
+                self._check(self.lib.pyodesys_cuda_fetch_compact_rows(device, int(opts.ctx_lane), _ptr(rows), total))
+            finally:
+                lane_lock.release()
             pieces.append((lo, rows, offsets))
             timings += t1
         _check_nan_y0(y0, status)
         return pieces, status, counters, timings
+
+    def _compact_call(self, device, m, y0, x0, xend, params, atol, rtol, dx0, dx_min, dx_max, mxsteps, mid,
+                      autorestart, return_on_error, max_rows, offsets, status, counters, lo, sl, t1, opts):
+        return self.lib.pyodesys_cuda_integrate_adaptive_compact(
+            device, m, _ptr(y0[sl]), _ptr(x0[sl]), _ptr(xend[sl]), _ptr(params[sl]), _ptr(atol), atol.size,
+            float(rtol), _ptr(None if dx0 is None else dx0[sl]), _ptr(None if dx_min is None else dx_min[sl]),
+            _ptr(None if dx_max is None else dx_max[sl]), int(mxsteps), mid, int(autorestart),
+            int(return_on_error), int(max_rows), offsets.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+            _ptr(status[sl], _i32), ctypes.cast(ctypes.c_void_p(counters.ctypes.data + lo*4), _i32), _ptr(t1),
+            ctypes.byref(opts))
 
     def integrate_predefined_device(self, n, nt, y0, xout, params, atol, rtol, yout, nreached, status,
                                     counters=None, dx0=None, dx_min=None, dx_max=None, mxsteps=0,

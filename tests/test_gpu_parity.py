@@ -901,7 +901,7 @@ def test_adaptive_output_is_compacted_on_the_device(cuda_device):
     nrows = res.info.xout.nrows()
     rowbytes = 3*8
     assert res.info.d2h_bytes <= nrows.sum()*rowbytes + 10000*(8 + 4 + 6*4) + 64
-    assert res.info.d2h_bytes < 0.35*10000*1001*rowbytes
+    assert res.info.d2h_bytes < 0.5*10000*1001*rowbytes  # the bounded buffers of round 1: 240 MB
     xy, nr, st, cn, _t = mod.integrate_adaptive_arrays(b['y0'], x[:, 0], x[:, 1], full_params(b['y0'], b['params']),
                                                        b['atol'], b['rtol'], mxsteps=b['nsteps'], method='dopri5')
     assert np.array_equal(nr, nrows) and np.array_equal(cn, res.info.counters)
@@ -927,8 +927,11 @@ def test_auto_switch_restarts_only_what_did_not_finish(cuda_device):
     rtol, atol = 1e-10, 1e-10
     tsys_, osys = tsys.loglog_decay4(), tsys.lin_decay4()
     n = 12
-    ks = np.array([[7e13, 3, 2] if i % 4 == 0 else [7.0, 3, 2] for i in range(n)])  # every fourth one is very stiff
+    ks = np.tile([7e13, 3, 2], (n, 1))
     y0s = np.tile([1.0, 3.0, 2.0, 5.0], (n, 1))
+    # every fourth system has the full span (needs far more than the 30 steps of the first formulation), the others
+    # a span they finish well inside it
+    spans = [(1e-16, 7.0) if i % 4 == 0 else (1e-16, 1e-13) for i in range(n)]
     seen = []
 
     class Spy:
@@ -942,10 +945,10 @@ def test_auto_switch_restarts_only_what_did_not_finish(cuda_device):
             seen.append(np.atleast_2d(y0).shape[0])
             return self.inner.integrate(x, y0, params, **kw)
 
-    comb = integrate_chained([Spy(tsys_), Spy(osys)], {'nsteps': [60, 5000], 'return_on_error': [True, False]},
-                             [(1e-16, 7)]*n, y0s, ks, atol=atol, rtol=rtol, first_step=1e-14)
-    assert seen[0] == n and len(seen) == 2 and 0 < seen[1] < n
+    comb = integrate_chained([Spy(tsys_), Spy(osys)], {'nsteps': [30, 5000], 'return_on_error': [True, False]},
+                             spans, y0s, ks, atol=atol, rtol=rtol, first_step=1e-14)
+    assert seen == [n, n//4], seen
     for i, res in enumerate(comb):
         ref = bateman_full(y0s[i], list(ks[i]) + [0], res.xout - res.xout[0])
-        assert res.info['success'] and abs(res.xout[-1] - 7) < 1e-12 and np.all(np.diff(res.xout) >= 0)
+        assert res.info['success'] and abs(res.xout[-1]/spans[i][1] - 1) < 1e-12 and np.all(np.diff(res.xout) >= 0)
         assert np.allclose(res.yout, ref, rtol=rtol*1000, atol=atol*1000)
