@@ -52,7 +52,7 @@ template <int S> struct SView {  // array-like view with a compile-time stride: 
 
 // Shared memory of one block (doubles).  "[i][system]" arrays have the odd pitch NSYSP: the evaluator (lane = system)
 // reads consecutive words, the lanes of a group (lane = row i) hit distinct banks.
-template <int G> struct CoopLayout {
+template <int G, int EXTRA = 0> struct CoopLayout {
     static constexpr int R = (NY + G - 1) / G;
     static constexpr int NSYS = kCoopBlock / G;    // systems per block
     static constexpr int NSYSP = NSYS | 1;
@@ -69,8 +69,9 @@ template <int G> struct CoopLayout {
     static constexpr int oJ = oDF + (ODESYS_AUTONOMOUS ? 0 : NY * NSYSP);  // Jacobian [(i * NYP + j)][system]
     static constexpr int NYE = NY + (NY & 1);                        // vectors that are moved 16 bytes at a time
     static constexpr int oScr = (oJ + NY * NYP * NSYSP + 1) & ~1;    // per system: two staging vectors [NYE] (16-byte aligned)
-    static constexpr int oInt = oScr + 2 * NYE * NSYS;               // ints: status[NSYS], fresh[NSYS]
-    static constexpr int kDoubles = oInt + NSYS;
+    static constexpr int oInt = oScr + 2 * NYE * NSYS;               // ints: status, fresh, request [NSYS] each
+    static constexpr int oExtra = oInt + 2 * NSYS;                   // EXTRA doubles per system (stepper state)
+    static constexpr int kDoubles = oExtra + EXTRA * NSYS;
     typedef odesys_anyode::OdeSysT<SView<NSYS>> ESys;
 };
 
@@ -138,8 +139,13 @@ template <int G> __device__ __noinline__ void coop_eval_jac(int e) {
     ist[e] |= st;
 }
 
+__device__ __forceinline__ double *c_smem_base() {
+    extern __shared__ double c_smem[];
+    return c_smem;
+}
 // executed by every thread of the block between two block barriers; the evaluator role rotates over the warps
-template <int G, bool JAC> __device__ __forceinline__ long long coop_evaluate(int evalno, int error_outside_bounds) {
+// (JAC: 0 right-hand side only, 1 + Jacobian, 2 + Jacobian for the systems whose request flag is set)
+template <int G, int JAC> __device__ __forceinline__ long long coop_evaluate(int evalno, int error_outside_bounds) {
     typedef CoopLayout<G> L;
     __syncthreads();  // staged states (Y, X) are complete
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -151,7 +157,8 @@ template <int G, bool JAC> __device__ __forceinline__ long long coop_evaluate(in
 #endif
     if (rel < L::NE && e < L::NSYS) {
         coop_eval_rhs<G>(e, error_outside_bounds);
-        if (JAC) coop_eval_jac<G>(e);
+        if (JAC == 1 || (JAC == 2 && reinterpret_cast<const int *>(c_smem_base() + L::oInt)[2 * L::NSYS + e]))
+            coop_eval_jac<G>(e);
 #ifdef PYODESYS_COOP_PROFILE
         body = clock64() - t_body;
 #endif
@@ -181,13 +188,17 @@ template <int G> struct Coop {
 #endif
 
     // stage the distributed vector yv, evaluate, bring back the rows this lane owns; returns the callback status
-    template <bool JAC>
-    __device__ __forceinline__ int eval(const Grp<G> &g, const KernelArgs &a, double x, const double *yv, double *f) {
+    template <int JAC>
+    __device__ __forceinline__ int eval(const Grp<G> &g, const KernelArgs &a, double x, const double *yv, double *f,
+                                        bool request = false) {
         extern __shared__ double c_smem[];
 #pragma unroll
         for (int r = 0; r < R; ++r)
             if (g.owns(r)) c_smem[L::oY + (r * G + g.gl) * L::NSYSP + sysl] = yv[r];
-        if (g.gl == 0) c_smem[L::oX + sysl] = x;
+        if (g.gl == 0) {
+            c_smem[L::oX + sysl] = x;
+            if (JAC == 2) reinterpret_cast<int *>(c_smem + L::oInt)[2 * L::NSYS + sysl] = request ? 1 : 0;
+        }
 #ifdef PYODESYS_COOP_PROFILE
         const long long t_ev = clock64();
 #endif
@@ -407,12 +418,23 @@ template <int G> struct CoopRos4 {
         err_old = 1.0f;
     }
 
+    static constexpr bool kAlwaysInit = false;  // init() only chooses a starting step
+    static constexpr int kExtraDoubles = 0;
     // Hairer's starting step (initial_step in integrators.cuh); executed by every thread of the block (two
     // evaluation slots), the result is used by the groups that asked for it
+    __device__ __forceinline__ double init(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t0, const double *y,
+                                           double span, bool want, bool have_h, int &nfev, int &njev) {
+        AnyODE::ignore(njev);
+        AnyODE::ignore(have_h);
+        int used = 0;
+        const double hs = auto_step(c, g, a, t0, y, span, used);
+        if (want) nfev += used;
+        return hs;
+    }
     __device__ __forceinline__ double auto_step(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t0,
                                                 const double *y, double span, int &nfev) {
         double f0[R], y1[R], f1[R];
-        c.template eval<false>(g, a, t0, y, f0);
+        c.template eval<0>(g, a, t0, y, f0);
         double d0 = 0.0, d1 = 0.0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -429,7 +451,7 @@ template <int G> struct CoopRos4 {
         const double dir = span >= 0 ? 1.0 : -1.0;
 #pragma unroll
         for (int r = 0; r < R; ++r) y1[r] = fma(dir * h0, f0[r], y[r]);
-        const int st = c.template eval<false>(g, a, t0 + dir * h0, y1, f1);
+        const int st = c.template eval<0>(g, a, t0 + dir * h0, y1, f1);
         nfev += 2;
         double d2 = 0.0;
 #pragma unroll
@@ -446,12 +468,17 @@ template <int G> struct CoopRos4 {
     }
 
     __device__ __forceinline__ int attempt(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t, const double *y,
-                                           double h, double *ynew, double &err, Counters &cnt) {
+                                           double h, double *ynew, double &err, Counters &cnt, int &nfev, int &njev,
+                                           bool live) {
         extern __shared__ double c_smem[];
+        if (live) {
+            nfev += 6;
+            njev += 1;
+        }
         double W[R][NY], dfdt[R], f[R], tmp[R], b[R];
         int ord[R];
         bool identity;
-        int bad = c.template eval<true>(g, a, t, y, f);
+        int bad = c.template eval<1>(g, a, t, y, f);
         const double ih = fast_rcp<2>(h);
         const double diag = 4.0 * ih;  // 1/gamma = 4
         // W = I/(gamma h) - J: the rows this lane owns, from the Jacobian the evaluator left in shared memory
@@ -486,7 +513,7 @@ template <int G> struct CoopRos4 {
             g1[r] = b[r];
             tmp[r] = fma(RC(A21), b[r], y[r]);
         }
-        bad |= c.template eval<false>(g, a, fma(RC(C2X), h, t), tmp, f);
+        bad |= c.template eval<0>(g, a, fma(RC(C2X), h, t), tmp, f);
         const double c21 = RC(C21) * ih;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -499,7 +526,7 @@ template <int G> struct CoopRos4 {
             g2[r] = b[r];
             tmp[r] = fma(RC(A32), b[r], fma(RC(A31), g1[r], y[r]));
         }
-        bad |= c.template eval<false>(g, a, fma(RC(C3X), h, t), tmp, f);
+        bad |= c.template eval<0>(g, a, fma(RC(C3X), h, t), tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             b[r] = fma(ih, fma(RC(C32), g2[r], RC(C31) * g1[r]), f[r]);
@@ -511,7 +538,7 @@ template <int G> struct CoopRos4 {
             g3[r] = b[r];
             tmp[r] = fma(RC(A43), b[r], fma(RC(A42), g2[r], fma(RC(A41), g1[r], y[r])));
         }
-        bad |= c.template eval<false>(g, a, fma(RC(C4X), h, t), tmp, f);
+        bad |= c.template eval<0>(g, a, fma(RC(C4X), h, t), tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             b[r] = fma(ih, fma(RC(C43), g3[r], fma(RC(C42), g2[r], RC(C41) * g1[r])), f[r]);
@@ -524,7 +551,7 @@ template <int G> struct CoopRos4 {
             tmp[r] = fma(RC(A54), b[r], fma(RC(A53), g3[r], fma(RC(A52), g2[r],
                                                                           fma(RC(A51), g1[r], y[r]))));
         }
-        bad |= c.template eval<false>(g, a, t + h, tmp, f);
+        bad |= c.template eval<0>(g, a, t + h, tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r)
             b[r] = fma(ih, fma(RC(C54), g4[r], fma(RC(C53), g3[r],
@@ -535,7 +562,7 @@ template <int G> struct CoopRos4 {
             g5[r] = b[r];
             tmp[r] += b[r];
         }
-        bad |= c.template eval<false>(g, a, t + h, tmp, f);
+        bad |= c.template eval<0>(g, a, t + h, tmp, f);
 #pragma unroll
         for (int r = 0; r < R; ++r)
             b[r] = fma(ih, fma(RC(C65), g5[r], fma(RC(C64), g4[r], fma(RC(C63), g3[r],
@@ -559,7 +586,7 @@ template <int G> struct CoopRos4 {
     }
 
     // rosenbrock4_controller::try_step (same rule as GroupRos4::control)
-    __device__ __forceinline__ bool control(double err, double &hnext, double h) {
+    __device__ __forceinline__ bool control(const Coop<G> &, const Grp<G> &, double err, double &hnext, double h) {
         constexpr float isafe = 1.0f / 0.9f, fac1 = 5.0f, fac2 = 1.0f / 6.0f;
         const float ef = (float)fmin(fmax(err, 1e-30), 1e30);
         const float lg = __log2f(ef);
@@ -585,8 +612,10 @@ template <int G> struct CoopRos4 {
         return false;
     }
 
-    __device__ __forceinline__ void dense(const Coop<G> &c, const Grp<G> &g, double theta, const double *yold,
+    __device__ __forceinline__ void dense(const Coop<G> &c, const Grp<G> &g, double theta, double, const double *yold,
                                           const double *ynew, double *out) {
+        AnyODE::ignore(c);
+        AnyODE::ignore(g);
         const double s1 = 1.0 - theta;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -604,9 +633,8 @@ template <int G> struct CoopRos4 {
 // loop = one Rosenbrock step attempt of every system of the block (lock-step), preceded - when some group just
 // loaded a system without a given first step - by the two evaluations of the starting-step heuristic.
 // ----------------------------------------------------------------------------------------------
-template <int G, int MODE>
-__global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros4_kernel(const KernelArgs a) {
-    typedef CoopLayout<G> L;
+template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel_body(const KernelArgs &a) {
+    typedef CoopLayout<G, St::kExtraDoubles> L;
     constexpr int R = L::R;
     extern __shared__ double c_smem[];
     const int lane = threadIdx.x & 31u;
@@ -624,16 +652,17 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
     g.prow = c_smem + L::oScr + (size_t)c.sysl * 2 * L::NYE;
     g.ys = g.prow + L::NYE;
     int *ist = reinterpret_cast<int *>(c_smem + L::oInt);
-    if (threadIdx.x < 2 * L::NSYS) ist[threadIdx.x] = 0;
+    for (int k = threadIdx.x; k < 4 * L::NSYS; k += kCoopBlock) ist[k] = 0;
     for (int k = threadIdx.x; k < L::oScr - L::oP; k += kCoopBlock) c_smem[L::oP + k] = 0.0;  // finite garbage for idle slots
     __syncthreads();
 
     const int64_t ngroups = (int64_t)gridDim.x * L::NSYS;
     int64_t s = (int64_t)blockIdx.x * L::NSYS + c.sysl - ngroups;  // static schedule cursor
 
-    CoopRos4<G> st;
+    St st;
     st.begin();
     double y[R], t = 0, h = 1.0, tend = 0, dir = 1, hmin = 0, hmax = INFINITY;
+    bool have_h = false;
     int64_t steps_left = 0;
     int k_out = 0, restarts = 0, nfail = 0, nfev = 0, njev = 0;
     Counters cnt = {0, 0, 0, 0};
@@ -656,6 +685,7 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
                     steps_left = a.mxsteps;
                     st.begin();
                     need_h = true;
+                    have_h = false;
                 } else {
                     status = ST_MXSTEPS;
                 }
@@ -742,8 +772,9 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
                 steps_left = a.mxsteps > 0 ? a.mxsteps : INT64_MAX;
                 st.begin();
                 h = a.dx0 ? a.dx0[s] : 0.0;
-                need_h = (h == 0.0);
-                if (!need_h) h = fabs(h) * dir;
+                have_h = (h != 0.0);
+                need_h = St::kAlwaysInit || !have_h;
+                if (have_h) h = fabs(h) * dir;
                 active = true;
                 bool fin = true;
 #pragma unroll
@@ -774,9 +805,9 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
 
         // ---- starting step size where none was given: two evaluation slots, taken by the whole block ----------------
         if (__syncthreads_or(live && need_h)) {
-            const double hs = st.auto_step(c, g, a, t, y, live ? tend - t : 0.0, nfev);
-            if (live && need_h) h = hs;
-            else if (active) nfev -= 2;  // slots this system did not use
+            const bool want = live && need_h;
+            const double hs = st.init(c, g, a, t, y, live ? tend - t : 0.0, want, have_h, nfev, njev);
+            if (want && !have_h) h = hs;
             need_h = false;
         }
 
@@ -794,12 +825,10 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
         }
         double ynew[R], err = 0.0, hnext = hh;
         Counters scratch = cnt;
-        const int bad = st.attempt(c, g, a, t, y, hh, ynew, err, live ? cnt : scratch);
+        const int bad = st.attempt(c, g, a, t, y, hh, ynew, err, live ? cnt : scratch, nfev, njev, live);
         COOP_ACC(8, t_att);
         if (!live) continue;
         COOP_T0(t_post);
-        nfev += 6;
-        njev += 1;
         cnt.nsteps += 1;
         steps_left -= 1;
         bool ok;
@@ -809,9 +838,9 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
             nfail += 1;
             if (nfail >= 12) nfail = 1 << 20;
             double ignored;
-            st.control(2.0, ignored, hh);
+            st.control(c, g, 2.0, ignored, hh);
         } else {
-            ok = st.control(err, hnext, hh);
+            ok = st.control(c, g, err, hnext, hh);
             if (ok) nfail = 0;
         }
         if (!ok) {
@@ -831,7 +860,7 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
 #pragma unroll
                         for (int r = 0; r < R; ++r) yo[r] = ynew[r];
                     } else {
-                        st.dense(c, g, (xk - t) / hh, y, ynew, yo);
+                        st.dense(c, g, (xk - t) / hh, hh, y, ynew, yo);
                     }
 #pragma unroll
                     for (int r = 0; r < R; ++r)
@@ -874,6 +903,11 @@ __global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros
         for (int k = 6; k < 10; ++k) atomicAdd(out + k, (unsigned long long)c.prof[k]);
     }
 #endif
+}
+
+template <int G, int MODE>
+__global__ void __launch_bounds__(kCoopBlock, PYODESYS_COOP_MIN_BLOCKS) coop_ros4_kernel(const KernelArgs a) {
+    coop_kernel_body<CoopRos4<G>, G, MODE>(a);
 }
 
 #endif  // ODESYS_HAS_JAC

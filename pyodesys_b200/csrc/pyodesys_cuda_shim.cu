@@ -28,6 +28,7 @@
 #define ODESYS_COOP_KERNEL (ODESYS_GROUP_KERNEL && ODESYS_NY >= 9)
 #if ODESYS_COOP_KERNEL
 #include "coop_integrators.cuh"
+#include "coop_bdf.cuh"
 #endif
 #include "pyodesys_cuda.h"
 
@@ -192,6 +193,29 @@ template <int MODE> int launch_coop(DevCtx &c, const KernelArgs &a, cudaStream_t
 }
 #endif
 
+#if ODESYS_COOP_KERNEL
+constexpr int kCoopBdfG = PYODESYS_COOP_BDF_G;
+template <int MODE> int launch_coop_bdf(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
+    auto kern = coop_bdf_kernel<kCoopBdfG, MODE>;
+    typedef CoopBdf<kCoopBdfG>::L L;
+    const size_t smem = (size_t)L::kDoubles * sizeof(double);
+    if (smem > 227 * 1024) return fail("ny = %d needs %zu bytes of shared memory per block in the cooperative BDF kernel", NY, smem);
+    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kCoopBlock, smem));
+    if (occ < 1) occ = 1;
+    if (blocks_per_sm > 0 && blocks_per_sm < occ) occ = blocks_per_sm;
+    int64_t grid = (int64_t)c.sm_count * occ;
+    const int64_t need = (a.n + L::NSYS - 1) / L::NSYS;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kCoopBlock, smem, stream>>>(a);
+    g_launches.fetch_add(1);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+#endif
+
 #if ODESYS_SMEM_KERNEL
 // one system per thread, W / vectors / parameters in shared memory, rolled loops (one warp per block)
 template <int MODE> int launch_smem(DevCtx &c, const KernelArgs &a, cudaStream_t stream, int blocks_per_sm) {
@@ -274,6 +298,17 @@ template <int MODE> int dispatch(DevCtx &c, const KernelArgs &a, int method, cud
         if (a.linear_solver == PYODESYS_CUDA_LINSOL_GMRES) return launch<M_BDF_KRYLOV, MODE>(c, a, stream, bps);
 #endif
         return launch<M_BDF, MODE>(c, a, stream, bps);
+#elif ODESYS_COOP_KERNEL
+    case PYODESYS_CUDA_BDF: {
+        // ny > 8: the block-cooperative BDF (lane groups for the linear algebra, one system per lane for f and J)
+        const bool extras = opt && ((ODESYS_NROOTS > 0 && opt->max_roots > 0) || opt->max_invariant_violation != 0.0 ||
+                                    (ODESYS_HAS_DX_MAX && opt->get_dx_max_factor > 0.0) ||
+                                    opt->linear_solver != PYODESYS_CUDA_LINSOL_DENSE);
+        if (extras || ODESYS_HAS_FIRST_STEP)
+            return fail("method bdf for ny > 8 runs on the block-cooperative kernel, which carries no event functions / "
+                        "invariant guard / get_dx0 / get_dx_max / matrix-free solver");
+        return launch_coop_bdf<MODE>(c, a, stream, bps);
+    }
 #elif ODESYS_HAS_JAC
     case PYODESYS_CUDA_BDF: return fail("the BDF kernel keeps its difference table in registers and is limited to ny <= 8; use rosenbrock4");
 #else
@@ -622,7 +657,7 @@ int64_t pyodesys_cuda_query(const char *key) {
         {"coop_group_size", kCoopG}, {"coop_systems_per_block", CoopLayout<kCoopG>::NSYS},
         {"coop_smem_bytes", (int64_t)CoopLayout<kCoopG>::kDoubles * 8},
 #endif
-        {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF},
+        {"has_smem_kernel", ODESYS_SMEM_KERNEL}, {"has_bdf", ODESYS_THREAD_BDF || ODESYS_COOP_KERNEL},
 #if ODESYS_SMEM_KERNEL
         {"smem_doubles_per_thread", kSmemDoublesPerThread},
 #endif

@@ -85,7 +85,7 @@ def cache_dir():
 
 def _csrc_digest():
     h = hashlib.sha256()
-    for fn in ('integrators.cuh', 'bdf_integrator.cuh', 'group_integrators.cuh', 'coop_integrators.cuh', 'smem_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
+    for fn in ('integrators.cuh', 'bdf_integrator.cuh', 'group_integrators.cuh', 'coop_integrators.cuh', 'coop_bdf.cuh', 'smem_integrators.cuh', 'pyodesys_cuda_shim.cu', 'odesys_prelude.h'):
         path = os.path.join(_csrc, fn)
         if os.path.exists(path):
             with open(path, 'rb') as fh:
