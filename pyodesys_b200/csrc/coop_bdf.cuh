@@ -271,10 +271,12 @@ template <int G> struct CoopBdf {
             // ---- simplified Newton iteration, one evaluation slot of the block per iteration -----------------------
             bool gdone = !live || converged || bad != 0;  // this group takes no further part in the iteration
             float nrm_old = -1.0f;
+            if (!converged) {  // (a group that converged in the first pass keeps its correction through the second)
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                d[r] = 0.0;
-                yk[r] = ypred[r];
+                for (int r = 0; r < R; ++r) {
+                    d[r] = 0.0;
+                    yk[r] = ypred[r];
+                }
             }
             for (int k = 0; k < cbdf::NEWTON_MAXITER; ++k) {
                 if (!__syncthreads_or(!gdone)) break;

@@ -378,7 +378,7 @@ template <int G> __device__ __forceinline__ void c_apply(const Grp<G> &g, const 
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < R; ++r)
-        if (g.owns(r)) g.prow[ord[r]] = b[r];
+        if (g.owns(r) && (unsigned)ord[r] < (unsigned)NY) g.prow[ord[r]] = b[r];  // (a group without a valid inverse takes part in the collective only)
     __syncwarp();
     double bs[NY], acc[R];
     lds_vec<NY>(g.prow, bs);
@@ -389,13 +389,15 @@ template <int G> __device__ __forceinline__ void c_apply(const Grp<G> &g, const 
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[r] = fma(a[r][m], bs[m], acc[r]);
     }
-    if (identity) {
+    // (warp vote: the groups of a warp may hold inverses from different eliminations - the BDF stepper keeps them
+    // across steps - and the permuting path below synchronises the whole warp)
+    if (__all_sync(FULL_MASK, identity)) {
 #pragma unroll
         for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? acc[r] : 0.0;
     } else {
 #pragma unroll
         for (int r = 0; r < R; ++r)
-            if (g.owns(r)) g.ys[ord[r]] = acc[r];
+            if (g.owns(r) && (unsigned)ord[r] < (unsigned)NY) g.ys[ord[r]] = acc[r];
         __syncwarp();
 #pragma unroll
         for (int r = 0; r < R; ++r) b[r] = g.owns(r) ? g.ys[r * G + g.gl] : 0.0;
@@ -670,7 +672,13 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
 #pragma unroll
     for (int r = 0; r < R; ++r) y[r] = 0.0;
 
+#ifdef PYODESYS_COOP_DEBUG_ITERS
+    long long dbg_iters = 0;
+#endif
     for (;;) {
+#ifdef PYODESYS_COOP_DEBUG_ITERS
+        if (++dbg_iters > PYODESYS_COOP_DEBUG_ITERS) break;  // debugging aid: tells a livelock from a deadlock
+#endif
         COOP_T0(t_top);
         // ---- (B) + (E): termination test of the running system, retire ----------------------------------------
         if (active) {
