@@ -184,6 +184,27 @@ int pyodesys_cuda_integrate_adaptive_compact(
 int pyodesys_cuda_fetch_compact_rows(int device, int ctx_lane, double *rows /* host [offsets[n], 1 + ny] */,
                                      int64_t nrows_total);
 
+/* Compaction of a device-resident adaptive result WITHOUT ANY ALLOCATION.  This entry point has no counterpart in
+ * the reference: it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the compaction stage of
+ * pyodesys_cuda_integrate_adaptive_compact - exclusive scan of nrows, then one warp per system packs its rows - on
+ * buffers the caller owns: input xyout_dev[n, max_rows_per_system, 1 + ny] and nrows_dev[n] exactly as
+ * pyodesys_cuda_integrate_adaptive leaves them with ptr_kind = 1; output offsets_dev[n + 1] (device) and
+ * rows_dev[rows_capacity, 1 + ny] (device).  Rows beyond rows_capacity are not written: offsets_dev[n] is the
+ * number of rows the result has, compare it with rows_capacity after synchronising (rows_capacity = 0 computes the
+ * offsets only; rows_dev may then be NULL).  All work is queued on ``stream`` (a cudaStream_t, NULL = the default
+ * stream) and the call returns without synchronising; it calls no cudaMalloc / cudaFree / allocating routine.
+ * The scratch of the scan (one partial sum per 2048 systems) is a static __device__ array of
+ * PYODESYS_CUDA_NOALLOC_MAX_TILES int64 = 64 KiB that every GPU which loads the library holds until exit, hence
+ * n <= PYODESYS_CUDA_NOALLOC_MAX_SYSTEMS per call (larger n: error -1 with a message that says so).  Every call on a
+ * device shares that array (its used part is cleared at the start of each call): calls that overlap on the GPU -
+ * different streams, several host threads - race; serialise them on one stream. */
+#define PYODESYS_CUDA_NOALLOC_MAX_TILES 8192
+#define PYODESYS_CUDA_NOALLOC_MAX_SYSTEMS (8192LL * 2048LL)
+int pyodesys_cuda_compact_rows_noalloc(int device, int64_t n, int64_t max_rows_per_system, const double *xyout_dev,
+                                       const int32_t *nrows_dev, int64_t *offsets_dev, double *rows_dev,
+                                       int64_t rows_capacity, void *stream);
+
 /* Verification hooks (host pointers): evaluate the generated OdeSys::rhs / dense_jac_rmaj
  * (odesys_anyode_template.cpp:147-204,246-293) for a batch, and run the in-register LU that
  * the Rosenbrock stepper uses (role of AnyODE::getrf_callback/getrs_callback,

@@ -631,6 +631,58 @@ __global__ void compact_rows(const double *xyout, const long long *offsets, int6
     }
 }
 
+
+// ---- compaction without any allocation (pyodesys_cuda_compact_rows_noalloc) -----------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  The scratch of the scan - one partial sum per tile of
+// kScanTile systems - lives in this file-scope array: kNoAllocMaxTiles * 8 bytes = 64 KiB that every GPU which
+// loads the library holds until exit.  In HOST code ``g_noalloc_tile_sums`` is only a stand-in for the symbol; the
+// device address is taken once per device with cudaGetSymbolAddress (noalloc_scratch below) and passed to the kernels.
+constexpr int kNoAllocMaxTiles = PYODESYS_CUDA_NOALLOC_MAX_TILES;
+constexpr int64_t kNoAllocMaxSystems = (int64_t)kNoAllocMaxTiles * kScanTile;  // 16 777 216
+static_assert(kNoAllocMaxSystems == PYODESYS_CUDA_NOALLOC_MAX_SYSTEMS, "header and scan tile size disagree");
+static __device__ __align__(256) long long g_noalloc_tile_sums[kNoAllocMaxTiles];
+
+// compact_rows with a bound: rows that would land beyond ``capacity`` rows of ``out`` are not written (the caller
+// sees offsets[n] > capacity and knows)
+__global__ void compact_rows_bounded(const double *xyout, const long long *offsets, int64_t n, int64_t max_rows,
+                                     int rowlen, double *out, long long capacity) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < n; s += nwarps) {
+        const long long o = offsets[s];
+        long long e = offsets[s + 1];
+        if (e > capacity) e = capacity;
+        const long long cnt = (e - o) * rowlen;
+        const double *src = xyout + s * max_rows * rowlen;
+        double *dst = out + o * rowlen;
+        for (long long i = lane; i < cnt; i += 32) dst[i] = src[i];
+    }
+}
+
+struct NoAllocDev {
+    long long *scratch = nullptr;  // device address of g_noalloc_tile_sums ON THIS DEVICE
+    int sm_count = 0;
+};
+NoAllocDev g_noalloc[kMaxDev];
+std::mutex g_noalloc_mtx;
+
+// device address of the scratch array on ``device`` (made current here); looked up once per device
+int noalloc_scratch(int device, NoAllocDev **out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mtx);
+    CU_CHECK(cudaSetDevice(device));
+    NoAllocDev &d = g_noalloc[device];
+    if (!d.scratch) {
+        long long *ptr = nullptr;
+        CU_CHECK(cudaGetSymbolAddress((void **)&ptr, g_noalloc_tile_sums));
+        if (!ptr) return fail("cudaGetSymbolAddress returned a null address for the scratch array on device %d", device);
+        CU_CHECK(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device));
+        d.scratch = ptr;
+    }
+    *out = &d;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1156,6 +1208,45 @@ int pyodesys_cuda_fetch_compact_rows(int device, int ctx_lane, double *rows, int
     CU_CHECK(cudaSetDevice(device));
     CU_CHECK(cudaMemcpyAsync(rows, c.buf[B_COMPACT], (size_t)nrows_total * (1 + NY) * 8, cudaMemcpyDeviceToHost, c.stream));
     CU_CHECK(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+
+// See include/pyodesys_cuda.h.  Everything is queued on ``stream``; nothing is allocated, nothing is synchronised.
+int pyodesys_cuda_compact_rows_noalloc(int device, int64_t n, int64_t max_rows, const double *xyout_dev,
+                                       const int32_t *nrows_dev, int64_t *offsets_dev, double *rows_dev,
+                                       int64_t rows_capacity, void *stream) {
+    if (device < 0 || device >= kMaxDev) return fail("invalid device %d", device);
+    if (n < 0 || max_rows < 1 || rows_capacity < 0) return fail("invalid sizes (n=%lld, max_rows=%lld, rows_capacity=%lld)", (long long)n, (long long)max_rows, (long long)rows_capacity);
+    if (n > kNoAllocMaxSystems)
+        return fail("pyodesys_cuda_compact_rows_noalloc handles at most %lld systems per call (static scratch of %d tile "
+                    "sums), got %lld: split the batch or use pyodesys_cuda_integrate_adaptive_compact",
+                    (long long)kNoAllocMaxSystems, kNoAllocMaxTiles, (long long)n);
+    if (!offsets_dev) return fail("offsets_dev must not be NULL");
+    if (n > 0 && (!xyout_dev || !nrows_dev)) return fail("xyout_dev/nrows_dev must not be NULL");
+    if (rows_capacity > 0 && !rows_dev) return fail("rows_dev is NULL with rows_capacity=%lld", (long long)rows_capacity);
+    NoAllocDev *d = nullptr;
+    if (noalloc_scratch(device, &d)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    long long *d_off = reinterpret_cast<long long *>(offsets_dev);
+    if (n == 0) {
+        CU_CHECK(cudaMemsetAsync(d_off, 0, 8, st));
+        return 0;
+    }
+    const int ntiles = (int)((n + kScanTile - 1) / kScanTile);
+    // the array keeps what the last call left: the part this call uses starts from zero
+    CU_CHECK(cudaMemsetAsync(d->scratch, 0, (size_t)ntiles * 8, st));
+    scan_tile_sums<<<ntiles, kScanBlock, 0, st>>>(nrows_dev, n, d->scratch);
+    scan_tiles<<<1, kScanBlock, 0, st>>>(d->scratch, ntiles);
+    scan_offsets<<<ntiles, kScanBlock, 0, st>>>(nrows_dev, n, d->scratch, d_off);
+    g_launches.fetch_add(3);
+    CU_CHECK(cudaGetLastError());
+    if (rows_capacity > 0) {
+        const int blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)d->sm_count * 8);
+        compact_rows_bounded<<<blocks, 256, 0, st>>>(xyout_dev, d_off, n, max_rows, 1 + NY, rows_dev,
+                                                    (long long)rows_capacity);
+        g_launches.fetch_add(1);
+        CU_CHECK(cudaGetLastError());
+    }
     return 0;
 }
 

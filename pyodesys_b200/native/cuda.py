@@ -223,6 +223,10 @@ class CudaModule:
         lib.pyodesys_cuda_device_pci_bus_id.restype = ctypes.c_int
         lib.pyodesys_cuda_device_pci_bus_id.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
         lib.pyodesys_cuda_device_count.restype = ctypes.c_int
+        lib.pyodesys_cuda_compact_rows_noalloc.restype = ctypes.c_int
+        lib.pyodesys_cuda_compact_rows_noalloc.argtypes = [
+            ctypes.c_int, ctypes.c_int64, ctypes.c_int64, _d, _i32, ctypes.POINTER(ctypes.c_int64), _d,
+            ctypes.c_int64, ctypes.c_void_p]
         self.pinned = PinnedPool(lib)
         self._lane_locks = {}  # (device, ctx_lane) -> lock: a compacting call and its fetch form one transaction
         self._lane_locks_guard = threading.Lock()
@@ -524,6 +528,16 @@ class CudaModule:
             ctypes.byref(opts))
         self._check(rc)
         return timings
+
+    def compact_rows_noalloc(self, n, max_rows, xyout, nrows, offsets, rows, rows_capacity, device=0, stream=None):
+        """ ``pyodesys_cuda_compact_rows_noalloc`` (include/pyodesys_cuda.h): compaction of a device-resident
+        adaptive result on caller-owned device buffers, scan scratch in a static device array - no allocation, no
+        synchronisation; at most ``PYODESYS_CUDA_NOALLOC_MAX_SYSTEMS`` systems per call.  Arguments are device
+        pointers as ints (``tensor.data_ptr()``). """
+        rc = self.lib.pyodesys_cuda_compact_rows_noalloc(
+            int(device), int(n), int(max_rows), _ptr(xyout), _ptr(nrows, _i32),
+            _ptr(offsets, ctypes.POINTER(ctypes.c_int64)), _ptr(rows), int(rows_capacity), stream)
+        self._check(rc)
 
     # -- reference-shaped entry points --------------------------------------------------------
     @staticmethod
