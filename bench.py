@@ -609,7 +609,12 @@ def sharded_arm(args, wl, dist, rank, world):
     in one pinned array).  strong: the configuration's batch (n systems in total) over N GPUs; weak: N * n systems. """
     import torch
     out = None
-    dist.barrier()
+    # The waiting ranks must not hold their GPU: an NCCL barrier is a spinning kernel, and two processes on one GPU
+    # are time-sliced - rank 0's kernels on device r would get half of it (measured: 2.2x slower chunks on device 1).
+    # Hence a CPU-side (gloo) barrier, after every rank has drained its own device.
+    torch.cuda.synchronize()
+    cpu_group = dist.new_group(backend='gloo')
+    dist.barrier(group=cpu_group)
     if rank == 0:
         os.sched_setaffinity(0, range(os.cpu_count() or 1))  # this arm drives every GPU: undo the per-rank binding
         devices = list(range(world))
@@ -622,10 +627,12 @@ def sharded_arm(args, wl, dist, rank, world):
             h_k = torch.from_numpy(bb['params']).pin_memory()
             res = None
             for _ in range(2):
+                res = None
                 res = wl.odesys.integrate(wl.x, h_y0.numpy(), h_k.numpy(), devices=devices, **kw)
             reps = 3
             t0 = time.perf_counter()
             for _ in range(reps):
+                res = None  # hand the page-locked result block back to the pool before the next call
                 res = wl.odesys.integrate(wl.x, h_y0.numpy(), h_k.numpy(), devices=devices, **kw)
                 float(res.yout[-1, -1, -1])
             dt = (time.perf_counter() - t0)/reps
@@ -636,6 +643,7 @@ def sharded_arm(args, wl, dist, rank, world):
                     r1 = wl.odesys.integrate(wl.x, h_y0.numpy(), h_k.numpy(), device=0, **kw)
                 t0 = time.perf_counter()
                 for _ in range(reps):
+                    r1 = None
                     r1 = wl.odesys.integrate(wl.x, h_y0.numpy(), h_k.numpy(), device=0, **kw)
                     float(r1.yout[-1, -1, -1])
                 one = (time.perf_counter() - t0)/reps
@@ -644,7 +652,8 @@ def sharded_arm(args, wl, dist, rank, world):
             sched = getattr(res.info, 'shard_stats', None)
             if sched:
                 out[label]["schedule"] = sched
-    dist.barrier()
+            res = None
+    dist.barrier(group=cpu_group)
     return out
 
 
