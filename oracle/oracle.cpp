@@ -499,8 +499,8 @@ struct BDF : StepperBase {
     double h_cur = 0, c_lu = 0, newton_tol = 0, safety = 0.9;
     // the tolerances arrive already calibrated (odesys_kappa, odesys_prelude.h)
     Settings cs;
-    int order = 1, n_equal = 0;
-    bool have_lu = false, jac_current = false, fresh = true, newton_failed = false;
+    int order = 1, n_equal = 0, n_attempt = 0;
+    bool have_lu = false, jac_current = false, fresh = true, newton_failed = false, refresh_jac = false;
     bool krylov = false;
     bool adaptive() const override { return true; }
 
@@ -522,6 +522,8 @@ struct BDF : StepperBase {
         newton_tol = std::max(10 * DBL_EPSILON / rtol, std::min(0.03, std::sqrt(rtol)));
         order = 1;
         n_equal = 0;
+        n_attempt = 0;
+        refresh_jac = false;
         have_lu = false;
         fresh = true;
         newton_failed = false;
@@ -568,6 +570,7 @@ struct BDF : StepperBase {
     }
     int attempt(Work &w, double t, const double *y, double h, double *ynew, double *err) override {
         (void)y;
+        n_attempt += 1;
         if (fresh) {
             for (int i = 0; i < NY; ++i) D[1][i] = h * f0[i];
             h_cur = h;
@@ -593,6 +596,15 @@ struct BDF : StepperBase {
         int n_iter = 0;
         newton_failed = false;
         if (krylov) jac_current = true;
+        if (refresh_jac) {  // a new order / step was selected: the iteration matrix is re-formed, with a new Jacobian
+            refresh_jac = false;
+            if (!krylov && !jac_current) {
+                double dfdt[NY];
+                if (w.sys.dense_jac_rmaj(tnew, ypred, nullptr, Jm, NY, dfdt)) return 1;
+                jac_current = true;
+                have_lu = false;
+            }
+        }
         while (!converged) {
             if (!krylov && (!have_lu || c != c_lu)) {
                 for (int r = 0; r < NY; ++r)
@@ -677,7 +689,7 @@ struct BDF : StepperBase {
         for (int j = order; j >= 0; --j)
             for (int i = 0; i < NY; ++i) D[j][i] += D[j + 1][i];
         *hnext = h;
-        if (n_equal < order + 1) return true;
+        if (n_equal < order + 1 || n_attempt % (order <= 2 ? ODESYS_BDF_EPOCH / 2 : ODESYS_BDF_EPOCH) != 0) return true;  // odesys_prelude.h
         double tmp[NY];
         double em = INFINITY, ep = INFINITY;
         if (order > 1) {
@@ -702,6 +714,7 @@ struct BDF : StepperBase {
         *hnext = h * std::min(10.0, safety * best);
         n_equal = 0;
         have_lu = false;
+        refresh_jac = ODESYS_BDF_REFRESH_JAC != 0;
         return true;
     }
     // Interpolating polynomial through the last order+1 solution values (Newton backward form).

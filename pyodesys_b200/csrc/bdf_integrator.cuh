@@ -141,6 +141,9 @@ template <bool KRYLOV> struct BdfStepper {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 1;
+    // systems are started on a grid of kEpoch loop iterations, so that the step attempts of the lanes of a warp are
+    // numbered alike and their order / step selections (odesys_prelude.h) coincide
+    static constexpr int kEpoch = ODESYS_BDF_EPOCH;
     static constexpr int ND = bdfc::MAXORD + 3;
     static constexpr int kSharedDoublesPerThread = ND * NY;
     double *Dsm;   // this thread's column of the difference table in shared memory
@@ -157,8 +160,8 @@ template <bool KRYLOV> struct BdfStepper {
     float iscale[NY];   // 1 / (atol_i + rtol |y_i|): the norms only steer Newton and the step size -> fp32
     double h_cur, c_lu, atol_[NY], rtol_;
     float newton_tol, safety;
-    int order, n_equal;
-    bool have_lu, jac_current, fresh, newton_failed;
+    int order, n_equal, n_attempt;
+    bool have_lu, jac_current, fresh, newton_failed, refresh_jac;
     static constexpr bool krylov = KRYLOV;  // Newton corrections by gmres_solve on OdeSys::jtimes: no Jacobian, no LU
 
     __device__ __forceinline__ double alpha(int k) const { return (1.0 - kBdfKappa[k]) * kBdfGamma[k]; }
@@ -193,6 +196,8 @@ template <bool KRYLOV> struct BdfStepper {
         newton_tol = (float)fmax(10.0 * DBL_EPSILON / rtol_, fmin(0.03, sqrt(rtol_)));
         order = 1;
         n_equal = 0;
+        n_attempt = 0;
+        refresh_jac = false;
         have_lu = false;
         fresh = true;
         newton_failed = false;
@@ -261,6 +266,7 @@ template <bool KRYLOV> struct BdfStepper {
     }
     __device__ __forceinline__ int attempt(Sys &sys, const KernelArgs &a, const Tol &, double t, const double *,
                                            double h, double *ynew, double &err, Counters &cnt) {
+        n_attempt += 1;
         if (fresh) {
 #pragma unroll
             for (int i = 0; i < NY; ++i) Dx(1, i) *= h;
@@ -298,6 +304,14 @@ template <bool KRYLOV> struct BdfStepper {
 #pragma unroll
         for (int i = 0; i < NY; ++i) ynew[i] = Dx(0, i);
         if (krylov) jac_current = true;  // J is applied at (tnew, ypred) by every product
+        if (refresh_jac) {  // a new order / step was selected: the iteration matrix is re-formed, with a new Jacobian
+            refresh_jac = false;
+            if (!krylov && !jac_current) {
+                if (eval_jac(sys, tnew, ypred)) return 1;
+                jac_current = true;
+                have_lu = false;
+            }
+        }
         for (int pass = 0; pass < 2 && !converged; ++pass) {
             if (!krylov && (!have_lu || c != c_lu)) {
 #pragma unroll
@@ -409,7 +423,8 @@ template <bool KRYLOV> struct BdfStepper {
             }
         }
         hnext = h;
-        if (n_equal < order + 1) return true;
+        // selection only on the grid of attempts (odesys_prelude.h; half the period while the order is low)
+        if (n_equal < order + 1 || n_attempt % (order <= 2 ? ODESYS_BDF_EPOCH / 2 : ODESYS_BDF_EPOCH) != 0) return true;
         // error estimates one order down / up: errconst_{k-1} D[k], errconst_{k+1} D[k+2]
         double vm[NY], vp[NY];
 #pragma unroll
@@ -453,6 +468,7 @@ template <bool KRYLOV> struct BdfStepper {
         hnext = h * (double)fminf(10.0f, safety * best);
         n_equal = 0;
         have_lu = false;
+        refresh_jac = ODESYS_BDF_REFRESH_JAC != 0;
         return true;
     }
     __device__ __forceinline__ void accepted(const double *) {}

@@ -38,6 +38,9 @@ template <int G> struct CoopBdf {
     static constexpr int R = L::R;
     static constexpr bool kAlwaysInit = true;  // init() evaluates f(t0, y0) and the first Jacobian
     static constexpr int kExtraDoubles = cbdf::ND * NY;
+    // systems start on a grid of kEpoch block iterations: the order / step selections of all systems of the block -
+    // rescaling, new Jacobian, new inverse - fall into the same iteration (odesys_prelude.h)
+    static constexpr int kEpoch = ODESYS_BDF_EPOCH;
 
     double W[R][NY];  // (I - c J)^-1 (c_invert layout)
     int ord[R];
@@ -46,8 +49,8 @@ template <int G> struct CoopBdf {
     float iscale[R];
     double h_cur, c_lu;
     float newton_tol, safety;
-    int order, n_equal;
-    bool have_lu, jac_current, fresh, newton_failed;
+    int order, n_equal, n_attempt;
+    bool have_lu, jac_current, fresh, newton_failed, refresh_jac;
 
     __device__ __forceinline__ double &Dx(const Coop<G> &c, const Grp<G> &g, int j, int r) const {
         extern __shared__ double c_smem[];
@@ -82,6 +85,8 @@ template <int G> struct CoopBdf {
     __device__ __forceinline__ void begin() {
         order = 1;
         n_equal = 0;
+        n_attempt = 0;
+        refresh_jac = false;
         have_lu = false;
         fresh = true;
         newton_failed = false;
@@ -193,6 +198,7 @@ template <int G> struct CoopBdf {
                                            double h, double *ynew, double &err, Counters &cnt, int &nfev, int &njev,
                                            bool live) {
         extern __shared__ double c_smem[];
+        if (live) n_attempt += 1;
         if (fresh) {
 #pragma unroll
             for (int r = 0; r < R; ++r)
@@ -229,6 +235,25 @@ template <int G> struct CoopBdf {
         int n_iter = 0, bad = 0;
         newton_failed = false;
         err = 2.0;
+        // ---- a new order / step was selected: new Jacobian at (tnew, ypred).  The slot also yields f(tnew, ypred),
+        // which is what the first Newton iteration needs.
+        bool have_f0 = false;
+        int st0 = 0;
+        double f0p[R];
+        {
+            const bool want_j = live && refresh_jac && !jac_current;
+            if (live) refresh_jac = false;
+            if (__syncthreads_or(want_j)) {
+                st0 = c.template eval<2>(g, a, tnew, ypred, f0p, want_j);
+                have_f0 = true;
+                if (want_j) {
+                    njev += 1;
+                    if (st0 != 0) bad = 1;
+                    jac_current = true;
+                    have_lu = false;
+                }
+            }
+        }
         for (int pass = 0; pass < 2; ++pass) {
             // ---- (I - c J)^-1 where c or J changed (warp vote: the inverse runs with full-warp shuffles) ----------
             const bool need_lu = live && !converged && !bad && (!have_lu || cc != c_lu);
@@ -280,7 +305,14 @@ template <int G> struct CoopBdf {
             }
             for (int k = 0; k < cbdf::NEWTON_MAXITER; ++k) {
                 if (!__syncthreads_or(!gdone)) break;
-                const int st = c.template eval<0>(g, a, tnew, yk, f);
+                int st;
+                if (k == 0 && have_f0) {  // (block-uniform) f(tnew, ypred) came with the Jacobian
+                    st = st0;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) f[r] = f0p[r];
+                } else {
+                    st = c.template eval<0>(g, a, tnew, yk, f);
+                }
                 if (!gdone) {
                     nfev += 1;
                     n_iter = k + 1;
@@ -324,12 +356,12 @@ template <int G> struct CoopBdf {
             // ---- not converged with a Jacobian from an earlier step: refresh it at (tnew, ypred), second pass ----------
             const bool refresh = live && !converged && !bad && !jac_current && pass == 0;
             if (!__syncthreads_or(refresh)) break;
-            double fp[R];
-            const int st = c.template eval<2>(g, a, tnew, ypred, fp, refresh);
+            st0 = c.template eval<2>(g, a, tnew, ypred, f0p, refresh);
+            have_f0 = true;  // the second pass starts from ypred again
             if (refresh) {
                 nfev += 1;
                 njev += 1;
-                if (st != 0) bad = 1;
+                if (st0 != 0) bad = 1;
                 jac_current = true;
                 have_lu = false;
             }
@@ -373,7 +405,7 @@ template <int G> struct CoopBdf {
             for (int j = order; j >= 0; --j) Dx(c, g, j, r) += Dx(c, g, j + 1, r);
         }
         hnext = h;
-        if (n_equal < order + 1) return true;
+        if (n_equal < order + 1 || n_attempt % (order <= 2 ? ODESYS_BDF_EPOCH / 2 : ODESYS_BDF_EPOCH) != 0) return true;
         double vm[R], vp[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -401,6 +433,7 @@ template <int G> struct CoopBdf {
         hnext = h * (double)fminf(10.0f, safety * best);
         n_equal = 0;
         have_lu = false;
+        refresh_jac = ODESYS_BDF_REFRESH_JAC != 0;
         return true;
     }
     // the same norm with the group's own mask (control runs under per-group divergence)

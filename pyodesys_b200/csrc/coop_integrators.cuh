@@ -421,6 +421,7 @@ template <int G> struct CoopRos4 {
     }
 
     static constexpr bool kAlwaysInit = false;  // init() only chooses a starting step
+    static constexpr int kEpoch = 0;  // no start grid (see CoopBdf)
     static constexpr int kExtraDoubles = 0;
     // Hairer's starting step (initial_step in integrators.cuh); executed by every thread of the block (two
     // evaluation slots), the result is used by the groups that asked for it
@@ -675,10 +676,16 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
 #ifdef PYODESYS_COOP_DEBUG_ITERS
     long long dbg_iters = 0;
 #endif
+    int epoch_phase = 0;  // St::kEpoch > 0: idle groups draw their next system every kEpoch-th iteration only
     for (;;) {
 #ifdef PYODESYS_COOP_DEBUG_ITERS
         if (++dbg_iters > PYODESYS_COOP_DEBUG_ITERS) break;  // debugging aid: tells a livelock from a deadlock
 #endif
+        bool may_fetch = true;
+        if (St::kEpoch > 0) {
+            may_fetch = epoch_phase == 0;
+            epoch_phase = epoch_phase + 1 == St::kEpoch ? 0 : epoch_phase + 1;
+        }
         COOP_T0(t_top);
         // ---- (B) + (E): termination test of the running system, retire ----------------------------------------
         if (active) {
@@ -727,7 +734,7 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
             }
         }
         // ---- (A) fetch a new system for an idle group ------------------------------------------------------------
-        if (!active && !exhausted) {
+        if (may_fetch && !active && !exhausted) {
             if (a.work_counter != nullptr) {
                 unsigned long long nxt = 0;
                 if (g.gl == 0) nxt = atomicAdd(a.work_counter, 1ull);
@@ -806,7 +813,7 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
         }
         COOP_ACC(6, t_top);
         COOP_T0(t_bar);
-        if (__syncthreads_and(!active)) break;
+        if (__syncthreads_and(!active && exhausted)) break;
         COOP_ACC(7, t_bar);
         // a system that is about to retire (finished span, failure) idles through this iteration
         const bool live = active && t != tend && nfail >= 0 && nfail < (1 << 20);

@@ -406,6 +406,7 @@ template <> struct Stepper<M_RK4> {
     static constexpr bool kAdaptive = false;
     static constexpr int kOrder = 4;
     static constexpr int kSharedDoublesPerThread = 0;
+    static constexpr int kEpoch = 0;  // no start grid (see BdfStepper)
     __device__ __forceinline__ void bind_shared(double *, int, int) {}
     __device__ __forceinline__ int begin(OdeSys &, const KernelArgs &, const Tol &, double, const double *) { return 0; }
     __device__ __forceinline__ void auto_step(OdeSys &, const KernelArgs &, const Tol &, double, const double *,
@@ -463,6 +464,7 @@ template <> struct Stepper<M_DOPRI5> {
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 5;
     static constexpr int kSharedDoublesPerThread = 0;
+    static constexpr int kEpoch = 0;  // no start grid (see BdfStepper)
     __device__ __forceinline__ void bind_shared(double *, int, int) {}
     double k1[NY];                                   // f(t, y), FSAL
     double k3[NY], k4[NY], k5[NY], k6[NY];           // stages of the last attempt (dense output forms from them)
@@ -698,6 +700,7 @@ template <class Store> struct Ros4Stepper : Store {
     static constexpr bool kAdaptive = true;
     static constexpr int kOrder = 4;
     static constexpr int kSharedDoublesPerThread = 0;
+    static constexpr int kEpoch = 0;  // no start grid (see BdfStepper)
     __device__ __forceinline__ void bind_shared(double *, int, int) {}
     using Store::g1;
     using Store::g2;
@@ -1041,10 +1044,20 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
     double g_old[NROOTS];
     int n_roots = 0;
 #endif
+    // St::kEpoch > 0: idle lanes draw their next system only every kEpoch-th iteration of this loop (an active lane
+    // makes exactly one step attempt per iteration, so the attempts of all lanes of the warp are numbered alike
+    // modulo kEpoch; a lane waits 2.5 iterations on average, of the hundreds its next system takes)
+    int epoch_phase = 0;
 
     for (;;) {
+        bool may_fetch = true;
+        if (St::kEpoch > 0) {
+            may_fetch = epoch_phase == 0;
+            epoch_phase = epoch_phase + 1 == St::kEpoch ? 0 : epoch_phase + 1;
+        }
         // ---- (A) fetch a new system for every idle lane ---------------------------------------
-        if (a.work_counter != nullptr) {
+        if (!may_fetch) {
+        } else if (a.work_counter != nullptr) {
             const unsigned need = __ballot_sync(FULL_MASK, !active && !exhausted);
             if (need) {
                 const int leader = __ffs(need) - 1;
@@ -1064,7 +1077,7 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
         } else if (!active && !exhausted) {
             s += nthreads;
         }
-        if (!active && !exhausted) {
+        if (may_fetch && !active && !exhausted) {
             if (s >= a.n) {
                 exhausted = true;
             } else {
@@ -1148,7 +1161,7 @@ __global__ void __launch_bounds__(BLOCK, PYODESYS_MIN_BLOCKS_FOR(METHOD)) integr
                 }
             }
         }
-        if (__all_sync(FULL_MASK, !active)) break;
+        if (__all_sync(FULL_MASK, !active && exhausted)) break;
         if (!active) continue;
 
         // ---- (B) termination / failure bookkeeping for this lane --------------------------------

@@ -44,6 +44,21 @@ ODESYS_FN double odesys_effective_rtol(int method, double rtol) {
     return r > floor_ ? r : floor_;
 }
 
+// BDF: order / step-size selection happens on a fixed grid of step attempts ("epochs"), not whenever order + 1
+// equal steps have accumulated: after attempt number k of a system (counted from the start of the integration) a
+// new order and step are chosen only if k is a multiple of ODESYS_BDF_EPOCH and at least order + 1 equal steps were
+// taken (CVODE likewise waits - its ``qwait`` - before it reconsiders order and step; waiting longer is always
+// allowed).  The Jacobian is re-evaluated with every such selection (the iteration matrix is re-formed then
+// anyway).  Why a grid: on the GPU the systems of a warp (thread kernel) or block (cooperative kernel) start on
+// the same grid, so the expensive, formerly divergent parts of a step - rescaling the difference table,
+// Jacobian, factorisation - fall into the same iteration for all of them.  The CPU oracle applies the same rule.
+#ifndef ODESYS_BDF_EPOCH
+#define ODESYS_BDF_EPOCH 6
+#endif
+#ifndef ODESYS_BDF_REFRESH_JAC
+#define ODESYS_BDF_REFRESH_JAC 1
+#endif
+
 namespace AnyODE {
 enum Status : int { success = 0, recoverable_error = 1, unrecoverable_error = -1 };
 template <class T> ODESYS_FN void ignore(const T &) {}

@@ -487,7 +487,9 @@ def test_bdf_robertson_batch_vs_oracle_and_lsoda(cuda_device, golden):
                                           np.maximum(10*b['rtol']*np.abs(y_cpu[:, -1]), 10*b['atol'])).max()
     # same algorithm -> about the same amount of work (the step-size factors use fp32 powers on the device)
     assert abs(info.counters[0].sum() - cn[0].sum()) <= 0.05*cn[0].sum()
-    assert info.counters[2].sum() < 0.1*info.counters[0].sum()  # the Jacobian is reused across many steps
+    # the Jacobian is reused across the steps of an epoch (odesys_prelude.h: one evaluation per order / step selection)
+    assert info.counters[2].sum() < 0.25*info.counters[0].sum()
+    assert abs(info.counters[2].sum() - cn[2].sum()) <= 0.05*cn[2].sum()
     assert np.abs(y_gpu.sum(axis=1) - 1).max() < 1e-9
     g = golden['robertson_1e5']
     ref = np.array(g['yout'])[:, -1, :]
