@@ -13,7 +13,8 @@
 //                    addressed by the current order; in registers the compiler turned the order-predicated
 //                    copies into dynamic indexing and moved the whole stepper (472 B) to local memory
 //                    (153 ms per 1e6 Robertson systems against 20 ms for Rosenbrock-4)
-//   Jm               the stored Jacobian (re-evaluated only after a Newton convergence failure), registers
+//   Jm               the stored Jacobian (re-evaluated with every order / step selection and after a Newton
+//                    convergence failure): SHARED memory behind D, it is read once per factorisation
 //   W, piv           LU of I - c Jm, c = h / alpha_k, re-formed only when c or Jm changed, registers
 // One step: predictor sum, <= 4 simplified Newton iterations (1 rhs + 1 triangular solve each), error
 // estimate errconst_k * d; after k+1 equal steps the estimates for orders k-1, k, k+1 choose the next order
@@ -25,6 +26,9 @@ namespace pyodesys_cuda {
 
 #if ODESYS_HAS_JAC
 
+#ifndef PYODESYS_BDF_BRANCHFREE_PRED
+#define PYODESYS_BDF_BRANCHFREE_PRED 0
+#endif
 namespace bdfc {
 constexpr int MAXORD = 5;
 constexpr int NEWTON_MAXITER = 4;
@@ -38,8 +42,9 @@ __constant__ double kBdfGamma[7] = {0.0, 1.0, 1.5, 1.0 + 0.5 + 1.0 / 3, 1.0 + 0.
 __constant__ double kBdfKappa[7] = {0.0, -0.1850, -1.0 / 9, -0.0823, -0.0415, 0.0, 0.0};
 
 struct BdfSink {
-    double *J;
-    __device__ __forceinline__ void setj(int i, int j, double v) { J[i * NY + j] = v; }
+    double *J;   // this thread's column of the stored Jacobian (shared memory)
+    int stride;
+    __device__ __forceinline__ void setj(int i, int j, double v) { J[(i * NY + j) * stride] = v; }
     __device__ __forceinline__ void setdfdt(int, double) {}
 };
 
@@ -137,6 +142,11 @@ __device__ PYODESYS_GMRES_INLINE int gmres_solve(Sys &sys, double t, const doubl
 
 // KRYLOV = false: LU of I - c J in registers;  true: matrix-free (gmres_solve), a kernel of its own so that the
 // dense path carries none of its registers
+// gamma_j for a compile-time j (folds to an immediate in unrolled loops)
+__device__ __forceinline__ double bdf_gamma_c(int j) {
+    return j == 1 ? 1.0 : j == 2 ? 1.5 : j == 3 ? 11.0 / 6 : j == 4 ? 25.0 / 12 : j == 5 ? 137.0 / 60 : j == 6 ? 2.45 : 0.0;
+}
+
 template <bool KRYLOV> struct BdfStepper {
     typedef OdeSys Sys;
     static constexpr bool kAdaptive = true;
@@ -145,7 +155,7 @@ template <bool KRYLOV> struct BdfStepper {
     // numbered alike and their order / step selections (odesys_prelude.h) coincide
     static constexpr int kEpoch = ODESYS_BDF_EPOCH;
     static constexpr int ND = bdfc::MAXORD + 3;
-    static constexpr int kSharedDoublesPerThread = ND * NY;
+    static constexpr int kSharedDoublesPerThread = ND * NY + NY * NY;
     double *Dsm;   // this thread's column of the difference table in shared memory
     int dstride;   // = blockDim.x
     __device__ __forceinline__ void bind_shared(double *base, int tid, int nthreads) {
@@ -153,12 +163,12 @@ template <bool KRYLOV> struct BdfStepper {
         dstride = nthreads;
     }
     __device__ __forceinline__ double &Dx(int j, int i) { return Dsm[(j * NY + i) * dstride]; }
-    double Jm[NY * NY];
+    __device__ __forceinline__ double &Jx(int r, int q) { return Dsm[(ND * NY + r * NY + q) * dstride]; }
     RegArr<NY * NY> W;  // factors of I - c Jm (ny == 3: its explicit inverse, see lin_factor in integrators.cuh)
     int piv[NY];
     double d[NY];
     float iscale[NY];   // 1 / (atol_i + rtol |y_i|): the norms only steer Newton and the step size -> fp32
-    double h_cur, c_lu, atol_[NY], rtol_;
+    double h_cur, c_lu;
     float newton_tol, safety;
     int order, n_equal, n_attempt;
     bool have_lu, jac_current, fresh, newton_failed, refresh_jac;
@@ -166,9 +176,9 @@ template <bool KRYLOV> struct BdfStepper {
 
     __device__ __forceinline__ double alpha(int k) const { return (1.0 - kBdfKappa[k]) * kBdfGamma[k]; }
     __device__ __forceinline__ double errconst(int k) const { return fma(kBdfKappa[k], kBdfGamma[k], 1.0 / (k + 1)); }
-    __device__ __forceinline__ void set_scale(const double *y) {
+    __device__ __forceinline__ void set_scale(const KernelArgs &a, const double *y) {
 #pragma unroll
-        for (int i = 0; i < NY; ++i) iscale[i] = rcp_ftz(fmaxf((float)fma(rtol_, fabs(y[i]), atol_[i]), 1e-37f));
+        for (int i = 0; i < NY; ++i) iscale[i] = rcp_ftz(fmaxf((float)fma(a.rtol, fabs(y[i]), a.atol[i]), 1e-37f));
     }
     // weighted rms norm in single precision (sqrt.approx: one MUFU instead of the IEEE sqrt subroutine)
     __device__ __forceinline__ float rms(const double *v) const {
@@ -183,17 +193,14 @@ template <bool KRYLOV> struct BdfStepper {
         return r;
     }
     __device__ __forceinline__ int eval_jac(Sys &sys, double t, const double *y) {
-        BdfSink sink{Jm};
+        BdfSink sink{&Jx(0, 0), dstride};
         const int njev0 = sys.njev;
         const int bad = sys.dense_jac_sink(t, y, sink);
         sys.njev = njev0 + 1;
         return bad;
     }
     __device__ __forceinline__ int begin(Sys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y) {
-        rtol_ = tol.rtol;
-#pragma unroll
-        for (int i = 0; i < NY; ++i) atol_[i] = tol.atol[i];
-        newton_tol = (float)fmax(10.0 * DBL_EPSILON / rtol_, fmin(0.03, sqrt(rtol_)));
+        newton_tol = (float)fmax(10.0 * DBL_EPSILON / tol.rtol, fmin(0.03, sqrt(tol.rtol)));
         order = 1;
         n_equal = 0;
         n_attempt = 0;
@@ -218,12 +225,8 @@ template <bool KRYLOV> struct BdfStepper {
         jac_current = true;
         return bad;
     }
-    __device__ __forceinline__ void auto_step(Sys &sys, const KernelArgs &a, const Tol &, double t, const double *y,
+    __device__ __forceinline__ void auto_step(Sys &sys, const KernelArgs &a, const Tol &tl, double t, const double *y,
                                               double span, double &h) {
-        Tol tl;
-        tl.rtol = rtol_;
-#pragma unroll
-        for (int i = 0; i < NY; ++i) tl.atol[i] = atol_[i];
         double f0[NY];
 #pragma unroll
         for (int i = 0; i < NY; ++i) f0[i] = Dx(1, i);
@@ -286,16 +289,24 @@ template <bool KRYLOV> struct BdfStepper {
             double s = Dx(0, i), ps = 0.0;
 #pragma unroll
             for (int j = 1; j <= bdfc::MAXORD; ++j) {
+#if PYODESYS_BDF_BRANCHFREE_PRED
+                // rows above the order hold finite leftovers: loaded unconditionally, selected to zero (no branches)
+                double dj = Dx(j, i);
+                dj = (j <= order) ? dj : 0.0;
+                s += dj;
+                ps = fma(bdf_gamma_c(j), dj, ps);
+#else
                 if (j <= order) {
                     const double dj = Dx(j, i);
                     s += dj;
-                    ps = fma(kBdfGamma[j], dj, ps);
+                    ps = fma(bdf_gamma_c(j), dj, ps);
                 }
+#endif
             }
             ypred[i] = s;
             psi[i] = ps * ialpha;
         }
-        set_scale(ypred);
+        set_scale(a, ypred);
         const double c = h * ialpha;
         bool converged = false;
         int n_iter = 0;
@@ -317,8 +328,8 @@ template <bool KRYLOV> struct BdfStepper {
 #pragma unroll
                 for (int r = 0; r < NY; ++r)
 #pragma unroll
-                    for (int q = 0; q < NY; ++q) W[r * NY + q] = fma(-c, Jm[r * NY + q], r == q ? 1.0 : 0.0);
-                const bool ok = lin_factor<false>(W, piv, rtol_, cnt);
+                    for (int q = 0; q < NY; ++q) W[r * NY + q] = fma(-c, Jx(r, q), r == q ? 1.0 : 0.0);
+                const bool ok = lin_factor<false>(W, piv, a.rtol, cnt);
                 cnt.nlu += 1;
                 c_lu = c;
                 have_lu = ok;
@@ -385,7 +396,7 @@ template <bool KRYLOV> struct BdfStepper {
             return 0;
         }
         safety = 0.9f * (2 * bdfc::NEWTON_MAXITER + 1) / (float)(2 * bdfc::NEWTON_MAXITER + n_iter);
-        set_scale(ynew);
+        set_scale(a, ynew);
         const float ef = (float)errconst(order) * rms(d);
         if (!(ef <= 3.0e38f) || !finite_all(ynew)) return 1;
         err = (double)ef;
@@ -404,22 +415,20 @@ template <bool KRYLOV> struct BdfStepper {
         jac_current = false;
         n_equal += 1;
         // D[order+2] = d - D[order+1]; D[order+1] = d; D[j] += D[j+1] for j = order..0
+        // (shared memory is addressed by the order directly; the running sum stays in a register)
 #pragma unroll
-        for (int j = ND - 1; j >= 2; --j) {
-            if (j == order + 2) {
+        for (int i = 0; i < NY; ++i) {
+            const double di = d[i];
+            Dx(order + 2, i) = di - Dx(order + 1, i);
+            Dx(order + 1, i) = di;
+            double carry = di;
 #pragma unroll
-                for (int i = 0; i < NY; ++i) Dx(j, i) = d[i] - Dx(j - 1, i);
-            }
-            if (j == order + 1) {
-#pragma unroll
-                for (int i = 0; i < NY; ++i) Dx(j, i) = d[i];
-            }
-        }
-#pragma unroll
-        for (int j = bdfc::MAXORD; j >= 0; --j) {
-            if (j <= order) {
-#pragma unroll
-                for (int i = 0; i < NY; ++i) Dx(j, i) += Dx(j + 1, i);
+            for (int j = bdfc::MAXORD; j >= 0; --j) {
+                const double nv = carry + Dx(j, i);
+                if (j <= order) {
+                    Dx(j, i) = nv;
+                    carry = nv;
+                }
             }
         }
         hnext = h;
@@ -432,17 +441,12 @@ template <bool KRYLOV> struct BdfStepper {
             vm[i] = 0.0;
             vp[i] = 0.0;
         }
+        if (order > 1) {
 #pragma unroll
-        for (int j = 2; j < ND; ++j) {
-            if (j == order) {
-#pragma unroll
-                for (int i = 0; i < NY; ++i) vm[i] = Dx(j, i);
-            }
-            if (j == order + 2) {
-#pragma unroll
-                for (int i = 0; i < NY; ++i) vp[i] = Dx(j, i);
-            }
+            for (int i = 0; i < NY; ++i) vm[i] = Dx(order, i);
         }
+#pragma unroll
+        for (int i = 0; i < NY; ++i) vp[i] = Dx(order + 2, i);
         const float inf = __int_as_float(0x7f800000);
         float fm = -1.0f, fp = -1.0f;
         if (order > 1) {
