@@ -26,9 +26,6 @@ namespace pyodesys_cuda {
 
 #if ODESYS_HAS_JAC
 
-#ifndef PYODESYS_BDF_BRANCHFREE_PRED
-#define PYODESYS_BDF_BRANCHFREE_PRED 0
-#endif
 namespace bdfc {
 constexpr int MAXORD = 5;
 constexpr int NEWTON_MAXITER = 4;
@@ -289,19 +286,11 @@ template <bool KRYLOV> struct BdfStepper {
             double s = Dx(0, i), ps = 0.0;
 #pragma unroll
             for (int j = 1; j <= bdfc::MAXORD; ++j) {
-#if PYODESYS_BDF_BRANCHFREE_PRED
-                // rows above the order hold finite leftovers: loaded unconditionally, selected to zero (no branches)
-                double dj = Dx(j, i);
-                dj = (j <= order) ? dj : 0.0;
-                s += dj;
-                ps = fma(bdf_gamma_c(j), dj, ps);
-#else
                 if (j <= order) {
                     const double dj = Dx(j, i);
                     s += dj;
                     ps = fma(bdf_gamma_c(j), dj, ps);
                 }
-#endif
             }
             ypred[i] = s;
             psi[i] = ps * ialpha;

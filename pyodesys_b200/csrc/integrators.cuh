@@ -1008,9 +1008,10 @@ __device__ __noinline__ bool locate_roots(St &st, Sys &sys, const KernelArgs &a,
 #ifndef PYODESYS_MIN_BLOCKS
 #define PYODESYS_MIN_BLOCKS (ODESYS_NY <= 4 ? 4 : 1)
 #endif
-// BDF carries 8 difference vectors + J + LU per lane: give it the full register file (2 blocks of 128 per SM)
+// BDF keeps its difference table and the Jacobian in shared memory; ny <= 4: 4 blocks of 128 per SM (128 registers,
+// ~20 spilled values outside the Newton loop) beat 3 blocks without spills: 36.0 against 40.4 ms per 1e6 Robertson
 #ifndef PYODESYS_BDF_MIN_BLOCKS
-#define PYODESYS_BDF_MIN_BLOCKS (ODESYS_NY <= 4 ? 3 : 1)
+#define PYODESYS_BDF_MIN_BLOCKS (ODESYS_NY <= 4 ? 4 : 1)
 #endif
 #define PYODESYS_MIN_BLOCKS_FOR(METHOD) (((METHOD) == M_BDF || (METHOD) == M_BDF_KRYLOV) ? PYODESYS_BDF_MIN_BLOCKS : PYODESYS_MIN_BLOCKS)
 // GUARD: compiled with the invariant test of rhs (max_invariant_violation != 0); the unguarded instantiation is the
