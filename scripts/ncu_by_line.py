@@ -68,6 +68,11 @@ for f, c in byfile.most_common():
 print('--- lines')
 for (f, ln), c in byline.most_common(top):
     print('%6.2f %%  samples %6d  %s:%d' % (100.0*c/tot, samples[(f, ln)], f, ln))
+ts = sum(samples.values())
+if ts:
+    print('--- lines by stall samples (share of %d samples ~ share of the time)' % ts)
+    for (f, ln), c in samples.most_common(top):
+        print('%6.2f %%  instr %5.2f %%  %s:%d' % (100.0*c/ts, 100.0*byline[(f, ln)]/tot, f, ln))
 print('--- opcodes')
 for op, c in byop.most_common(25):
     print('%6.2f %%  %s' % (100.0*c/tot, op))
