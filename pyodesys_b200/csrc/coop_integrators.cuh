@@ -27,9 +27,9 @@ namespace pyodesys_cuda {
 
 #if ODESYS_HAS_JAC
 
-#ifndef PYODESYS_COOP_G
 // smallest group whose lanes keep their rows of W in at most 56 doubles (ny = 14: 4 lanes x 4 rows; ny = 28: 16 x 2)
 #define PYODESYS_COOP_FITS(g) ((((NY + (g) - 1) / (g)) * NY) <= 56)
+#ifndef PYODESYS_COOP_G
 #define PYODESYS_COOP_G (PYODESYS_COOP_FITS(4) ? 4 : PYODESYS_COOP_FITS(8) ? 8 : PYODESYS_COOP_FITS(16) ? 16 : 32)
 #endif
 // Threads per block.  The systems of a block step in lock-step and every evaluation is a serial phase of ONE warp
