@@ -496,7 +496,7 @@ struct BDF : StepperBase {
     DenseLU lu;
     double gamma_[BDF_MAXORD + 2], alpha_[BDF_MAXORD + 2], errc_[BDF_MAXORD + 2];
     double f0[NY], d[NY], scale[NY];
-    double h_cur = 0, c_lu = 0, newton_tol = 0, safety = 0.9;
+    double h_cur = 0, c_lu = 0, newton_tol = 0, newton_floor = 0, safety = 0.9;
     // the tolerances arrive already calibrated (odesys_kappa, odesys_prelude.h)
     Settings cs;
     int order = 1, n_equal = 0, n_attempt = 0;
@@ -519,7 +519,10 @@ struct BDF : StepperBase {
         }
         cs = *w.cfg;
         const double rtol = cs.rtol;
-        newton_tol = std::max(10 * DBL_EPSILON / rtol, std::min(0.03, std::sqrt(rtol)));
+        newton_tol = std::max(10 * DBL_EPSILON / rtol, ODESYS_BDF_NEWTON_TOL);  // odesys_prelude.h
+        // a correction this small is at the rounding level of the residual (eps / rtol in units of the tolerance):
+        // the contraction-rate test would compare noise with noise and call a converged iteration divergent
+        newton_floor = std::max(0.03 * newton_tol, 3 * DBL_EPSILON / rtol);
         order = 1;
         n_equal = 0;
         n_attempt = 0;
@@ -633,13 +636,14 @@ struct BDF : StepperBase {
                 w.nsolve += 1;
                 const double dy_norm = rms(dy, scale);
                 double rate = -1;
+                const bool tiny = dy_norm <= newton_floor;
                 if (dy_norm_old >= 0) rate = dy_norm / dy_norm_old;
-                if (rate >= 0 && (rate >= 1 || std::pow(rate, BDF_NEWTON_MAXITER - k) / (1 - rate) * dy_norm > newton_tol)) break;
+                if (!tiny && rate >= 0 && (rate >= 1 || std::pow(rate, BDF_NEWTON_MAXITER - k) / (1 - rate) * dy_norm > newton_tol)) break;
                 for (int i = 0; i < NY; ++i) {
                     yk[i] += dy[i];
                     d[i] += dy[i];
                 }
-                if (dy_norm == 0 || (rate >= 0 && rate / (1 - rate) * dy_norm < newton_tol)) {
+                if (tiny || (rate >= 0 && rate / (1 - rate) * dy_norm < newton_tol)) {
                     converged = true;
                     break;
                 }

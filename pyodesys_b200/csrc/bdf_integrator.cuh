@@ -166,7 +166,7 @@ template <bool KRYLOV> struct BdfStepper {
     double d[NY];
     float iscale[NY];   // 1 / (atol_i + rtol |y_i|): the norms only steer Newton and the step size -> fp32
     double h_cur, c_lu;
-    float newton_tol, safety;
+    float newton_tol, newton_floor, safety;
     int order, n_equal, n_attempt;
     bool have_lu, jac_current, fresh, newton_failed, refresh_jac;
     static constexpr bool krylov = KRYLOV;  // Newton corrections by gmres_solve on OdeSys::jtimes: no Jacobian, no LU
@@ -197,7 +197,9 @@ template <bool KRYLOV> struct BdfStepper {
         return bad;
     }
     __device__ __forceinline__ int begin(Sys &sys, const KernelArgs &a, const Tol &tol, double t, const double *y) {
-        newton_tol = (float)fmax(10.0 * DBL_EPSILON / tol.rtol, fmin(0.03, sqrt(tol.rtol)));
+        newton_tol = (float)fmax(10.0 * DBL_EPSILON / tol.rtol, ODESYS_BDF_NEWTON_TOL);  // odesys_prelude.h
+        // a correction this small is at the rounding level of the residual: converged, whatever the rate looks like
+        newton_floor = fmaxf(0.03f * newton_tol, (float)(3.0 * DBL_EPSILON / tol.rtol));
         order = 1;
         n_equal = 0;
         n_attempt = 0;
@@ -348,8 +350,9 @@ template <bool KRYLOV> struct BdfStepper {
                 // contraction rate of the simplified Newton iteration; the tests are the usual ones
                 // (rate >= 1, or rate^(MAXITER-k)/(1-rate) |dy| > tol: will not converge in time) without divisions
                 float rate = -1.0f;
+                const bool tiny = nrm <= newton_floor;
                 if (nrm_old >= 0.0f) rate = nrm * rcp_ftz(nrm_old);
-                if (rate >= 0.0f) {
+                if (!tiny && rate >= 0.0f) {
                     float rp = rate;
                     if (k <= 2) rp *= rate;
                     if (k <= 1) rp *= rate;
@@ -360,7 +363,7 @@ template <bool KRYLOV> struct BdfStepper {
                     yk[i] += dy[i];
                     d[i] += dy[i];
                 }
-                if (nrm == 0.0f || (rate >= 0.0f && rate * nrm < newton_tol * (1.0f - rate))) {
+                if (tiny || (rate >= 0.0f && rate * nrm < newton_tol * (1.0f - rate))) {
                     converged = true;
                     break;
                 }

@@ -41,6 +41,13 @@ template <int G> struct CoopBdf {
     // systems start on a grid of kEpoch block iterations: the order / step selections of all systems of the block -
     // rescaling, new Jacobian, new inverse - fall into the same iteration (odesys_prelude.h)
     static constexpr int kEpoch = ODESYS_BDF_EPOCH;
+#ifdef PYODESYS_COOP_TRACE
+    int trace_iter, trace_code;  // debugging aid: Newton iterations and outcome of the last attempt
+    float trace_nrm[4];
+    __device__ __forceinline__ double trace_order() const { return (double)order; }
+    __device__ __forceinline__ double trace_flags() const { return trace_code + 100.0 * trace_iter + 10000.0 * n_equal; }
+    __device__ __forceinline__ double trace_extra(int k) const { return (double)trace_nrm[k]; }
+#endif
 
     double W[R][NY];  // (I - c J)^-1 (c_invert layout)
     int ord[R];
@@ -48,7 +55,7 @@ template <int G> struct CoopBdf {
     double d[R];
     float iscale[R];
     double h_cur, c_lu;
-    float newton_tol, safety;
+    float newton_tol, newton_floor, safety;
     int order, n_equal, n_attempt;
     bool have_lu, jac_current, fresh, newton_failed, refresh_jac;
 
@@ -95,6 +102,7 @@ template <int G> struct CoopBdf {
         h_cur = 0.0;
         c_lu = 0.0;
         newton_tol = 0.03f;
+        newton_floor = 0.0f;
         identity = true;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -110,7 +118,8 @@ template <int G> struct CoopBdf {
     // Hairer's starting step for order 1.  Executed by the whole block; ``want`` marks the groups that use it.
     __device__ __forceinline__ double init(Coop<G> &c, const Grp<G> &g, const KernelArgs &a, double t0, const double *y,
                                            double span, bool want, bool have_h, int &nfev, int &njev) {
-        newton_tol = (float)fmax(10.0 * DBL_EPSILON / a.rtol, fmin(0.03, sqrt(a.rtol)));
+        newton_tol = (float)fmax(10.0 * DBL_EPSILON / a.rtol, ODESYS_BDF_NEWTON_TOL);  // odesys_prelude.h
+        newton_floor = fmaxf(0.03f * newton_tol, (float)(3.0 * DBL_EPSILON / a.rtol));  // see BdfStepper
         double f0[R], y1[R], f1[R];
         c.template eval<2>(g, a, t0, y, f0, want);
         if (want) {
@@ -270,23 +279,9 @@ template <int G> struct CoopBdf {
                         }
                     }
                 }
-                // groups that keep their inverse run the elimination on a copy (the routine is a warp collective)
-                double Wtmp[R][NY];
-                int otmp[R];
-                bool itmp = true;
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-#pragma unroll
-                    for (int j = 0; j < NY; ++j) Wtmp[r][j] = need_lu ? W[r][j] : ((g.owns(r) && r * G + g.gl == j) ? 1.0 : 0.0);
-                const bool ok = c_invert<G>(g, Wtmp, otmp, itmp);
+                // groups that keep their inverse only take part in the collectives of the elimination
+                const bool ok = c_invert<G>(g, W, ord, identity, need_lu);
                 if (need_lu) {
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        ord[r] = otmp[r];
-#pragma unroll
-                        for (int j = 0; j < NY; ++j) W[r][j] = Wtmp[r][j];
-                    }
-                    identity = itmp;
                     cnt.nlu += 1;
                     c_lu = cc;
                     have_lu = ok;
@@ -322,12 +317,16 @@ template <int G> struct CoopBdf {
                 for (int r = 0; r < R; ++r) dy[r] = fma(cc, f[r], -psi[r]) - d[r];
                 c_apply<G>(g, W, ord, identity, dy);  // warp collectives: every group, results used where !gdone
                 const float nrm = rms(dy);
+#ifdef PYODESYS_COOP_TRACE
+                if (!gdone) trace_nrm[k] = nrm;
+#endif
                 if (!gdone) {
                     cnt.nsolve += 1;
                     bool stop = !(nrm <= 3.0e38f);
                     float rate = -1.0f;
+                    const bool tiny = nrm <= newton_floor;
                     if (!stop && nrm_old >= 0.0f) rate = nrm * rcp_ftz(nrm_old);
-                    if (!stop && rate >= 0.0f) {
+                    if (!stop && !tiny && rate >= 0.0f) {
                         float rp = rate;
                         if (k <= 2) rp *= rate;
                         if (k <= 1) rp *= rate;
@@ -341,7 +340,7 @@ template <int G> struct CoopBdf {
                             yk[r] += dy[r];
                             d[r] += dy[r];
                         }
-                        if (nrm == 0.0f || (rate >= 0.0f && rate * nrm < newton_tol * (1.0f - rate))) {
+                        if (tiny || (rate >= 0.0f && rate * nrm < newton_tol * (1.0f - rate))) {
                             converged = true;
                             gdone = true;
                         }
@@ -366,6 +365,10 @@ template <int G> struct CoopBdf {
                 have_lu = false;
             }
         }
+#ifdef PYODESYS_COOP_TRACE
+        trace_iter = n_iter;
+        trace_code = bad ? 3 : (!converged ? (jac_current ? 2 : 1) : 0);
+#endif
         if (bad) return 1;
         if (!converged) {
             newton_failed = true;

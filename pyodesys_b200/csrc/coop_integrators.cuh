@@ -139,6 +139,63 @@ template <int G> __device__ __noinline__ void coop_eval_jac(int e) {
     ist[e] |= st;
 }
 
+// ---- evaluation split over the four warps of a block ------------------------------------------------------------
+// With one evaluator warp, an evaluation is a latency-bound serial phase (a single warp issues one dependent FP64
+// instruction every few cycles while the other three wait at the barrier: 30 % of a block's time for Rosenbrock-4 on
+// the radiolysis network, more for BDF).  The code generator deals the rows of f and the columns of J to
+// ODESYS_EVAL_PARTS = 4 self-contained pieces (each with its own common-subexpression elimination; shared reaction
+// rates are recomputed, so a piece is ~1/2 of f and ~1/4 of J); warp w evaluates piece w for all systems of the block.
+#ifndef PYODESYS_COOP_SPLIT_EVAL
+#define PYODESYS_COOP_SPLIT_EVAL 1
+#endif
+#if PYODESYS_COOP_SPLIT_EVAL && defined(ODESYS_EVAL_PARTS) && ODESYS_EVAL_PARTS == 4
+#define PYODESYS_COOP_SPLIT 1
+#else
+#define PYODESYS_COOP_SPLIT 0
+#endif
+template <int G> struct CoopSplit {
+    static constexpr bool value = PYODESYS_COOP_SPLIT && kCoopWarps == 4 && ((kCoopBlock / G) <= 32);
+};
+#if PYODESYS_COOP_SPLIT
+template <int G> struct CoopSinkF {
+    typedef CoopLayout<G> L;
+    double *F;  // already offset by the evaluator's system
+    __device__ __forceinline__ void set(int i, double v) { F[i * L::NSYSP] = v; }
+};
+// jac: 0 no, 1 yes, 2 where the system's request flag is set
+template <int G, int P> __device__ __noinline__ void coop_eval_part(int e, int error_outside_bounds, int jac) {
+    typedef CoopLayout<G> L;
+    extern __shared__ double c_smem[];
+    double *sm = c_smem;
+    typename L::ESys es;
+    es.m_p = SView<L::NSYS>{sm + L::oP + e};
+    es.m_p_cse = SView<L::NSYS>{sm + L::oPC + e};
+    double y[NY];
+#pragma unroll
+    for (int i = 0; i < NY; ++i) y[i] = sm[L::oY + i * L::NSYSP + e];
+    const double x = sm[L::oX + e];
+    int *ist = reinterpret_cast<int *>(sm + L::oInt);
+    CoopSinkF<G> sf{sm + L::oF + e};
+    int st = es.template rhs_sink_part<P>(x, y, sf);
+    if (P == 0) {
+#if ODESYS_HAS_BOUNDS
+        if (error_outside_bounds && es.outside_bounds(y)) st = AnyODE::Status::recoverable_error;
+#endif
+#if ODESYS_NONNEGATIVE
+#pragma unroll
+        for (int i = 0; i < NY; ++i)
+            if (y[i] < 0) st = AnyODE::Status::recoverable_error;
+#endif
+        ist[e] = st;
+    }
+    AnyODE::ignore(error_outside_bounds);
+    if (jac == 1 || (jac == 2 && ist[2 * L::NSYS + e])) {
+        CoopSinkJ<G> sink{sm + L::oJ + e, sm + L::oDF + e};
+        es.template dense_jac_sink_part<P>(x, y, sink);
+    }
+}
+#endif
+
 __device__ __forceinline__ double *c_smem_base() {
     extern __shared__ double c_smem[];
     return c_smem;
@@ -149,12 +206,29 @@ template <int G, int JAC> __device__ __forceinline__ long long coop_evaluate(int
     typedef CoopLayout<G> L;
     __syncthreads();  // staged states (Y, X) are complete
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int rel = (warp - (evalno % kCoopWarps) + kCoopWarps) % kCoopWarps;
-    const int e = rel * 32 + lane;
     long long body = 0;
 #ifdef PYODESYS_COOP_PROFILE
     const long long t_body = clock64();
 #endif
+#if PYODESYS_COOP_SPLIT
+    if (CoopSplit<G>::value) {
+        if (lane < L::NSYS) {
+            switch (warp) {  // (warp-uniform)
+            case 0: coop_eval_part<G, 0>(lane, error_outside_bounds, JAC); break;
+            case 1: coop_eval_part<G, 1>(lane, error_outside_bounds, JAC); break;
+            case 2: coop_eval_part<G, 2>(lane, error_outside_bounds, JAC); break;
+            default: coop_eval_part<G, 3>(lane, error_outside_bounds, JAC); break;
+            }
+        }
+#ifdef PYODESYS_COOP_PROFILE
+        body = clock64() - t_body;
+#endif
+        __syncthreads();  // results (F, J, status) are complete
+        return body;
+    }
+#endif
+    const int rel = (warp - (evalno % kCoopWarps) + kCoopWarps) % kCoopWarps;
+    const int e = rel * 32 + lane;
     if (rel < L::NE && e < L::NSYS) {
         coop_eval_rhs<G>(e, error_outside_bounds);
         if (JAC == 1 || (JAC == 2 && reinterpret_cast<const int *>(c_smem_base() + L::oInt)[2 * L::NSYS + e]))
@@ -272,7 +346,7 @@ template <int N> __device__ __forceinline__ void sts_vec(double *buf, const doub
 // literal register row and needs no selects.
 template <int G, int KS>
 __device__ __forceinline__ void c_pivot_step(const Grp<G> &g, double (*a)[NY], int *ord, double *dinv, int k, int kl,
-                                             bool &ok, bool &identity) {
+                                             bool &ok, bool &identity, bool part) {
     constexpr int R = Grp<G>::R;
     double *buf = (k & 1) ? g.ys : g.prow;  // two staging vectors in turn: one warp synchronisation per step
     int best = -1, bslot = 0;
@@ -291,7 +365,8 @@ __device__ __forceinline__ void c_pivot_step(const Grp<G> &g, double (*a)[NY], i
     const int mx = (kmax < 0) ? -1 : (kmax & ~127);
     ok = ok && (mx >= 0x00100000) && (mx < 0x7ff00000);
     const int nat = __shfl_sync(FULL_MASK, nat_here, g.lane0 + kl);
-    const bool natural = nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx;
+    // (a group that only takes part in the collectives - ``part`` false, see c_invert - never forces the slow path)
+    const bool natural = !part || (nat >= 0 && nat + (PYODESYS_COOP_PIVOT_SHIFT << 20) >= mx);
     double prow[NY];
     bool piv[R];
     if (__all_sync(FULL_MASK, natural)) {
@@ -316,6 +391,7 @@ __device__ __forceinline__ void c_pivot_step(const Grp<G> &g, double (*a)[NY], i
         }
     }
     __syncwarp();
+    if (!part) return;  // (after the last collective of the step; uniform over the warp in the common case)
     lds_vec<NY>(buf, prow);
     const double d = fast_rcp<2>(prow[0]);
 #pragma unroll
@@ -331,40 +407,49 @@ __device__ __forceinline__ void c_pivot_step(const Grp<G> &g, double (*a)[NY], i
     }
 }
 
-template <int G> __device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord, bool &identity) {
+// ``part`` = false: this group keeps the inverse it has (BDF: groups whose step and Jacobian did not change) and only
+// takes part in the warp collectives of the elimination; its a / ord / identity are left alone.
+template <int G>
+__device__ __forceinline__ bool c_invert(const Grp<G> &g, double (*a)[NY], int *ord, bool &identity, bool part = true) {
     constexpr int R = Grp<G>::R;
     static_assert(R <= 4 && G <= 32, "pivot key packs the slot in 2 bits, the lane in 5");
     bool ok = true;
-    identity = true;  // every pivot so far was the natural one: W^-1 comes out in variable order
+    bool ident = true;  // every pivot so far was the natural one: W^-1 comes out in variable order
     double dinv[R];
+    int ordw[R];  // participants: the order under construction; others: all rows "used" (they publish nothing)
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        ord[r] = g.owns(r) ? NY : -1;
+        ordw[r] = (g.owns(r) && part) ? NY : -1;
         dinv[r] = 0.0;
     }
     // natural row k = slot ks, lane kl of the group: slots unrolled (literal register rows), lanes rolled
     if (R > 0) {
 #pragma unroll 1
-        for (int kl = 0; kl < G && kl < NY; ++kl) c_pivot_step<G, 0>(g, a, ord, dinv, kl, kl, ok, identity);
+        for (int kl = 0; kl < G && kl < NY; ++kl) c_pivot_step<G, 0>(g, a, ordw, dinv, kl, kl, ok, ident, part);
     }
     if (R > 1) {
 #pragma unroll 1
-        for (int kl = 0; kl < G && G + kl < NY; ++kl) c_pivot_step<G, 1 % R>(g, a, ord, dinv, G + kl, kl, ok, identity);
+        for (int kl = 0; kl < G && G + kl < NY; ++kl) c_pivot_step<G, 1 % R>(g, a, ordw, dinv, G + kl, kl, ok, ident, part);
     }
     if (R > 2) {
 #pragma unroll 1
-        for (int kl = 0; kl < G && 2 * G + kl < NY; ++kl) c_pivot_step<G, 2 % R>(g, a, ord, dinv, 2 * G + kl, kl, ok, identity);
+        for (int kl = 0; kl < G && 2 * G + kl < NY; ++kl) c_pivot_step<G, 2 % R>(g, a, ordw, dinv, 2 * G + kl, kl, ok, ident, part);
     }
     if (R > 3) {
 #pragma unroll 1
-        for (int kl = 0; kl < G && 3 * G + kl < NY; ++kl) c_pivot_step<G, 3 % R>(g, a, ord, dinv, 3 * G + kl, kl, ok, identity);
+        for (int kl = 0; kl < G && 3 * G + kl < NY; ++kl) c_pivot_step<G, 3 % R>(g, a, ordw, dinv, 3 * G + kl, kl, ok, ident, part);
     }
-    // deferred normalisation: row p of the inverse is the accumulated row divided by its pivot
+    const bool all_ident = __all_sync(FULL_MASK, ident || !part);
+    if (part) {
+        // deferred normalisation: row p of the inverse is the accumulated row divided by its pivot
 #pragma unroll
-    for (int r = 0; r < R; ++r)
+        for (int r = 0; r < R; ++r) {
+            ord[r] = ordw[r];
 #pragma unroll
-        for (int j = 0; j < NY; ++j) a[r][j] *= dinv[r];
-    identity = __all_sync(FULL_MASK, identity);
+            for (int j = 0; j < NY; ++j) a[r][j] *= dinv[r];
+        }
+        identity = all_ident;
+    }
     return ok;
 }
 
@@ -422,6 +507,11 @@ template <int G> struct CoopRos4 {
 
     static constexpr bool kAlwaysInit = false;  // init() only chooses a starting step
     static constexpr int kEpoch = 0;  // no start grid (see CoopBdf)
+#ifdef PYODESYS_COOP_TRACE
+    __device__ __forceinline__ double trace_order() const { return 4.0; }
+    __device__ __forceinline__ double trace_flags() const { return 0.0; }
+    __device__ __forceinline__ double trace_extra(int) const { return 0.0; }
+#endif
     static constexpr int kExtraDoubles = 0;
     // Hairer's starting step (initial_step in integrators.cuh); executed by every thread of the block (two
     // evaluation slots), the result is used by the groups that asked for it
@@ -753,7 +843,21 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
                     else v = a.params[s * a.params_ld + i];
                     c_smem[L::oP + i * L::NSYS + c.sysl] = v;
                 }
-                if (g.gl == 0) ist[L::NSYS + c.sysl] = 1;  // the evaluator runs OdeSys::setup() for this slot
+                if (CoopSplit<G>::value) {
+                    // parameter-only sub-expressions (template:104-110), once per system, by the first lane of the
+                    // group: with four evaluating warps nobody could own the "first evaluation" of a slot
+#if ODESYS_NPCSE > 0
+                    __syncwarp(g.mask);
+                    if (g.gl == 0) {
+                        typename L::ESys es;
+                        es.m_p = SView<L::NSYS>{c_smem + L::oP + c.sysl};
+                        es.m_p_cse = SView<L::NSYS>{c_smem + L::oPC + c.sysl};
+                        es.setup();
+                    }
+#endif
+                } else if (g.gl == 0) {
+                    ist[L::NSYS + c.sysl] = 1;  // the evaluator runs OdeSys::setup() for this slot
+                }
                 cnt = {0, 0, 0, 0};
                 nfev = 0;
                 njev = 0;
@@ -858,6 +962,15 @@ template <class St, int G, int MODE> __device__ __forceinline__ void coop_kernel
             ok = st.control(c, g, err, hnext, hh);
             if (ok) nfail = 0;
         }
+#ifdef PYODESYS_COOP_TRACE
+        // debugging aid: one record of 12 doubles per attempt of system 0 at KernelArgs::root_out
+        if (s == 0 && g.gl == 0 && cnt.nsteps <= 4000) {
+            double *tr = a.root_out + 12 * (cnt.nsteps - 1);
+            tr[0] = t; tr[1] = hh; tr[2] = err; tr[3] = ok ? 1.0 : 0.0; tr[4] = bad; tr[5] = st.trace_order();
+            tr[6] = hnext; tr[7] = st.trace_flags();
+            for (int q = 0; q < 4; ++q) tr[8 + q] = st.trace_extra(q);
+        }
+#endif
         if (!ok) {
             cnt.nreject += 1;
             if (fabs(hnext) <= 16.0 * DBL_EPSILON * fabs(t) || fabs(hnext) == 0.0 || (hmin > 0.0 && fabs(hh) <= hmin))

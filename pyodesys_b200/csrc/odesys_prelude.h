@@ -58,6 +58,16 @@ ODESYS_FN double odesys_effective_rtol(int method, double rtol) {
 #ifndef ODESYS_BDF_REFRESH_JAC
 #define ODESYS_BDF_REFRESH_JAC 1
 #endif
+// Convergence tolerance of the simplified Newton iteration, in units of the local error tolerance (weighted rms
+// norm).  scipy's BDF uses min(0.03, sqrt(rtol)) - 3e-5 at the calibrated rtol of 1e-9 -, which is BELOW the rounding
+// floor of the corrections on kinetics networks: the residual c f(y) carries eps x (gross reaction rate) x c, and
+// on a species that is controlled by atol that is 1e-3 .. 1e-2 tolerance units once c = h / alpha reaches ~10
+// (radiolysis, t > 500: corrections stagnate at 7e-3, the rate test calls the iteration divergent, the step is
+// halved seven times, grows back and fails again - hundreds of rejections on 1-4 % of the systems).  CVODE asks
+// for 0.1; 0.03 keeps the algebraic error at 3 % of the tolerance and is above the floor.
+#ifndef ODESYS_BDF_NEWTON_TOL
+#define ODESYS_BDF_NEWTON_TOL 0.03
+#endif
 
 namespace AnyODE {
 enum Status : int { success = 0, recoverable_error = 1, unrecoverable_error = -1 };

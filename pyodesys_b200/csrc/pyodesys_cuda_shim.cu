@@ -795,8 +795,8 @@ static int integrate_predefined_impl(int device, int64_t n, int nt, const double
         a.y0 = y0; a.params = params; a.xout = xout; a.dx0 = dx0; a.dx_min = dx_min; a.dx_max = dx_max;
         a.yout = yout; a.nreached = nreached; a.status = status; a.counters = counters;
         if (want_roots(q)) { a.root_out = opt->root_out; a.root_indices = opt->root_indices; a.nroots_found = opt->nroots_found; }
-#ifdef PYODESYS_COOP_PROFILE
-        if (opt) a.root_out = opt->root_out;  // profiling build: phase counters land here
+#if defined(PYODESYS_COOP_PROFILE) || defined(PYODESYS_COOP_TRACE)
+        if (opt) a.root_out = opt->root_out;  // profiling / tracing build: phase counters or the step trace land here
 #endif
         if (a.work_counter) CU_CHECK(cudaMemsetAsync(a.work_counter, 0, sizeof(unsigned long long), stream));
         CU_CHECK(cudaEventRecord(c.ev[0], stream));

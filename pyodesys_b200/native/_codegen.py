@@ -182,6 +182,49 @@ def _accumulate_lines(cses, exprs, cc, prefix='acc', indent='        '):
     return lines, ['%s%d' % (prefix, i) for i in range(len(exprs))]
 
 
+
+EVAL_PARTS = 4       # the block-cooperative kernel has four warps: each evaluates one part
+EVAL_PARTS_MIN_NY = 9
+
+
+def _balanced_parts(nitems, part_cost, weights, nparts=EVAL_PARTS, sweeps=2):
+    """ Split ``range(nitems)`` into ``nparts`` groups that minimise the largest ``part_cost(group)`` (the operation
+    count of the group AFTER its own common-subexpression elimination: rows of a kinetics right-hand side share
+    their reaction rates, so the cost of a group is far from additive).  Greedy start by weight, then single-item
+    moves away from the most expensive group while that lowers the maximum. """
+    order = sorted(range(nitems), key=lambda i: -weights[i])
+    parts = [[] for _ in range(nparts)]
+    load = [0]*nparts
+    for i in order:
+        q = min(range(nparts), key=lambda k: load[k])
+        parts[q].append(i)
+        load[q] += weights[i]
+    cost = [part_cost(sorted(pt)) if pt else 0 for pt in parts]
+    for _ in range(sweeps):
+        improved = False
+        worst = max(range(nparts), key=lambda k: cost[k])
+        for i in list(parts[worst]):
+            if len(parts[worst]) <= 1:
+                break
+            c_without = part_cost(sorted(j for j in parts[worst] if j != i))
+            best = None
+            for q in range(nparts):
+                if q == worst:
+                    continue
+                c_with = part_cost(sorted(parts[q] + [i]))
+                if max(c_with, c_without) < cost[worst] and (best is None or c_with < best[1]):
+                    best = (q, c_with)
+            if best is not None:
+                parts[worst].remove(i)
+                parts[best[0]].append(i)
+                cost[worst], cost[best[0]] = c_without, best[1]
+                improved = True
+                break
+        if not improved:
+            break
+    return [sorted(pt) for pt in parts], cost
+
+
 def generate(odesys, namespace_override=None, namespace_extend=None):
     """ Build the header for ``odesys`` (a :class:`pyodesys_b200.symbolic.SymbolicSys`). """
     ns_over = dict(namespace_override or {})
@@ -356,6 +399,50 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         jac_sink_body = '\n'.join(_lazy_lines(jac_cses, outs, cc))
         jac_sink_body += '\n        this->njev++;\n        return AnyODE::Status::success;'
 
+    # ---- evaluation in EVAL_PARTS independent pieces (block-cooperative kernel: one piece per warp) -------------
+    # rows of f / columns of J are dealt to the parts so that the largest part - after its own CSE - is as small as
+    # possible; each part is a self-contained sink function that sets only its rows / columns
+    parts_rhs_body = parts_jac_body = None
+    eval_parts_cost = None
+    if (use_cse and ny >= EVAL_PARTS_MIN_NY and nj and 'p_rhs' not in ns_over and 'p_jac' not in ns_over and
+            os.getenv('PYODESYS_EVAL_PARTS', '1') == '1'):
+        f_common = common_exprs[:ny]
+        j_common = common_exprs[ny:ny + ny*ny]
+        d_common = common_exprs[ny + ny*ny:ny + nj]
+
+        def cost_rows(rows):
+            c, e2 = cse_cb([f_common[i] for i in rows], be.numbered_symbols('cse'))
+            return _count([e for _s, e in c] + list(e2))
+
+        def cost_cols(cols):
+            c, e2 = cse_cb([j_common[i*ny + j] for j in cols for i in range(ny)], be.numbered_symbols('cse'))
+            return _count([e for _s, e in c] + list(e2))
+
+        rparts, rcost = _balanced_parts(ny, cost_rows, [sympy.count_ops(e) + 1 for e in f_common])
+        cparts, ccost = _balanced_parts(ny, cost_cols,
+                                        [sum(sympy.count_ops(j_common[i*ny + j]) for i in range(ny)) + 1
+                                         for j in range(ny)])
+        eval_parts_cost = {'rhs': rcost, 'jac': ccost}
+        chunks_r, chunks_j = [], []
+        for q in range(EVAL_PARTS):
+            rows, cols = rparts[q], cparts[q]
+            c, e2 = cse_cb([f_common[i] for i in rows], be.numbered_symbols('cse'))
+            acc_lines, acc_names = _accumulate_lines(c, e2, cc, indent='            ')
+            body = acc_lines + ['            s.set(%d, %s);' % (i, nm) for i, nm in zip(rows, acc_names)]
+            chunks_r.append('        %sif constexpr (P == %d) {\n%s\n        }' % ('' if q == 0 else 'else ', q,
+                                                                                 '\n'.join(body)))
+            idx = [(i, j) for j in cols for i in range(ny)]
+            c, e2 = cse_cb([j_common[i*ny + j] for i, j in idx], be.numbered_symbols('cse'))
+            outs = [('s.setj(%d, %d, %%s);' % ij, e) for ij, e in zip(idx, e2)]
+            if q == 0:  # the time derivative goes with the first part
+                cd, ed = cse_cb(list(d_common), be.numbered_symbols('dcse'))
+                c = list(c) + list(cd)
+                outs += [('s.setdfdt(%d, %%s);' % i, e) for i, e in enumerate(ed)]
+            chunks_j.append('        %sif constexpr (P == %d) {\n%s\n        }' % (
+                '' if q == 0 else 'else ', q, '\n'.join(_lazy_lines(c, outs, cc, indent='            '))))
+        parts_rhs_body = '\n'.join(chunks_r) + '\n        return AnyODE::Status::success;'
+        parts_jac_body = '\n'.join(chunks_j) + '\n        return AnyODE::Status::success;'
+
     if 'p_first_step' in ns_over:
         fs_body = '        ' + ns_over['p_first_step']
         has_fs = True
@@ -429,6 +516,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         ('ODESYS_HAS_BOUNDS', int(lb is not None or ub is not None)),
         ('ODESYS_NONNEGATIVE', int(bool(getattr(odesys, '_nonnegative', False)))),
         ('ODESYS_NINVAR', ninvar), ('ODESYS_NNZ', nnz), ('ODESYS_HAS_JTIMES', int(has_jtimes)),
+        ('ODESYS_EVAL_PARTS', EVAL_PARTS if parts_rhs_body else 0),
     ]
     struct_body = '''
     int nfev, njev;
@@ -472,6 +560,18 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
         AnyODE::ignore(x); AnyODE::ignore(y);
 %(jac_sink)s
     }
+#if ODESYS_EVAL_PARTS > 0
+    // the same expressions dealt to ODESYS_EVAL_PARTS self-contained pieces: part P sets its rows of f / its columns
+    // of J only (the counters nfev / njev are left to the caller)
+    template <int P, class Sink> ODESYS_FN AnyODE::Status rhs_sink_part(double x, const double * const y, Sink &s) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(s);
+%(parts_rhs)s
+    }
+    template <int P, class Sink> ODESYS_FN AnyODE::Status dense_jac_sink_part(double x, const double * const y, Sink &s) {
+        AnyODE::ignore(x); AnyODE::ignore(y); AnyODE::ignore(s);
+%(parts_jac)s
+    }
+#endif
     // template:127-133 - number of stored Jacobian entries, -1 for dense storage
     ODESYS_FN int get_nnz() const { return ODESYS_NNZ; }
 #if ODESYS_NNZ >= 0
@@ -536,7 +636,7 @@ def generate(odesys, namespace_override=None, namespace_extend=None):
     }
 #endif
 ''' % dict(csc=csc_body, jtimes=jtimes_body, invar=invar_body, bounds=bounds_body, setup='\n'.join(setup_lines), rhs=rhs_body, jac=jac_body,
-           rhs_sink=rhs_sink_body, jac_sink=jac_sink_body, fs=fs_body, dxmax=dxmax_body, roots=roots_body)
+           rhs_sink=rhs_sink_body, jac_sink=jac_sink_body, parts_rhs=parts_rhs_body or '', parts_jac=parts_jac_body or '', fs=fs_body, dxmax=dxmax_body, roots=roots_body)
 
     text = '''// -*- mode: read-only -*-
 // Generated by pyodesys_b200.native._codegen (CUDA counterpart of
