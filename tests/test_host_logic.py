@@ -313,3 +313,30 @@ def test_linear_solver_names_of_the_cvode_wrapper():
     # the slot that was ``reserved`` in ABI v3 keeps its offset (old callers passed 0 = dense)
     assert Options.linear_solver.offset == Options.max_roots.offset + 4
     assert Options.root_out.offset == Options.linear_solver.offset + 4
+
+
+def test_eval_parts_cover_every_row_and_column_once():
+    """ the four evaluation pieces of the block-cooperative kernel (``_codegen._balanced_parts``): every row of f and
+    every column of J is set by exactly one piece, the largest piece is well below the whole """
+    import re
+    from pyodesys_b200 import systems
+    from pyodesys_b200.native import _codegen
+    gen = systems.radiolysis(compile=False)._native.gen
+    txt = gen.text
+    assert '#define ODESYS_EVAL_PARTS 4' in txt
+    ny = gen.ny
+    body = txt[txt.index('rhs_sink_part'):txt.index('dense_jac_sink_part')]
+    rows = [int(m) for m in re.findall(r's\.set\((\d+),', body)]
+    assert sorted(rows) == list(range(ny))
+    jbody = txt[txt.index('dense_jac_sink_part'):]
+    jbody = jbody[:jbody.index('#endif')]
+    ent = re.findall(r's\.setj\((\d+), (\d+),', jbody)
+    assert len(ent) == ny*ny and len(set(ent)) == ny*ny
+    parts = [jbody.split('if constexpr (P == %d)' % q)[1].split('if constexpr')[0] for q in range(4)]
+    cols = [set(int(j) for _i, j in re.findall(r's\.setj\((\d+), (\d+),', pt)) for pt in parts]
+    assert all(cols[a].isdisjoint(cols[b]) for a in range(4) for b in range(a)) and set.union(*cols) == set(range(ny))
+    # small systems keep the single-piece evaluation
+    assert '#define ODESYS_EVAL_PARTS 0' in systems.robertson(compile=False)._native.gen.text
+    # the partition helper itself: additive costs -> a balanced split
+    pts, cost = _codegen._balanced_parts(8, lambda items: len(items), [1]*8)
+    assert sorted(i for pt in pts for i in pt) == list(range(8)) and max(len(pt) for pt in pts) == 2
