@@ -407,19 +407,22 @@ template <bool KRYLOV> struct BdfStepper {
         jac_current = false;
         n_equal += 1;
         // D[order+2] = d - D[order+1]; D[order+1] = d; D[j] += D[j+1] for j = order..0
-        // (shared memory is addressed by the order directly; the running sum stays in a register)
+        // (shared memory is addressed by the order directly; the running sums stay in registers)
+        double carry[NY];
 #pragma unroll
         for (int i = 0; i < NY; ++i) {
             const double di = d[i];
             Dx(order + 2, i) = di - Dx(order + 1, i);
             Dx(order + 1, i) = di;
-            double carry = di;
+            carry[i] = di;
+        }
 #pragma unroll
-            for (int j = bdfc::MAXORD; j >= 0; --j) {
-                const double nv = carry + Dx(j, i);
-                if (j <= order) {
-                    Dx(j, i) = nv;
-                    carry = nv;
+        for (int j = bdfc::MAXORD; j >= 0; --j) {
+            if (j <= order) {  // one (mostly warp-uniform) branch per row instead of selects per element
+#pragma unroll
+                for (int i = 0; i < NY; ++i) {
+                    carry[i] += Dx(j, i);
+                    Dx(j, i) = carry[i];
                 }
             }
         }
