@@ -89,6 +89,9 @@ struct DevCtx {
     int64_t compact_rows = 0;  // rows left in buf[B_COMPACT] by the last compacting adaptive call
 };
 constexpr int kMaxSlices = 64;
+#ifndef PYODESYS_CUDA_SLICE_MB_DEFAULT
+#define PYODESYS_CUDA_SLICE_MB_DEFAULT 8.0
+#endif
 constexpr int kLanes = 2;  // independent call contexts per device (options.ctx_lane): two host threads can keep one GPU busy
 DevCtx g_ctx[kMaxDev][kLanes];
 int lane_of(const pyodesys_cuda_options *opt) { return (opt && opt->ctx_lane > 0 && opt->ctx_lane < kLanes) ? opt->ctx_lane : 0; }
@@ -513,8 +516,19 @@ struct SlicePlan {
     int64_t size(int j, int64_t total) const { return (j + 1) * len > total ? total - j * len : len; }
 };
 
+// bytes of output per slice of the streaming launch: what stays exposed at the end of a call is the device-to-host
+// copy of the slices that complete last (PYODESYS_CUDA_SLICE_MB overrides)
+size_t slice_bytes() {
+    static const size_t v = [] {
+        const char *e = getenv("PYODESYS_CUDA_SLICE_MB");
+        const double mb = e ? atof(e) : 0.0;
+        return (size_t)((mb >= 0.25 && mb <= 1024.0 ? mb : PYODESYS_CUDA_SLICE_MB_DEFAULT) * (1u << 20));
+    }();
+    return v;
+}
+
 SlicePlan plan_slices(int64_t n, size_t out_bytes_per_system) {
-    int64_t len = (int64_t)((size_t)(16u << 20) / (out_bytes_per_system ? out_bytes_per_system : 1));
+    int64_t len = (int64_t)(slice_bytes() / (out_bytes_per_system ? out_bytes_per_system : 1));
     const int64_t lo = std::max<int64_t>(16384, (n + kMaxSlices - 1) / kMaxSlices), hi = (n + 7) / 8;
     if (len > hi) len = hi;
     if (len < lo) len = lo;
