@@ -154,6 +154,20 @@ int pyodesys_cuda_integrate_predefined(
     double *timings,       /* [PYODESYS_CUDA_NTIMINGS] host, or NULL */
     int ptr_kind, const pyodesys_cuda_options *options);
 
+/* The predefined-mode call over SEVERAL devices (host pointers; ABI v4).  Role in the reference: the OpenMP loop of
+ * multi_predefined (call sites _cvode_wrapper.pyx:339-345, _odeint_wrapper.pyx:163-166) - a bag of tasks over the
+ * systems, here over chunks of ``chunk`` systems and over devices: ``lanes`` (1 or 2) host threads per entry of
+ * ``devices`` draw chunk numbers from one atomic counter and run the single-device path on their window of the
+ * caller's arrays (counters: column windows of [NCOUNTERS, n]); each thread is bound to the CPUs of its GPU's NUMA
+ * node.  No collective, no gather.  busy_s[ndev] / chunks_taken[ndev] (may be NULL) report the schedule.  Results
+ * are those of the single-device call bit for bit.  Event functions are not routed through this entry point. */
+int pyodesys_cuda_integrate_predefined_multi(
+    const int *devices, int ndev, int lanes, int64_t chunk, int64_t n, int nt,
+    const double *y0, const double *xout, const double *params, const double *atol, int natol, double rtol,
+    const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps, int method, int autorestart,
+    int return_on_error, double *yout, int32_t *nreached, int32_t *status, int32_t *counters,
+    double *busy_s, int32_t *chunks_taken, const pyodesys_cuda_options *options);
+
 int pyodesys_cuda_integrate_adaptive(
     int device, int64_t n,
     const double *y0, const double *x0 /* [n] */, const double *xend /* [n] */,

@@ -33,6 +33,9 @@
 #include "pyodesys_cuda.h"
 
 #include <algorithm>
+#include <ctype.h>
+#include <sched.h>
+#include <string>
 #include <vector>
 #include <atomic>
 #include <thread>
@@ -1181,6 +1184,118 @@ int pyodesys_cuda_integrate_predefined(int device, int64_t n, int nt, const doub
                                              counters, timings, ptr_kind, opt);
     if (rc != 0) drain_after_failure(device);
     return rc;
+}
+
+// ---- several devices from one call -------------------------------------------------------------
+// The batch is cut into chunks of ``chunk`` systems; ``lanes`` host threads per device (each with its own call
+// context: streams + staging buffers) draw chunk numbers from one atomic counter - whichever lane is free takes the
+// next chunk, so devices and lanes that run ahead (stiffness varies with the parameters) simply take more - and run
+// the ordinary host-pointer path on their window of the caller's arrays.  Every thread is bound to the CPUs of its
+// GPU's NUMA node.  No collective, no gather: the device-to-host copies land in the caller's arrays.
+static bool local_cpus_of(int device, cpu_set_t *set) {
+    char bus[32] = "";
+    if (cudaDeviceGetPCIBusId(bus, (int)sizeof(bus), device) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    for (char *q = bus; *q; ++q) *q = (char)tolower(*q);
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/local_cpulist", bus);
+    FILE *fh = fopen(path, "r");
+    if (!fh) return false;
+    char line[4096] = "";
+    const bool got = fgets(line, sizeof(line), fh) != nullptr;
+    fclose(fh);
+    if (!got) return false;
+    CPU_ZERO(set);
+    int count = 0;
+    for (char *tok = strtok(line, ",\n"); tok; tok = strtok(nullptr, ",\n")) {
+        int lo = 0, hi = 0;
+        const int k = sscanf(tok, "%d-%d", &lo, &hi);
+        if (k < 1) continue;
+        if (k == 1) hi = lo;
+        for (int cpu = lo; cpu <= hi && cpu < CPU_SETSIZE; ++cpu) {
+            CPU_SET(cpu, set);
+            ++count;
+        }
+    }
+    return count > 0;
+}
+
+int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int lanes, int64_t chunk, int64_t n, int nt,
+                                             const double *y0, const double *xout, const double *params,
+                                             const double *atol, int natol, double rtol, const double *dx0,
+                                             const double *dx_min, const double *dx_max, int64_t mxsteps, int method,
+                                             int autorestart, int return_on_error, double *yout, int32_t *nreached,
+                                             int32_t *status, int32_t *counters, double *busy_s, int32_t *chunks_taken,
+                                             const pyodesys_cuda_options *opt) {
+    if (!devices || ndev < 1 || ndev > kMaxDev) return fail("invalid device list (ndev=%d)", ndev);
+    if (lanes < 1 || lanes > kLanes) return fail("lanes must be 1..%d, got %d", kLanes, lanes);
+    if (chunk < 1 || n < 0 || nt < 1) return fail("invalid sizes (n=%lld, chunk=%lld, nt=%d)", (long long)n, (long long)chunk, nt);
+    if (opt && (opt->max_roots > 0 || opt->root_out)) return fail("event functions are not routed through the multi-device entry point");
+    for (int d = 0; d < ndev; ++d)
+        if (devices[d] < 0 || devices[d] >= kMaxDev) return fail("invalid device %d", devices[d]);
+    const int nworkers = ndev * lanes;
+    for (int d = 0; d < ndev; ++d) {
+        if (busy_s) busy_s[d] = 0.0;
+        if (chunks_taken) chunks_taken[d] = 0;
+    }
+    if (n == 0) return 0;
+    pyodesys_cuda_options base;
+    memset(&base, 0, sizeof(base));
+    if (opt) base = *opt;
+    const bool shared_x = base.xout_shared != 0;
+    const int64_t prow = base.params_ld > 0 ? base.params_ld : (base.iv_from_y0 ? ODESYS_NPARAMS : NP_TOT);
+    const int64_t nchunks = (n + chunk - 1) / chunk;
+    std::atomic<int64_t> next{0};
+    std::atomic<int> failed{0};
+    std::vector<std::string> errs((size_t)nworkers);
+    std::vector<double> busy((size_t)nworkers, 0.0);
+    std::vector<int> taken((size_t)nworkers, 0);
+    auto work = [&](int w) {
+        const int dev = devices[w / lanes], lane = w % lanes;
+        cpu_set_t cpus;
+        if (local_cpus_of(dev, &cpus)) sched_setaffinity(0, sizeof(cpus), &cpus);  // this thread only
+        pyodesys_cuda_options o = base;
+        o.ctx_lane = lane;
+        o.counters_ld = n;  // the caller's [NCOUNTERS, n] array: this call fills a column window
+        while (!failed.load(std::memory_order_relaxed)) {
+            const int64_t k = next.fetch_add(1);
+            if (k >= nchunks) break;
+            const int64_t lo = k * chunk, len = std::min<int64_t>(chunk, n - lo);
+            double tm[PYODESYS_CUDA_NTIMINGS] = {0, 0, 0, 0};
+            const int rc = integrate_predefined_impl(
+                dev, len, nt, y0 + lo * NY, shared_x ? xout : xout + lo * nt, params ? params + lo * prow : nullptr, atol,
+                natol, rtol, dx0 ? dx0 + lo : nullptr, dx_min ? dx_min + lo : nullptr, dx_max ? dx_max + lo : nullptr,
+                mxsteps, method, autorestart, return_on_error, yout + lo * (int64_t)nt * NY, nreached + lo, status + lo,
+                counters ? counters + lo : nullptr, tm, 0, &o);
+            if (rc != 0) {
+                errs[(size_t)w] = g_err;  // thread-local text of THIS thread
+                failed.store(1);
+                break;
+            }
+            busy[(size_t)w] += tm[PYODESYS_CUDA_T_TOTAL];
+            taken[(size_t)w] += 1;
+        }
+    };
+    std::vector<std::thread> threads;
+    for (int w = 1; w < nworkers; ++w) threads.emplace_back(work, w);
+    cpu_set_t mine;
+    const bool have_mine = sched_getaffinity(0, sizeof(mine), &mine) == 0;
+    work(0);  // the calling thread is worker 0; its CPU binding is restored afterwards
+    if (have_mine) sched_setaffinity(0, sizeof(mine), &mine);
+    for (auto &t : threads) t.join();
+    for (int w = 0; w < nworkers; ++w) {
+        if (busy_s) busy_s[w / lanes] += busy[(size_t)w];
+        if (chunks_taken) chunks_taken[w / lanes] += taken[(size_t)w];
+    }
+    if (failed.load()) {
+        for (int d = 0; d < ndev; ++d) drain_after_failure(devices[d]);
+        for (const auto &e : errs)
+            if (!e.empty()) return fail("%s", e.c_str());
+        return fail("a device thread failed");
+    }
+    return 0;
 }
 
 int pyodesys_cuda_integrate_adaptive(int device, int64_t n, const double *y0, const double *x0, const double *xend,

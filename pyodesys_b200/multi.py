@@ -80,12 +80,20 @@ def gpu_cpu_affinity(device, lib=None):
     return cpus
 
 
-def chunk_size(n, ndevices, target=250000, minimum=32768):
-    """ Chunk length of the dynamic schedule: about ``target`` systems, at least four chunks per device when the batch
-    allows it (so that a slow chunk does not leave the other GPUs idle at the end), never below ``minimum`` (a persistent
-    grid of 148 SMs x 4 blocks x 128 lanes holds 75776 systems in flight), a multiple of 1024. """
-    per = -(-n // max(1, 4*ndevices))
-    c = max(minimum, min(target, per))
+def chunk_size(n, ndevices, target=1000000, minimum=32768):
+    """ Chunk length of the multi-device schedule.  A chunk is one call of the single-device path, which overlaps its
+    own copies with its kernel (streaming launch) and ends in the ~1 ms makespan tail of one-system-per-thread
+    scheduling, so chunks are made LARGE: measured on two GPUs (``scripts/sharded_chunks.py``) 2e6 systems take 16.9
+    ms in chunks of 1e6 against 18.8 ms in chunks of 2.5e5, 2e7 systems 160 against 178 ms.  Rule: a batch of fewer
+    than two ``target``-sized chunks per device is dealt in equal shares (one call per device); a larger one is cut
+    into chunks of ``target`` systems that the device lanes draw dynamically (a slow chunk - stiffness varies with the
+    parameters - then does not leave the other GPUs idle at the end).  Never below ``minimum`` unless the batch is
+    smaller, a multiple of 1024. """
+    g = max(1, ndevices)
+    if n < 2*target*g:
+        c = max(min(minimum, n), -(-n // g))
+    else:
+        c = target
     if c >= n:
         return n
     return -(-c // 1024)*1024
@@ -108,7 +116,7 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
     kw.pop('device', None)
     csize = int(kw.pop('shard_chunk', 0)) or chunk_size(n, g)
     nchunks = -(-n // csize) if n else 0
-    lanes = 2 if nchunks >= 2*g else 1
+    lanes = 2 if nchunks > g else 1  # more than one chunk per device: two call contexts keep a kernel running
     roots = kw.pop('roots_sink', None)
     return_on_root, max_roots = kw.pop('return_on_root', False), int(kw.pop('max_roots', 8))
     root_arrays = None
@@ -129,6 +137,24 @@ def integrate_sharded(mod, devices, intern_x, y0, params, force_predefined, atol
         nt = xout.shape[-1]
         yout = mod.pinned.empty((n, nt, ny), np.float64)
         nreached = mod.pinned.empty((n,), np.int32)
+
+    if not adaptive and root_arrays is None and os.environ.get('PYODESYS_SHARDED_NATIVE', '1') == '1':
+        # predefined output, no event functions: ONE call; chunk scheduling, device threads and NUMA binding are
+        # native (pyodesys_cuda_integrate_predefined_multi) - per-chunk Python work under the GIL cost ~4 ms per call
+        kwn = dict(kw)
+        kwn.pop('ctx_lane', None)
+        yout, nreached, status, counters, busy_d, taken_d = mod.integrate_predefined_multi(
+            devices, lanes, csize, y0, xout, params, atol, rtol, dx0=first_step, mxsteps=nsteps,
+            out=(yout, nreached, status, counters), **kwn)
+        binfo = BatchInfo('predefined', status, nreached, counters, 0.0, 0.0, intern_x, yout, params,
+                          kwargs.get('return_on_error', False), nt=nt,
+                          timings=_tdict(np.array([float(busy_d.max())/max(lanes, 1), 0.0, 0.0, float(busy_d.max())/max(lanes, 1)])),
+                          method=kwargs.get('method') or mod.default_method(),
+                          iv=y0 if kwargs.get('iv_from_y0', False) else None)
+        binfo.shard_stats = {"chunk": int(csize), "chunks": int(nchunks), "lanes_per_device": lanes, "driver": "native",
+                             "chunks_per_device": [int(v) for v in taken_d],
+                             "busy_s_per_device": [float(v) for v in busy_d]}
+        return binfo
 
     draw = itertools.count()  # the shared chunk counter: next() is atomic under the GIL
     nworkers = g*lanes

@@ -225,6 +225,11 @@ class CudaModule:
         lib.pyodesys_cuda_device_pci_bus_id.restype = ctypes.c_int
         lib.pyodesys_cuda_device_pci_bus_id.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
         lib.pyodesys_cuda_device_count.restype = ctypes.c_int
+        lib.pyodesys_cuda_integrate_predefined_multi.restype = ctypes.c_int
+        lib.pyodesys_cuda_integrate_predefined_multi.argtypes = [
+            ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_int,
+            _d, _d, _d, _d, ctypes.c_int, ctypes.c_double, _d, _d, _d, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+            ctypes.c_int, _d, _i32, _i32, _i32, _d, _i32, ctypes.c_void_p]
         lib.pyodesys_cuda_compact_rows_noalloc.restype = ctypes.c_int
         lib.pyodesys_cuda_compact_rows_noalloc.argtypes = [
             ctypes.c_int, ctypes.c_int64, ctypes.c_int64, _d, _i32, ctypes.POINTER(ctypes.c_int64), _d,
@@ -376,6 +381,36 @@ class CudaModule:
         self._check(rc)
         _check_nan_y0(y0, status)
         return yout, nreached, status, counters, timings
+
+    def integrate_predefined_multi(self, devices, lanes, chunk, y0, xout, params, atol, rtol, dx0=None, dx_min=None,
+                                   dx_max=None, mxsteps=0, method=None, autorestart=0, return_on_error=False,
+                                   special_settings=None, out=None, **kw):
+        """ ``pyodesys_cuda_integrate_predefined_multi``: the whole batch in ONE call, scheduled natively over
+        ``devices`` (``lanes`` host threads per device draw chunks of ``chunk`` systems from an atomic counter).
+        Returns ``(yout, nreached, status, counters, busy_s[ndev], chunks_taken[ndev])``; all outputs page-locked. """
+        y0, params, atol, dx0, dx_min, dx_max, mid, n = self._prep(y0, params, atol, dx0, dx_min, dx_max, method,
+                                                                   kw.get('iv_from_y0', False))
+        xout = np.ascontiguousarray(xout, dtype=np.float64)
+        shared = xout.ndim == 1
+        if not shared and xout.shape[0] != n:
+            raise ValueError("xout needs to be of shape (N, nt)")
+        nt = xout.shape[-1]
+        opts = self._options(xout_shared=shared, **kw)
+        if out is None:
+            out = (self.pinned.empty((n, nt, self.ny), np.float64), self.pinned.empty((n,), np.int32),
+                   self.pinned.empty((n,), np.int32), self.pinned.empty((NCOUNTERS, n), np.int32))
+        yout, nreached, status, counters = out
+        devs = (ctypes.c_int*len(devices))(*[int(d) for d in devices])
+        busy = np.zeros(len(devices))
+        taken = np.zeros(len(devices), dtype=np.int32)
+        rc = self.lib.pyodesys_cuda_integrate_predefined_multi(
+            devs, len(devices), int(lanes), int(chunk), n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size,
+            float(rtol), _ptr(dx0), _ptr(dx_min), _ptr(dx_max), int(mxsteps), mid, int(autorestart), int(return_on_error),
+            _ptr(yout), _ptr(nreached, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(busy), _ptr(taken, _i32),
+            ctypes.cast(ctypes.byref(opts), ctypes.c_void_p))
+        self._check(rc)
+        _check_nan_y0(y0, status)
+        return yout, nreached, status, counters, busy, taken
 
     def integrate_adaptive_arrays(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
                                   mxsteps=0, method=None, autorestart=0, return_on_error=False,
