@@ -613,7 +613,13 @@ def sharded_arm(args, wl, dist, rank, world):
     # are time-sliced - rank 0's kernels on device r would get half of it (measured: 2.2x slower chunks on device 1).
     # Hence a CPU-side (gloo) barrier, after every rank has drained its own device.
     torch.cuda.synchronize()
-    cpu_group = dist.new_group(backend='gloo')
+    os.environ.setdefault('GLOO_SOCKET_IFNAME', 'lo')  # single node: the container's hostname may not resolve
+    try:
+        cpu_group = dist.new_group(backend='gloo')
+    except Exception as e:  # no gloo transport: fall back to the NCCL barrier (the waiting GPUs are then time-sliced)
+        print("bench.py: gloo group unavailable (%s): the sharded arm runs against NCCL barrier kernels" % e,
+              file=sys.stderr)
+        cpu_group = None
     dist.barrier(group=cpu_group)
     if rank == 0:
         os.sched_setaffinity(0, range(os.cpu_count() or 1))  # this arm drives every GPU: undo the per-rank binding
