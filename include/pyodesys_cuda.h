@@ -166,7 +166,8 @@ int pyodesys_cuda_integrate_predefined_multi(
     const double *y0, const double *xout, const double *params, const double *atol, int natol, double rtol,
     const double *dx0, const double *dx_min, const double *dx_max, int64_t mxsteps, int method, int autorestart,
     int return_on_error, double *yout, int32_t *nreached, int32_t *status, int32_t *counters,
-    double *busy_s, int32_t *chunks_taken, const pyodesys_cuda_options *options);
+    double *busy_s, int32_t *chunks_taken, int64_t *nfailed /* systems with status != 0, or NULL */,
+    const pyodesys_cuda_options *options);
 
 int pyodesys_cuda_integrate_adaptive(
     int device, int64_t n,

@@ -1228,7 +1228,8 @@ int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int l
                                              const double *dx_min, const double *dx_max, int64_t mxsteps, int method,
                                              int autorestart, int return_on_error, double *yout, int32_t *nreached,
                                              int32_t *status, int32_t *counters, double *busy_s, int32_t *chunks_taken,
-                                             const pyodesys_cuda_options *opt) {
+                                             int64_t *nfailed, const pyodesys_cuda_options *opt) {
+    if (nfailed) *nfailed = 0;
     if (!devices || ndev < 1 || ndev > kMaxDev) return fail("invalid device list (ndev=%d)", ndev);
     if (lanes < 1 || lanes > kLanes) return fail("lanes must be 1..%d, got %d", kLanes, lanes);
     if (chunk < 1 || n < 0 || nt < 1) return fail("invalid sizes (n=%lld, chunk=%lld, nt=%d)", (long long)n, (long long)chunk, nt);
@@ -1252,10 +1253,16 @@ int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int l
     std::vector<std::string> errs((size_t)nworkers);
     std::vector<double> busy((size_t)nworkers, 0.0);
     std::vector<int> taken((size_t)nworkers, 0);
+    std::atomic<int64_t> bad_systems{0};
+    const double t_entry = now_s();
+    const bool trace = getenv("PYODESYS_CUDA_MULTI_TRACE") != nullptr;
     auto work = [&](int w) {
         const int dev = devices[w / lanes], lane = w % lanes;
+        const double t_thread = now_s();
         cpu_set_t cpus;
         if (local_cpus_of(dev, &cpus)) sched_setaffinity(0, sizeof(cpus), &cpus);  // this thread only
+        const double t_bound = now_s();
+        double t_first = 0.0;
         pyodesys_cuda_options o = base;
         o.ctx_lane = lane;
         o.counters_ld = n;  // the caller's [NCOUNTERS, n] array: this call fills a column window
@@ -1276,7 +1283,17 @@ int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int l
             }
             busy[(size_t)w] += tm[PYODESYS_CUDA_T_TOTAL];
             taken[(size_t)w] += 1;
+            if (taken[(size_t)w] == 1) t_first = now_s();
+            if (nfailed) {  // the caller's screen for failed systems, done here by all workers in parallel
+                int64_t bad = 0;
+                for (int64_t i = lo; i < lo + len; ++i) bad += status[i] != 0;
+                if (bad) bad_systems.fetch_add(bad);
+            }
         }
+        if (trace)
+            fprintf(stderr, "multi: worker %d (device %d lane %d): started +%.3f ms, bound +%.3f, first chunk done +%.3f, "
+                    "exit +%.3f, busy %.3f ms, %d chunks\n", w, dev, lane, 1e3 * (t_thread - t_entry), 1e3 * (t_bound - t_entry),
+                    1e3 * (t_first - t_entry), 1e3 * (now_s() - t_entry), 1e3 * busy[(size_t)w], taken[(size_t)w]);
     };
     std::vector<std::thread> threads;
     for (int w = 1; w < nworkers; ++w) threads.emplace_back(work, w);
@@ -1289,6 +1306,7 @@ int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int l
         if (busy_s) busy_s[w / lanes] += busy[(size_t)w];
         if (chunks_taken) chunks_taken[w / lanes] += taken[(size_t)w];
     }
+    if (nfailed) *nfailed = bad_systems.load();
     if (failed.load()) {
         for (int d = 0; d < ndev; ++d) drain_after_failure(devices[d]);
         for (const auto &e : errs)

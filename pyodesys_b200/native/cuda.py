@@ -229,7 +229,7 @@ class CudaModule:
         lib.pyodesys_cuda_integrate_predefined_multi.argtypes = [
             ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_int,
             _d, _d, _d, _d, ctypes.c_int, ctypes.c_double, _d, _d, _d, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
-            ctypes.c_int, _d, _i32, _i32, _i32, _d, _i32, ctypes.c_void_p]
+            ctypes.c_int, _d, _i32, _i32, _i32, _d, _i32, ctypes.POINTER(ctypes.c_int64), ctypes.c_void_p]
         lib.pyodesys_cuda_compact_rows_noalloc.restype = ctypes.c_int
         lib.pyodesys_cuda_compact_rows_noalloc.argtypes = [
             ctypes.c_int, ctypes.c_int64, ctypes.c_int64, _d, _i32, ctypes.POINTER(ctypes.c_int64), _d,
@@ -403,13 +403,14 @@ class CudaModule:
         devs = (ctypes.c_int*len(devices))(*[int(d) for d in devices])
         busy = np.zeros(len(devices))
         taken = np.zeros(len(devices), dtype=np.int32)
+        nbad = ctypes.c_int64(0)
         rc = self.lib.pyodesys_cuda_integrate_predefined_multi(
             devs, len(devices), int(lanes), int(chunk), n, nt, _ptr(y0), _ptr(xout), _ptr(params), _ptr(atol), atol.size,
             float(rtol), _ptr(dx0), _ptr(dx_min), _ptr(dx_max), int(mxsteps), mid, int(autorestart), int(return_on_error),
             _ptr(yout), _ptr(nreached, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(busy), _ptr(taken, _i32),
-            ctypes.cast(ctypes.byref(opts), ctypes.c_void_p))
+            ctypes.byref(nbad), ctypes.cast(ctypes.byref(opts), ctypes.c_void_p))
         self._check(rc)
-        _check_nan_y0(y0, status)
+        _check_nan_y0(y0, status, nbad=int(nbad.value))
         return yout, nreached, status, counters, busy, taken
 
     def integrate_adaptive_arrays(self, y0, x0, xend, params, atol, rtol, dx0=None, dx_min=None, dx_max=None,
@@ -679,9 +680,11 @@ def root_info(roots, i, mode):
 _screen_memo = threading.local()
 
 
-def _check_nan_y0(y0, status):
-    """ deferred NaN screen of large batches: only rows the kernel rejected are looked at """
-    nbad = int(np.count_nonzero(status))  # one SIMD pass, 0.25 ms per 1e6 systems
+def _check_nan_y0(y0, status, nbad=None):
+    """ deferred NaN screen of large batches: only rows the kernel rejected are looked at.  ``nbad``: the number of
+    failed systems where the library counted them already (multi-device entry point) """
+    if nbad is None:
+        nbad = int(np.count_nonzero(status))  # one SIMD pass, 0.25 ms per 1e6 systems
     _screen_memo.last = (status, nbad)
     if y0.size <= (1 << 16) or not nbad:
         return
