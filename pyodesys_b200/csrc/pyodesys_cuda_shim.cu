@@ -33,6 +33,7 @@
 #include "pyodesys_cuda.h"
 
 #include <algorithm>
+#include <exception>
 #include <ctype.h>
 #include <sched.h>
 #include <string>
@@ -1209,7 +1210,8 @@ static bool local_cpus_of(int device, cpu_set_t *set) {
     if (!got) return false;
     CPU_ZERO(set);
     int count = 0;
-    for (char *tok = strtok(line, ",\n"); tok; tok = strtok(nullptr, ",\n")) {
+    char *save = nullptr;  // (strtok_r: several device threads parse their lists at the same time)
+    for (char *tok = strtok_r(line, ",\n", &save); tok; tok = strtok_r(nullptr, ",\n", &save)) {
         int lo = 0, hi = 0;
         const int k = sscanf(tok, "%d-%d", &lo, &hi);
         if (k < 1) continue;
@@ -1296,7 +1298,11 @@ int pyodesys_cuda_integrate_predefined_multi(const int *devices, int ndev, int l
                     1e3 * (t_first - t_entry), 1e3 * (now_s() - t_entry), 1e3 * busy[(size_t)w], taken[(size_t)w]);
     };
     std::vector<std::thread> threads;
-    for (int w = 1; w < nworkers; ++w) threads.emplace_back(work, w);
+    try {
+        for (int w = 1; w < nworkers; ++w) threads.emplace_back(work, w);
+    } catch (const std::exception &e) {  // no more threads: the workers that exist (and this thread) do all the chunks
+        if (trace) fprintf(stderr, "multi: %s after %zu threads\n", e.what(), threads.size());
+    }
     cpu_set_t mine;
     const bool have_mine = sched_getaffinity(0, sizeof(mine), &mine) == 0;
     work(0);  // the calling thread is worker 0; its CPU binding is restored afterwards
