@@ -438,6 +438,7 @@ def _main():
     sampler.mark()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kernel_s = 0.0
+    launches_t0 = mod.launch_count()
     for k in range(args.steps):
         flush.fill_(k)  # L2 flush, outside the event bracket
         ev[k][0].record(stream)
@@ -445,6 +446,7 @@ def _main():
         ev[k][1].record(stream)
         kernel_s += tm[0]
     torch.cuda.synchronize(dev)
+    launches_timed = mod.launch_count() - launches_t0  # this library's kernels inside the timed region
     if world > 1:
         dist.barrier()
     total_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
@@ -560,10 +562,12 @@ def _main():
         e2e_pass()
     if world > 1:
         dist.barrier()
+    launches_e0 = mod.launch_count()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         last, d2h_bytes, phases = e2e_pass()
     e2e_s = time.perf_counter() - t0
+    launches_e2e = mod.launch_count() - launches_e0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -571,7 +575,7 @@ def _main():
     h2d = n*(ny + wl.nparams)*8 + (n*2*8 if wl.adaptive else nt*8*(-(-n//ch)))
     e2e = {"value": n*world*e2e_steps/e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
            "d2h_bytes_per_step": int(d2h_bytes), "steps": e2e_steps, "ms_per_step": 1e3*e2e_s/e2e_steps,
-           "phases_ms": phases, "calls_per_step": -(-n//ch),
+           "phases_ms": phases, "calls_per_step": -(-n//ch), "gpu_launches": int(launches_e2e),
            "api": "NativeCudaSys.integrate(x, y0[N,%d], params[N,%d], atol, rtol, nsteps%s)" % (
                ny, wl.nparams, "" if wl.adaptive else ", force_predefined=True")}
     check["last"] = last
@@ -595,7 +599,7 @@ def _main():
                 "warmup": args.warmup, "ms_per_step": total_ms/args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": wl.config(args), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "gpu_launches": int(launches), "clocks": clocks, "check": check, "cpu_affinity": affinity}
+                "gpu_launches": int(launches_timed), "gpu_launches_whole_run": int(launches), "clocks": clocks, "check": check, "cpu_affinity": affinity}
         if sharded is not None:
             line["sharded"] = sharded
     if world > 1:
