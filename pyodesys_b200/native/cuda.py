@@ -379,7 +379,8 @@ class CudaModule:
             _ptr(yout), _ptr(nreached, _i32), _ptr(status, _i32), _ptr(counters, _i32), _ptr(timings), 0,
             ctypes.byref(opts))
         self._check(rc)
-        _check_nan_y0(y0, status)
+        nbad = int(self.lib.pyodesys_cuda_query(b'last_failed_systems'))  # counted while the call waited (or -1)
+        _check_nan_y0(y0, status, nbad=nbad if nbad >= 0 else None)
         return yout, nreached, status, counters, timings
 
     def integrate_predefined_multi(self, devices, lanes, chunk, y0, xout, params, atol, rtol, dx0=None, dx_min=None,
