@@ -133,7 +133,10 @@ typedef struct pyodesys_cuda_options {
 /* Compile-time facts of the system this library was generated for. Any pointer may be NULL. */
 int pyodesys_cuda_info(int *ny, int *np_tot, int *npcse, int *flops_rhs, int *flops_jac);
 
-/* abi version, warp-per-system flag, etc.: key/value lookup; returns -1 for unknown keys */
+/* abi version, warp-per-system flag, etc.: key/value lookup; returns -1 for unknown keys.  One key is dynamic:
+ * "last_failed_systems" = number of systems with status != 0 in the last integrate call of the CALLING THREAD where
+ * the library counted them while it waited for the device (streaming predefined calls), else -1 - the role of the
+ * ``success`` scan the reference's wrappers do per system (_odeint_wrapper.pyx:169-173). */
 int64_t pyodesys_cuda_query(const char *key);
 
 int pyodesys_cuda_integrate_predefined(
