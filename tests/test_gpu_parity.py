@@ -625,9 +625,14 @@ def test_streaming_call_is_invisible(cuda_device, monkeypatch):
     kw = dict(atol=b['atol'], rtol=b['rtol'], nsteps=3000, method='rosenbrock4', force_predefined=True,
               return_on_error=True, first_step=np.linspace(1e-6, 1e-5, n))
     out = {}
+    lib = rob._native.mod.lib
     for flag in ('1', '0'):
         monkeypatch.setenv('PYODESYS_CUDA_STREAMING', flag)
         r1 = rob.integrate(b['x'], b['y0'], b['params'], **kw)
+        # the streaming call screens the status words while it waits for the device; the chunked path leaves that
+        # to the caller (-1)
+        counted = int(lib.pyodesys_cuda_query(b'last_failed_systems'))
+        assert counted == (int((np.array(r1.info.status) != 0).sum()) if flag == '1' else -1), (flag, counted)
         r2 = rob.integrate(np.array([0.0, 1.0, 1e2, 1e4, 1e5]), b['y0'], b['params'], **kw)
         out[flag] = (np.array(r1.yout), np.array(r1.info.status), np.array(r1.info.counters), np.array(r1.info.nreached),
                      np.array(r2.yout), np.array(r2.info.nreached))
